@@ -1,0 +1,119 @@
+/* zsb.h — C ABI of the B200 batched inflate engine (libzsb.so).
+ *
+ * Two surfaces, both plain C (pointers and sizes only, no CUDA/torch types in any signature):
+ *
+ *  (1) The zlib z_stream surface the reference's callers bind:
+ *        inflateInit_      replaces reference src/inflate.c:226-229
+ *        inflateInit2_     replaces reference src/inflate.c:186-224   (windowBits -16 = Deflate64)
+ *        inflate           replaces reference src/inflate.c:597-1275
+ *        inflateEnd        replaces reference src/inflate.c:1277-1287
+ *        inflateReset/inflateReset2/inflateResetKeep   reference src/inflate.c:112-184
+ *      They are declared by the system <zlib.h> (the same header the reference compiles against) and
+ *      are exactly what src/wasm/inflate_stream_wasm.c:26,33,41,49-53, src/wasm/inflate9_stream_wasm.c:
+ *      19,27-30, src/wasm/wasm_stream_common.c:58 and test/payload_decompress.c:124,156,192 call.
+ *      libzsb.so exports them with zlib's signatures; every call runs on the GPU (there is no CPU
+ *      fallback: without a usable CUDA device they return Z_STREAM_ERROR / Z_MEM_ERROR).
+ *
+ *  (2) A thin batch call (new; the throughput surface).  Per member it is defined to be equivalent to
+ *      the reference sequence
+ *          inflateInit2(&s, window_bits); s.next_in/avail_in = in/in_len; s.next_out/avail_out = out/
+ *          out_cap; ret = inflate(&s, Z_FINISH); inflateEnd(&s);
+ *      (test/payload_decompress.c:124-192 with a buffer large enough for one call) and reports what
+ *      that sequence leaves on the z_stream: ret, msg, total_in, total_out, adler, data_type.
+ */
+#ifndef ZSB_H
+#define ZSB_H
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define ZSB_VERSION "0.1.0"
+#if defined(__GNUC__)
+#define ZSB_API __attribute__((visibility("default")))
+#else
+#define ZSB_API
+#endif
+
+/* One independent stream ("member").  in/out may be host or device pointers (all members of one call
+ * must be of the same kind; device pointers must belong to the context's device). */
+typedef struct zsb_member {
+    const void *in;      /* compressed bytes */
+    size_t in_len;       /* < 2^32 (zlib's avail_in is a uInt) */
+    void *out;           /* output buffer; bytes [total_out, out_cap) are unspecified after the call */
+    size_t out_cap;      /* < 2^32 */
+    int32_t window_bits; /* as inflateInit2: -8..-15 raw, -16 raw Deflate64, 8..15 zlib, +16 gzip, +32 auto */
+    int32_t reserved;
+} zsb_member;
+
+/* What the reference leaves on the z_stream after the one-shot sequence above (src/inflate.c:1253-1274). */
+typedef struct zsb_result {
+    int32_t ret;        /* Z_STREAM_END 1, Z_NEED_DICT 2, Z_STREAM_ERROR -2, Z_DATA_ERROR -3, Z_BUF_ERROR -5 */
+    int32_t msg_id;     /* 0 = strm->msg == NULL, else index for zsb_message() */
+    uint64_t total_in;
+    uint64_t total_out;
+    uint32_t check;     /* strm->adler: Adler-32 (zlib) / CRC-32 (gzip) of the output, 0 for raw */
+    int32_t data_type;  /* strm->data_type */
+} zsb_result;
+
+typedef struct zsb_ctx zsb_ctx;
+
+/* Create a context over `ndev` CUDA devices (device ordinals in `devices`; NULL/0 = current device).
+ * Returns NULL when no CUDA device is usable (zsb_create_error() says why). */
+ZSB_API zsb_ctx *zsb_create(const int *devices, int ndev);
+ZSB_API void zsb_destroy(zsb_ctx *ctx);
+ZSB_API const char *zsb_create_error(void);
+ZSB_API const char *zsb_last_error(const zsb_ctx *ctx);
+ZSB_API int zsb_num_devices(const zsb_ctx *ctx);
+
+/* Decode n members.  Host pointers: the batch is sharded over the context's devices by
+ * zsb_plan_shards(), staged through device arenas (host<->device copies included) and the call
+ * returns when every result and output byte is in host memory.  Device pointers: decoded in place on
+ * the first device, results copied to the host array `r`.  Returns 0, or a negative zsb error
+ * (ZSB_E_*) for failures of the call itself (per-member outcomes are in r[i].ret). */
+ZSB_API int zsb_inflate_batch(zsb_ctx *ctx, size_t n, const zsb_member *m, zsb_result *r);
+
+/* Device-resident, asynchronous form (the kernel-only path): `d_members` and `d_results` are device
+ * arrays on device `dev_index` of the context, all in/out pointers are device pointers on it.
+ * `d_order` (optional, device, n x uint32) is the order in which members are handed to the decoder
+ * groups (largest first balances best; NULL = identity).  `wbits_summary` = ZSB_HAS_* flags telling
+ * which optional kernels are needed (0 = derive by inspecting the descriptors, costs a host sync).
+ * Work is enqueued on `cuda_stream` (a cudaStream_t, NULL = default stream); no host sync. */
+ZSB_API int zsb_inflate_batch_device(zsb_ctx *ctx, int dev_index, size_t n, const zsb_member *d_members,
+                             zsb_result *d_results, const uint32_t *d_order, unsigned flags,
+                             void *cuda_stream);
+
+#define ZSB_HAS_WRAPPED 1u /* some member has window_bits >= 0 (header/trailer + checksum kernels needed) */
+#define ZSB_HAS_LARGE   2u /* reserved */
+#define ZSB_RAW_ONLY    4u /* every member has window_bits < 0: skip checksum/trailer kernels */
+
+/* Tuning knobs (0 keeps the default): lanes of a warp that cooperate on one member (1,2,4,8,16,32). */
+ZSB_API int zsb_set_option(zsb_ctx *ctx, const char *name, long value);
+ZSB_API long zsb_get_option(const zsb_ctx *ctx, const char *name);
+
+/* Number of kernels the last zsb_inflate_batch*() call launched (for accounting). */
+ZSB_API long zsb_last_launches(const zsb_ctx *ctx);
+
+/* Length-aware sharding (pure host code, no GPU needed): assigns each of n members with cost
+ * estimate cost[i] to one of nshards shards, longest-processing-time first.  shard_of[i] receives the
+ * shard index; load[s] (optional) the summed cost per shard.  Deterministic. */
+ZSB_API int zsb_plan_shards(size_t n, const uint64_t *cost, int nshards, int32_t *shard_of, uint64_t *load);
+
+/* Pinned host memory for fast host<->device staging. */
+ZSB_API void *zsb_host_alloc(size_t bytes);
+ZSB_API void zsb_host_free(void *p);
+
+/* strm->msg strings (reference src/inflate.c:652...1223, src/inffast.c:172,268,283); NULL for 0. */
+#define ZSB_NUM_MESSAGES 19
+ZSB_API const char *zsb_message(int msg_id);
+
+#define ZSB_E_ARG   (-100)
+#define ZSB_E_CUDA  (-101)
+#define ZSB_E_NOMEM (-102)
+
+#ifdef __cplusplus
+}
+#endif
+#endif

@@ -1,0 +1,502 @@
+// zsb_host.cu — host side of libzsb.so: contexts, the length-aware scheduler, staging, kernel launches.
+// C over the CUDA runtime; the only entry points are the extern "C" functions of include/zsb.h.
+// There is no CPU decode path in this library: every member is decoded by k_inflate on the GPU.
+#include <cuda_runtime.h>
+#include <algorithm>
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include <string>
+#include <vector>
+#include "zsb_kernels.cuh"
+#include "zsb_internal.h"
+
+using namespace zsb;
+
+static thread_local char g_create_err[256] = "";
+
+#define CK(ctx, call)                                                                              \
+    do {                                                                                           \
+        cudaError_t e_ = (call);                                                                   \
+        if (e_ != cudaSuccess) {                                                                   \
+            snprintf((ctx)->err, sizeof((ctx)->err), "%s:%d %s: %s", __FILE__, __LINE__, #call,    \
+                     cudaGetErrorString(e_));                                                      \
+            return ZSB_E_CUDA;                                                                     \
+        }                                                                                          \
+    } while (0)
+
+static const char *const k_messages[ZSB_NUM_MESSAGES] = {
+    nullptr,
+    "incorrect header check",
+    "unknown compression method",
+    "invalid window size",
+    "unknown header flags set",
+    "header crc mismatch",
+    "invalid block type",
+    "invalid stored block lengths",
+    "too many length or distance symbols",
+    "invalid code lengths set",
+    "invalid bit length repeat",
+    "invalid code -- missing end-of-block",
+    "invalid literal/lengths set",
+    "invalid distances set",
+    "invalid literal/length code",
+    "invalid distance code",
+    "invalid distance too far back",
+    "incorrect data check",
+    "incorrect length check",
+};
+
+extern "C" const char *zsb_message(int id) {
+    return (id > 0 && id < ZSB_NUM_MESSAGES) ? k_messages[id] : nullptr;
+}
+extern "C" const char *zsb_create_error(void) { return g_create_err; }
+extern "C" const char *zsb_last_error(const zsb_ctx *ctx) { return ctx ? ctx->err : g_create_err; }
+extern "C" int zsb_num_devices(const zsb_ctx *ctx) { return ctx ? (int)ctx->devs.size() : 0; }
+extern "C" long zsb_last_launches(const zsb_ctx *ctx) { return ctx ? ctx->launches : 0; }
+
+extern "C" void *zsb_host_alloc(size_t bytes) {
+    void *p = nullptr;
+    if (cudaHostAlloc(&p, bytes ? bytes : 1, cudaHostAllocPortable) != cudaSuccess) return nullptr;
+    return p;
+}
+extern "C" void zsb_host_free(void *p) {
+    if (p) cudaFreeHost(p);
+}
+
+// ---- length-aware sharding: longest processing time first --------------------------------------
+extern "C" int zsb_plan_shards(size_t n, const uint64_t *cost, int nshards, int32_t *shard_of, uint64_t *load) {
+    if (nshards < 1 || (n && (!cost || !shard_of))) return ZSB_E_ARG;
+    std::vector<uint64_t> ld((size_t)nshards, 0);
+    std::vector<uint32_t> idx(n);
+    for (size_t i = 0; i < n; i++) idx[i] = (uint32_t)i;
+    std::stable_sort(idx.begin(), idx.end(), [&](uint32_t a, uint32_t b) { return cost[a] > cost[b]; });
+    for (size_t k = 0; k < n; k++) {
+        int best = 0;
+        for (int s = 1; s < nshards; s++)
+            if (ld[s] < ld[best]) best = s;
+        shard_of[idx[k]] = best;
+        ld[best] += cost[idx[k]] ? cost[idx[k]] : 1;
+    }
+    if (load)
+        for (int s = 0; s < nshards; s++) load[s] = ld[s];
+    return 0;
+}
+
+template <int G>
+static int launch_inflate(zsb_ctx *ctx, zsb_dev &dv, size_t n, const zsb_member *dm, zsb_result *dr,
+                          const uint32_t *dorder, cudaStream_t st) {
+    using GG = Geo<G>;
+    auto kern = k_inflate<G>;
+    if (!dv.configured[G]) {
+        CK(ctx, cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)GG::smem));
+        int occ = 0;
+        CK(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, kern, GG::threads, GG::smem));
+        if (occ < 1) {
+            snprintf(ctx->err, sizeof ctx->err, "k_inflate<%d> does not fit an SM", G);
+            return ZSB_E_CUDA;
+        }
+        dv.occ[G] = occ;
+        dv.configured[G] = true;
+    }
+    size_t want = (n + GG::members - 1) / GG::members;
+    size_t cap = (size_t)dv.sm_count * dv.occ[G];
+    unsigned grid = (unsigned)std::max<size_t>(1, std::min(want, cap));
+    kern<<<grid, GG::threads, GG::smem, st>>>(dm, dr, dv.aux, dorder, (uint32_t)n, dv.counters, dv.fixed);
+    ctx->launches++;
+    CK(ctx, cudaGetLastError());
+    return 0;
+}
+
+static int ensure_aux(zsb_ctx *ctx, zsb_dev &dv, size_t n) {
+    if (n <= dv.aux_cap) return 0;
+    if (dv.aux) CK(ctx, cudaFree(dv.aux));
+    dv.aux = nullptr;
+    dv.aux_cap = 0;
+    size_t cap = std::max<size_t>(n, 1024);
+    CK(ctx, cudaMalloc(&dv.aux, cap * sizeof(Aux)));
+    dv.aux_cap = cap;
+    return 0;
+}
+
+static int run_device(zsb_ctx *ctx, zsb_dev &dv, size_t n, const zsb_member *dm, zsb_result *dr,
+                      const uint32_t *dorder, unsigned flags, cudaStream_t st) {
+    if (n == 0) return 0;
+    if (n > 0xffffff00ull) return ZSB_E_ARG;
+    int rc = ensure_aux(ctx, dv, n);
+    if (rc) return rc;
+    CK(ctx, cudaMemsetAsync(dv.counters, 0, 2 * sizeof(uint32_t), st));
+    switch (ctx->lanes) {
+    case 1: rc = launch_inflate<1>(ctx, dv, n, dm, dr, dorder, st); break;
+    case 2: rc = launch_inflate<2>(ctx, dv, n, dm, dr, dorder, st); break;
+    case 4: rc = launch_inflate<4>(ctx, dv, n, dm, dr, dorder, st); break;
+    case 8: rc = launch_inflate<8>(ctx, dv, n, dm, dr, dorder, st); break;
+    case 16: rc = launch_inflate<16>(ctx, dv, n, dm, dr, dorder, st); break;
+    default: rc = launch_inflate<32>(ctx, dv, n, dm, dr, dorder, st); break;
+    }
+    if (rc) return rc;
+    if (!(flags & ZSB_RAW_ONLY)) {
+        unsigned grid = (unsigned)std::min<size_t>(n, (size_t)dv.sm_count * 8);
+        k_check<<<grid, CHK_THREADS, 0, st>>>(dm, dr, dv.aux, (uint32_t)n, dv.counters + 1);
+        ctx->launches++;
+        CK(ctx, cudaGetLastError());
+    }
+    return 0;
+}
+
+// ---- contexts ----------------------------------------------------------------------------------
+static int init_device(zsb_ctx *ctx, zsb_dev &dv, int device) {
+    dv.device = device;
+    CK(ctx, cudaSetDevice(device));
+    cudaDeviceProp prop;
+    CK(ctx, cudaGetDeviceProperties(&prop, device));
+    if (prop.major < 10) {
+        snprintf(ctx->err, sizeof ctx->err, "device %d is sm_%d%d; libzsb is built for sm_100a only", device,
+                 prop.major, prop.minor);
+        return ZSB_E_CUDA;
+    }
+    dv.sm_count = prop.multiProcessorCount;
+    CK(ctx, cudaStreamCreateWithFlags(&dv.stream, cudaStreamNonBlocking));
+    CK(ctx, cudaStreamCreateWithFlags(&dv.copy_stream, cudaStreamNonBlocking));
+    CK(ctx, cudaMalloc(&dv.fixed, STREAM_BYTES));
+    CK(ctx, cudaMalloc(&dv.counters, 4 * sizeof(uint32_t)));
+    CrcConsts cc;
+    cc.x2n[0] = 0x40000000u;
+    for (int k = 1; k < 40; k++) cc.x2n[k] = gf2_mul(cc.x2n[k - 1], cc.x2n[k - 1]);
+    auto xpow = [&](uint64_t nbits) {
+        uint32_t r = 0x80000000u;
+        for (int k = 0; nbits; k++, nbits >>= 1)
+            if (nbits & 1) r = gf2_mul(r, cc.x2n[k]);
+        return r;
+    };
+    cc.tile_skip = xpow(8ull * (CHK_TILE - CHK_SPAN));
+    for (int k = 0; k < 8; k++) cc.span_pow[k] = xpow((8ull * CHK_SPAN) << k);
+    CK(ctx, cudaMemcpyToSymbol(c_crc, &cc, sizeof cc));
+    k_build_fixed<<<1, 128, 0, dv.stream>>>(dv.fixed);
+    CK(ctx, cudaGetLastError());
+    CK(ctx, cudaStreamSynchronize(dv.stream));
+    return 0;
+}
+
+static void free_device(zsb_dev &dv) {
+    cudaSetDevice(dv.device);
+    if (dv.stream) cudaStreamDestroy(dv.stream);
+    if (dv.copy_stream) cudaStreamDestroy(dv.copy_stream);
+    cudaFree(dv.fixed);
+    cudaFree(dv.counters);
+    cudaFree(dv.aux);
+    cudaFree(dv.d_in);
+    cudaFree(dv.d_out);
+    cudaFree(dv.d_desc);
+    if (dv.h_desc) cudaFreeHost(dv.h_desc);
+}
+
+extern "C" zsb_ctx *zsb_create(const int *devices, int ndev) {
+    g_create_err[0] = 0;
+    int count = 0;
+    cudaError_t e = cudaGetDeviceCount(&count);
+    if (e != cudaSuccess || count == 0) {
+        snprintf(g_create_err, sizeof g_create_err, "no CUDA device: %s (libzsb has no CPU path)",
+                 e != cudaSuccess ? cudaGetErrorString(e) : "device count is 0");
+        return nullptr;
+    }
+    zsb_ctx *ctx = new zsb_ctx();
+    int cur = 0;
+    cudaGetDevice(&cur);
+    std::vector<int> devs;
+    if (!devices || ndev <= 0) devs.push_back(cur);
+    else devs.assign(devices, devices + ndev);
+    ctx->devs.resize(devs.size());
+    for (size_t i = 0; i < devs.size(); i++) {
+        if (devs[i] < 0 || devs[i] >= count || init_device(ctx, ctx->devs[i], devs[i]) != 0) {
+            if (!ctx->err[0]) snprintf(ctx->err, sizeof ctx->err, "bad device ordinal %d", devs[i]);
+            snprintf(g_create_err, sizeof g_create_err, "%s", ctx->err);
+            for (size_t k = 0; k <= i; k++) free_device(ctx->devs[k]);
+            delete ctx;
+            cudaSetDevice(cur);
+            return nullptr;
+        }
+    }
+    cudaSetDevice(cur);
+    return ctx;
+}
+
+extern "C" void zsb_destroy(zsb_ctx *ctx) {
+    if (!ctx) return;
+    int cur = 0;
+    cudaGetDevice(&cur);
+    for (auto &dv : ctx->devs) free_device(dv);
+    cudaSetDevice(cur);
+    delete ctx;
+}
+
+extern "C" int zsb_set_option(zsb_ctx *ctx, const char *name, long value) {
+    if (!ctx || !name) return ZSB_E_ARG;
+    if (!strcmp(name, "lanes_per_member")) {
+        if (value != 1 && value != 2 && value != 4 && value != 8 && value != 16 && value != 32) return ZSB_E_ARG;
+        ctx->lanes = (int)value;
+        return 0;
+    }
+    if (!strcmp(name, "slab_bytes")) {
+        if (value < (1 << 20)) return ZSB_E_ARG;
+        ctx->slab_bytes = (size_t)value;
+        return 0;
+    }
+    return ZSB_E_ARG;
+}
+extern "C" long zsb_get_option(const zsb_ctx *ctx, const char *name) {
+    if (!ctx || !name) return ZSB_E_ARG;
+    if (!strcmp(name, "lanes_per_member")) return ctx->lanes;
+    if (!strcmp(name, "slab_bytes")) return (long)ctx->slab_bytes;
+    if (!strcmp(name, "sm_count")) return ctx->devs.empty() ? 0 : ctx->devs[0].sm_count;
+    return ZSB_E_ARG;
+}
+
+extern "C" int zsb_inflate_batch_device(zsb_ctx *ctx, int dev_index, size_t n, const zsb_member *d_members,
+                                        zsb_result *d_results, const uint32_t *d_order, unsigned flags,
+                                        void *cuda_stream) {
+    if (!ctx || dev_index < 0 || dev_index >= (int)ctx->devs.size() || (n && (!d_members || !d_results)))
+        return ZSB_E_ARG;
+    zsb_dev &dv = ctx->devs[dev_index];
+    int cur = 0;
+    cudaGetDevice(&cur);
+    if (cur != dv.device) CK(ctx, cudaSetDevice(dv.device));
+    ctx->launches = 0;
+    int rc = run_device(ctx, dv, n, d_members, d_results, d_order, flags, (cudaStream_t)cuda_stream);
+    if (cur != dv.device) cudaSetDevice(cur);
+    return rc;
+}
+
+// ---- host-pointer batches: shard, stage, decode, return ------------------------------------------
+template <typename T> static int grow(zsb_ctx *ctx, T *&p, size_t &cap, size_t need) {
+    if (need <= cap) return 0;
+    if (p) CK(ctx, cudaFree(p));
+    p = nullptr;
+    cap = 0;
+    size_t want = need + need / 8 + 4096;
+    CK(ctx, cudaMalloc(&p, want));
+    cap = want;
+    return 0;
+}
+
+struct Shard {
+    std::vector<uint32_t> idx;       // members of this shard, in address order of their inputs
+    bool dense_in = false, dense_out = false;
+    const uint8_t *hin_base = nullptr;
+    uint8_t *hout_base = nullptr;
+    size_t in_span = 0, out_span = 0;
+    std::vector<size_t> in_off, out_off;
+};
+
+static void plan_layout(const zsb_member *m, Shard &sh) {
+    const size_t k = sh.idx.size();
+    sh.in_off.resize(k);
+    sh.out_off.resize(k);
+    // dense test: ascending, non-overlapping, and the span is not much larger than the payload
+    auto dense = [&](bool out) {
+        size_t sum = 0;
+        uintptr_t lo = ~(uintptr_t)0, hi = 0, prev_end = 0;
+        for (size_t j = 0; j < k; j++) {
+            const zsb_member &x = m[sh.idx[j]];
+            uintptr_t p = out ? (uintptr_t)x.out : (uintptr_t)x.in;
+            size_t len = out ? x.out_cap : x.in_len;
+            if (len == 0) continue;
+            if (p < prev_end) return false;
+            prev_end = p + len;
+            lo = std::min(lo, p);
+            hi = std::max(hi, p + len);
+            sum += len;
+        }
+        if (sum == 0) return false;
+        return (hi - lo) <= sum + sum / 4 + (64u << 10);
+    };
+    sh.dense_in = dense(false);
+    sh.dense_out = dense(true);
+    size_t off = 0;
+    if (sh.dense_in) {
+        uintptr_t lo = ~(uintptr_t)0, hi = 0;
+        for (uint32_t i : sh.idx)
+            if (m[i].in_len) lo = std::min(lo, (uintptr_t)m[i].in), hi = std::max(hi, (uintptr_t)m[i].in + m[i].in_len);
+        uintptr_t base = lo & ~(uintptr_t)255;
+        sh.hin_base = (const uint8_t *)base;
+        sh.in_span = hi - base;
+        for (size_t j = 0; j < k; j++) sh.in_off[j] = m[sh.idx[j]].in_len ? (uintptr_t)m[sh.idx[j]].in - base : 0;
+    } else {
+        for (size_t j = 0; j < k; j++) {
+            sh.in_off[j] = off;
+            off += (m[sh.idx[j]].in_len + 15) & ~(size_t)15;
+        }
+        sh.in_span = off;
+    }
+    off = 0;
+    if (sh.dense_out) {
+        uintptr_t lo = ~(uintptr_t)0, hi = 0;
+        for (uint32_t i : sh.idx)
+            if (m[i].out_cap) lo = std::min(lo, (uintptr_t)m[i].out), hi = std::max(hi, (uintptr_t)m[i].out + m[i].out_cap);
+        uintptr_t base = lo & ~(uintptr_t)255;
+        sh.hout_base = (uint8_t *)base;
+        sh.out_span = hi - base;
+        for (size_t j = 0; j < k; j++) sh.out_off[j] = m[sh.idx[j]].out_cap ? (uintptr_t)m[sh.idx[j]].out - base : 0;
+    } else {
+        for (size_t j = 0; j < k; j++) {
+            sh.out_off[j] = off;
+            off += (m[sh.idx[j]].out_cap + 15) & ~(size_t)15;
+        }
+        sh.out_span = off;
+    }
+}
+
+static int batch_host(zsb_ctx *ctx, size_t n, const zsb_member *m, zsb_result *r) {
+    const int nd = (int)ctx->devs.size();
+    std::vector<int32_t> shard_of(n, 0);
+    if (nd > 1) {
+        std::vector<uint64_t> cost(n);
+        for (size_t i = 0; i < n; i++) cost[i] = (uint64_t)m[i].in_len + m[i].out_cap;
+        zsb_plan_shards(n, cost.data(), nd, shard_of.data(), nullptr);
+    }
+    std::vector<Shard> shards(nd);
+    for (size_t i = 0; i < n; i++) shards[shard_of[i]].idx.push_back((uint32_t)i);
+    bool raw_only = true;
+    for (size_t i = 0; i < n; i++) raw_only &= m[i].window_bits < 0;
+    const unsigned flags = raw_only ? ZSB_RAW_ONLY : ZSB_HAS_WRAPPED;
+    ctx->launches = 0;
+
+    // enqueue everything on every device, then drain
+    for (int s = 0; s < nd; s++) {
+        Shard &sh = shards[s];
+        zsb_dev &dv = ctx->devs[s];
+        const size_t k = sh.idx.size();
+        if (!k) continue;
+        CK(ctx, cudaSetDevice(dv.device));
+        plan_layout(m, sh);
+        int rc;
+        if ((rc = grow(ctx, dv.d_in, dv.d_in_cap, sh.in_span + 256))) return rc;
+        if ((rc = grow(ctx, dv.d_out, dv.d_out_cap, sh.out_span + 256))) return rc;
+        const size_t desc_bytes = k * (sizeof(zsb_member) + sizeof(zsb_result) + sizeof(uint32_t)) + 64;
+        if ((rc = grow(ctx, dv.d_desc, dv.d_desc_cap, desc_bytes))) return rc;
+        if (desc_bytes > dv.h_desc_cap) {
+            if (dv.h_desc) CK(ctx, cudaFreeHost(dv.h_desc));
+            dv.h_desc = nullptr;
+            CK(ctx, cudaHostAlloc(&dv.h_desc, desc_bytes + desc_bytes / 8, cudaHostAllocDefault));
+            dv.h_desc_cap = desc_bytes + desc_bytes / 8;
+        }
+        zsb_member *hm = (zsb_member *)dv.h_desc;
+        zsb_result *hr = (zsb_result *)(hm + k);
+        uint32_t *ho = (uint32_t *)(hr + k);
+        zsb_member *dm = (zsb_member *)dv.d_desc;
+        zsb_result *dr = (zsb_result *)(dm + k);
+        uint32_t *dord = (uint32_t *)(dr + k);
+        for (size_t j = 0; j < k; j++) {
+            const zsb_member &x = m[sh.idx[j]];
+            hm[j] = x;
+            hm[j].in = x.in ? dv.d_in + sh.in_off[j] : nullptr;
+            hm[j].out = x.out ? dv.d_out + sh.out_off[j] : nullptr;
+            if (x.in_len > 0xfffffff0ull || x.out_cap > 0xfffffff0ull) hm[j].window_bits = 1000;  // -> Z_STREAM_ERROR
+            ho[j] = (uint32_t)j;
+        }
+        // largest first: the persistent decoder groups then finish together
+        std::stable_sort(ho, ho + k, [&](uint32_t a, uint32_t b) {
+            return hm[a].in_len + hm[a].out_cap > hm[b].in_len + hm[b].out_cap;
+        });
+        cudaStream_t st = dv.stream;
+        CK(ctx, cudaMemcpyAsync(dm, hm, k * sizeof(zsb_member), cudaMemcpyHostToDevice, st));
+        CK(ctx, cudaMemcpyAsync(dord, ho, k * sizeof(uint32_t), cudaMemcpyHostToDevice, st));
+        if (sh.dense_in) {
+            const uint8_t *src = sh.hin_base;
+            // the 256-byte align-down may reach below the first member: start at the first real byte
+            size_t first = ~(size_t)0;
+            for (size_t j = 0; j < k; j++)
+                if (m[sh.idx[j]].in_len) first = std::min(first, sh.in_off[j]);
+            if (first != ~(size_t)0)
+                CK(ctx, cudaMemcpyAsync(dv.d_in + first, src + first, sh.in_span - first, cudaMemcpyHostToDevice, st));
+        } else {
+            for (size_t j = 0; j < k; j++)
+                if (m[sh.idx[j]].in_len)
+                    CK(ctx, cudaMemcpyAsync(dv.d_in + sh.in_off[j], m[sh.idx[j]].in, m[sh.idx[j]].in_len,
+                                            cudaMemcpyHostToDevice, st));
+        }
+        if ((rc = run_device(ctx, dv, k, dm, dr, dord, flags, st))) return rc;
+        CK(ctx, cudaMemcpyAsync(hr, dr, k * sizeof(zsb_result), cudaMemcpyDeviceToHost, st));
+        if (sh.dense_out) {
+            size_t first = ~(size_t)0;
+            for (size_t j = 0; j < k; j++)
+                if (m[sh.idx[j]].out_cap) first = std::min(first, sh.out_off[j]);
+            if (first != ~(size_t)0)
+                CK(ctx, cudaMemcpyAsync(sh.hout_base + first, dv.d_out + first, sh.out_span - first,
+                                        cudaMemcpyDeviceToHost, st));
+        }
+    }
+    for (int s = 0; s < nd; s++) {
+        Shard &sh = shards[s];
+        zsb_dev &dv = ctx->devs[s];
+        const size_t k = sh.idx.size();
+        if (!k) continue;
+        CK(ctx, cudaSetDevice(dv.device));
+        CK(ctx, cudaStreamSynchronize(dv.stream));
+        zsb_result *hr = (zsb_result *)((zsb_member *)dv.h_desc + k);
+        for (size_t j = 0; j < k; j++) r[sh.idx[j]] = hr[j];
+        if (!sh.dense_out) {
+            for (size_t j = 0; j < k; j++) {
+                const zsb_member &x = m[sh.idx[j]];
+                size_t nb = std::min<size_t>(hr[j].total_out, x.out_cap);
+                if (nb && x.out)
+                    CK(ctx, cudaMemcpyAsync(x.out, dv.d_out + sh.out_off[j], nb, cudaMemcpyDeviceToHost, dv.stream));
+            }
+            CK(ctx, cudaStreamSynchronize(dv.stream));
+        }
+    }
+    return 0;
+}
+
+static int batch_device_ptrs(zsb_ctx *ctx, size_t n, const zsb_member *m, zsb_result *r) {
+    zsb_dev &dv = ctx->devs[0];
+    CK(ctx, cudaSetDevice(dv.device));
+    int rc;
+    const size_t desc_bytes = n * (sizeof(zsb_member) + sizeof(zsb_result) + sizeof(uint32_t)) + 64;
+    if ((rc = grow(ctx, dv.d_desc, dv.d_desc_cap, desc_bytes))) return rc;
+    zsb_member *dm = (zsb_member *)dv.d_desc;
+    zsb_result *dr = (zsb_result *)(dm + n);
+    uint32_t *dord = (uint32_t *)(dr + n);
+    std::vector<uint32_t> ord(n);
+    bool raw_only = true;
+    for (size_t i = 0; i < n; i++) {
+        ord[i] = (uint32_t)i;
+        raw_only &= m[i].window_bits < 0;
+    }
+    std::stable_sort(ord.begin(), ord.end(), [&](uint32_t a, uint32_t b) {
+        return m[a].in_len + m[a].out_cap > m[b].in_len + m[b].out_cap;
+    });
+    std::vector<zsb_member> mm(m, m + n);
+    for (auto &x : mm)
+        if (x.in_len > 0xfffffff0ull || x.out_cap > 0xfffffff0ull) x.window_bits = 1000;
+    cudaStream_t st = dv.stream;
+    CK(ctx, cudaMemcpyAsync(dm, mm.data(), n * sizeof(zsb_member), cudaMemcpyHostToDevice, st));
+    CK(ctx, cudaMemcpyAsync(dord, ord.data(), n * sizeof(uint32_t), cudaMemcpyHostToDevice, st));
+    ctx->launches = 0;
+    if ((rc = run_device(ctx, dv, n, dm, dr, dord, raw_only ? ZSB_RAW_ONLY : ZSB_HAS_WRAPPED, st))) return rc;
+    CK(ctx, cudaMemcpyAsync(r, dr, n * sizeof(zsb_result), cudaMemcpyDeviceToHost, st));
+    CK(ctx, cudaStreamSynchronize(st));
+    return 0;
+}
+
+extern "C" int zsb_inflate_batch(zsb_ctx *ctx, size_t n, const zsb_member *m, zsb_result *r) {
+    if (!ctx || (n && (!m || !r))) return ZSB_E_ARG;
+    if (n == 0) return 0;
+    int cur = 0;
+    cudaGetDevice(&cur);
+    // host or device pointers?  decided by the first member that has any buffer
+    bool device_ptrs = false;
+    for (size_t i = 0; i < n; i++) {
+        const void *p = m[i].in ? m[i].in : m[i].out;
+        if (!p) continue;
+        cudaPointerAttributes at;
+        if (cudaPointerGetAttributes(&at, p) == cudaSuccess)
+            device_ptrs = at.type == cudaMemoryTypeDevice || at.type == cudaMemoryTypeManaged;
+        else
+            cudaGetLastError();
+        break;
+    }
+    int rc = device_ptrs ? batch_device_ptrs(ctx, n, m, r) : batch_host(ctx, n, m, r);
+    cudaSetDevice(cur);
+    return rc;
+}

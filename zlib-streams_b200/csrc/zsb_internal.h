@@ -1,0 +1,33 @@
+// zsb_internal.h — host-side context layout shared by zsb_host.cu and zsb_zstream.cu.
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include <vector>
+#include "../../include/zsb.h"
+
+namespace zsb { struct Aux; }
+
+struct zsb_dev {
+    int device = 0;
+    int sm_count = 0;
+    cudaStream_t stream = nullptr, copy_stream = nullptr;
+    uint16_t *fixed = nullptr;         // prebuilt fixed-code tables (one member slot)
+    uint32_t *counters = nullptr;      // [0] decode work counter, [1] check work counter
+    zsb::Aux *aux = nullptr;
+    size_t aux_cap = 0;
+    // staging arenas for host-pointer batches
+    uint8_t *d_in = nullptr, *d_out = nullptr, *d_desc = nullptr;
+    size_t d_in_cap = 0, d_out_cap = 0, d_desc_cap = 0;
+    uint8_t *h_desc = nullptr;
+    size_t h_desc_cap = 0;
+    bool configured[33] = {};
+    int occ[33] = {};
+};
+
+struct zsb_ctx {
+    std::vector<zsb_dev> devs;
+    int lanes = 32;                    // lanes of a warp that cooperate on one member
+    size_t slab_bytes = 256u << 20;
+    long launches = 0;
+    char err[256] = "";
+};

@@ -1,0 +1,214 @@
+// zsb_kernels.cuh — the three kernels of the batched inflate engine (sm_100a):
+//   k_inflate<G>   decode: wrapper header, block headers + table build in shared memory, symbol loop,
+//                  LZ77 copies, stored blocks.  One group of G lanes per member, persistent CTAs that
+//                  fetch members from a global counter (largest first when an order is supplied).
+//   k_check        Adler-32 / CRC-32 of each wrapped member's output and the trailer checks
+//                  (reference src/inflate.c:1194-1232 and UPDATE_CHECK :424-429), one CTA per member.
+//   k_build_fixed  the fixed-code tables (reference src/inflate.c:260-298), once per context.
+#pragma once
+#include "zsb_device.cuh"
+
+namespace zsb {
+
+// CTA size per group width: as many member slots as shared memory holds (96 x 2384 B), one CTA per SM
+// (two for G = 32, which is limited by the 1024-thread CTA instead).
+template <int G> struct Geo {
+    static constexpr int S = 32 / G;
+    static constexpr int threads = G == 1 ? 96 : G == 2 ? 192 : G == 4 ? 384 : G == 8 ? 768 : G == 16 ? 1024 : 512;
+    static constexpr int min_ctas = G == 32 ? 2 : 1;
+    static constexpr int members = threads / 32 * S;
+    static constexpr size_t smem = LUT_BYTES + (size_t)members * STREAM_BYTES;
+};
+
+template <int G>
+__global__ void __launch_bounds__(Geo<G>::threads, Geo<G>::min_ctas) k_inflate(const zsb_member *__restrict__ members, zsb_result *__restrict__ results,
+                          Aux *__restrict__ aux, const uint32_t *__restrict__ order, uint32_t n,
+                          uint32_t *counter, const uint16_t *__restrict__ fixed_tab) {
+    extern __shared__ __align__(16) uint8_t smem[];
+    uint32_t *lut = (uint32_t *)smem;
+    init_lut(lut, threadIdx.x, blockDim.x);
+    __syncthreads();
+    constexpr int S = 32 / G;
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int sub = lane % G, grp = lane / G;
+    uint16_t *T = (uint16_t *)(smem + LUT_BYTES) + (size_t)(warp * S + grp) * STREAM_U16;
+    const unsigned gmask = G == 32 ? 0xffffffffu : (((1u << G) - 1u) << (grp * G));
+    for (;;) {
+        uint32_t slot = 0;
+        if (sub == 0) slot = atomicAdd(counter, 1u);
+        slot = grp_bcast<G>(slot, gmask);
+        if (slot >= n) break;
+        uint32_t idx = order ? order[slot] : slot;
+        decode_member<G>(members[idx], results + idx, aux + idx, T, lut, fixed_tab, sub, gmask);
+    }
+}
+
+__global__ void k_build_fixed(uint16_t *fixed_tab) {
+    __shared__ __align__(16) uint16_t T[STREAM_U16];
+    if (threadIdx.x == 0) build_fixed(T);
+    __syncthreads();
+    for (int i = threadIdx.x; i < STREAM_U16; i += blockDim.x) fixed_tab[i] = T[i];
+}
+
+// ------------------------------------------------------------------------------------------------
+// Checksums.  CRC-32 (ISO-HDLC, reflected 0xEDB88320) and Adler-32 (RFC 1950) are the published
+// definitions the reference takes from madler/zlib crc32.c / adler32.c (submodule absent there).
+// CRC: 128 lanes own 256-byte spans of a 32 KiB tile, tiles are aligned to the END of the data so the
+// ragged part is a run of leading zeros (which do not change a zero register); a lane's register is
+// carried from tile to tile by multiplying with x^(8*(TILE-SPAN)), and lanes are merged by a tree of
+// multiplications with x^(8*SPAN*2^k).  Adler: s1 = 1 + sum(b), s2 = n + n*sum(b) - sum(i*b_i).
+// ------------------------------------------------------------------------------------------------
+constexpr uint32_t CRC_POLY = 0xEDB88320u;
+constexpr int CHK_THREADS = 128;
+constexpr uint32_t CHK_SPAN = 256;
+constexpr uint32_t CHK_TILE = CHK_THREADS * CHK_SPAN;
+
+// a(x)*b(x) mod P in the reflected representation (bit 31 is x^0)
+__host__ __device__ inline uint32_t gf2_mul(uint32_t a, uint32_t b) {
+    uint32_t p = 0;
+    for (int i = 0; i < 32; i++) {
+        if (a & (0x80000000u >> i)) p ^= b;
+        b = (b >> 1) ^ (CRC_POLY & (0u - (b & 1u)));
+    }
+    return p;
+}
+
+struct CrcConsts {
+    uint32_t x2n[40];      // x^(2^k) mod P
+    uint32_t tile_skip;    // x^(8*(TILE-SPAN))
+    uint32_t span_pow[8];  // x^(8*SPAN*2^k)
+};
+__constant__ CrcConsts c_crc;
+
+__device__ __forceinline__ uint32_t crc_xpow(uint64_t nbits) {
+    uint32_t r = 0x80000000u;
+    for (int k = 0; nbits; k++, nbits >>= 1)
+        if (nbits & 1) r = gf2_mul(r, c_crc.x2n[k]);
+    return r;
+}
+
+__device__ __forceinline__ uint32_t crc_span(uint32_t s, const uint8_t *p, uint32_t n, const uint32_t (*tab)[256]) {
+    while (n && ((uintptr_t)p & 3)) {
+        s = tab[0][(s ^ *p++) & 0xff] ^ (s >> 8);
+        n--;
+    }
+    const uint32_t *w = (const uint32_t *)p;
+    uint32_t nw = n >> 2;
+    for (uint32_t i = 0; i < nw; i++) {
+        s ^= w[i];
+        s = tab[3][s & 0xff] ^ tab[2][(s >> 8) & 0xff] ^ tab[1][(s >> 16) & 0xff] ^ tab[0][s >> 24];
+    }
+    p += nw * 4;
+    n &= 3;
+    while (n--) s = tab[0][(s ^ *p++) & 0xff] ^ (s >> 8);
+    return s;
+}
+
+__global__ void __launch_bounds__(CHK_THREADS)
+k_check(const zsb_member *__restrict__ members, zsb_result *__restrict__ results, const Aux *__restrict__ aux,
+        uint32_t n, uint32_t *counter) {
+    __shared__ uint32_t tab[4][256];
+    __shared__ uint32_t s_idx;
+    __shared__ uint32_t red[CHK_THREADS / 32][2];
+    __shared__ unsigned long long red64[CHK_THREADS / 32][2];
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    for (int i = tid; i < 256; i += CHK_THREADS) {
+        uint32_t c = i;
+        for (int k = 0; k < 8; k++) c = (c >> 1) ^ (CRC_POLY & (0u - (c & 1u)));
+        tab[0][i] = c;
+    }
+    __syncthreads();
+    for (int k = 1; k < 4; k++) {
+        for (int i = tid; i < 256; i += CHK_THREADS) {
+            uint32_t c = tab[k - 1][i];
+            tab[k][i] = (c >> 8) ^ tab[0][c & 0xff];
+        }
+        __syncthreads();
+    }
+    for (;;) {
+        if (tid == 0) s_idx = atomicAdd(counter, 1u);
+        __syncthreads();
+        const uint32_t idx = s_idx;
+        __syncthreads();
+        if (idx >= n) break;
+        const Aux a = aux[idx];
+        if (a.kind == 0) continue;
+        const uint8_t *out = (const uint8_t *)members[idx].out;
+        const uint32_t E = (uint32_t)results[idx].total_out;
+        uint32_t check = a.init_check;
+        if (E > 0 && a.kind == 2) {
+            // ---- CRC-32 ----
+            uint32_t s = 0;
+            const uint32_t ntiles = (E + CHK_TILE - 1) / CHK_TILE;
+            for (uint32_t t = ntiles; t-- > 0;) {            // t = tile index counted from the end
+                long long lo = (long long)E - (long long)(t + 1) * CHK_TILE + (long long)tid * CHK_SPAN;
+                long long hi = lo + CHK_SPAN;
+                if (hi > 0) {
+                    if (lo < 0) lo = 0;
+                    s = crc_span(s, out + lo, (uint32_t)(hi - lo), tab);
+                }
+                if (t) s = gf2_mul(c_crc.tile_skip, s);
+            }
+            // merge lanes: value(tid) * x^(8*SPAN*(127-tid))
+            for (int k = 0; k < 5; k++) {
+                uint32_t o = __shfl_down_sync(0xffffffffu, s, 1 << k);
+                if ((lane & ((2 << k) - 1)) == 0) s = gf2_mul(c_crc.span_pow[k], s) ^ o;
+            }
+            if (lane == 0) red[warp][0] = s;
+            __syncthreads();
+            if (tid == 0) {
+                uint32_t z = red[0][0];
+                for (int wv = 1; wv < CHK_THREADS / 32; wv++) z = gf2_mul(c_crc.span_pow[5], z) ^ red[wv][0];
+                check = ~(gf2_mul(crc_xpow(8ull * E), 0xFFFFFFFFu) ^ z);
+            }
+            __syncthreads();
+        } else if (E > 0) {
+            // ---- Adler-32 ----
+            const uint32_t P = 65521u;
+            unsigned long long S = 0, W = 0;
+            uint32_t head = (uint32_t)((4 - ((uintptr_t)out & 3)) & 3);
+            if (head > E) head = E;
+            const uint32_t nw = (E - head) >> 2;
+            const uint32_t *w32 = (const uint32_t *)(out + head);
+            uint32_t im = (head + 4u * tid) % P;             // byte index of this thread's word, mod P
+            const uint32_t step = (4u * CHK_THREADS) % P;
+            for (uint32_t w = tid; w < nw; w += CHK_THREADS) {
+                uint32_t v = w32[w];
+                uint32_t sb = __dp4a(v, 0x01010101u, 0u);
+                uint32_t q = __dp4a(v, 0x03020100u, 0u);
+                S += sb;
+                W += (unsigned long long)im * sb + q;
+                im += step;
+                if (im >= P) im -= P;
+            }
+            if (tid == 0) {
+                for (uint32_t i = 0; i < head; i++) { S += out[i]; W += (unsigned long long)i * out[i]; }
+                for (uint32_t i = head + 4 * nw; i < E; i++) { S += out[i]; W += (unsigned long long)(i % P) * out[i]; }
+            }
+            S %= P; W %= P;
+            for (int o = 16; o; o >>= 1) {
+                S += __shfl_down_sync(0xffffffffu, S, o);
+                W += __shfl_down_sync(0xffffffffu, W, o);
+            }
+            if (lane == 0) { red64[warp][0] = S; red64[warp][1] = W; }
+            __syncthreads();
+            if (tid == 0) {
+                unsigned long long s = 0, wsum = 0;
+                for (int wv = 0; wv < CHK_THREADS / 32; wv++) { s += red64[wv][0]; wsum += red64[wv][1]; }
+                s %= P; wsum %= P;
+                unsigned long long nm = E % P;
+                uint32_t s1 = (uint32_t)((1 + s) % P);
+                uint32_t s2 = (uint32_t)((nm + nm * s + (unsigned long long)P - wsum) % P);
+                check = (s2 << 16) | s1;
+            }
+            __syncthreads();
+        }
+        if (tid == 0) {
+            zsb_result r = results[idx];
+            finish_member(r, a, (const uint8_t *)members[idx].in, (uint32_t)members[idx].in_len, check, E);
+            results[idx] = r;
+        }
+    }
+}
+
+}  // namespace zsb
