@@ -1,0 +1,50 @@
+"""CPU tier: the C-ABI library loads, exports every symbol include/zsb.h declares, its pure-host entry
+points work, and the GPU entry points fail loudly (never fall back) where no CUDA device exists."""
+import ctypes
+import os
+import re
+
+import pytest
+
+import zsblib
+
+
+def test_library_exports_declared_symbols():
+    lib = zsblib.load_product()
+    hdr = open(os.path.join(zsblib.ROOT, "include", "zsb.h")).read()
+    declared = re.findall(r"ZSB_API[^;]*?\b(zsb_\w+)\s*\(", hdr)
+    assert sorted(set(declared)) == sorted(zsblib.API_SYMBOLS)
+    for name in declared + zsblib.ZLIB_SYMBOLS:
+        assert hasattr(lib, name), name
+
+
+def test_messages_match_reference_strings():
+    lib = zsblib.load_product()
+    import orclib
+    o = orclib.orc().lib
+    arr = (ctypes.c_char_p * 19).in_dll(o, "orc_messages")
+    assert lib.zsb_message(0) is None
+    for i in range(1, 19):
+        assert lib.zsb_message(i) == arr[i]
+
+
+def test_plan_shards_is_balanced_and_deterministic():
+    lib = zsblib.load_product()
+    import random
+    rnd = random.Random(3)
+    costs = [int(2 ** rnd.uniform(10, 24)) for _ in range(5000)]
+    for ns in (1, 2, 4, 8):
+        so, load = zsblib.plan_shards(lib, costs, ns)
+        so2, _ = zsblib.plan_shards(lib, costs, ns)
+        assert so == so2 and set(so) <= set(range(ns))
+        assert sum(load) == sum(costs)
+        assert max(load) - min(load) <= max(costs)
+        assert max(load) <= sum(costs) / ns * 1.02 + max(costs)
+
+
+def test_no_cpu_fallback_without_device():
+    import torch
+    if torch.cuda.is_available():
+        pytest.skip("a device is present")
+    with pytest.raises(RuntimeError, match="no CUDA device|zsb_create failed"):
+        zsblib.Zsb()

@@ -1,0 +1,45 @@
+"""CPU tier: the decoder's DEVICE source (zlib-streams_b200/csrc/zsb_device.cuh), compiled for the host by
+tests/emul with a group width of one lane, against the oracle: every observable field and every output
+byte.  The same cases run through the real kernels on the GPU in test_gpu_parity.py."""
+import hashlib
+
+import cases
+import orclib
+import zsblib
+
+CHK = orclib.ref() or orclib.orc()
+EM = zsblib.emul()
+
+
+def same(name, data, wb, cap):
+    a, ao = CHK.oneshot(data, cap, wb)
+    b, bo = EM.oneshot(data, cap, wb)
+    assert a.astuple() == b.astuple(), (name, wb, cap, a, b)
+    assert ao == bo, (name, "output differs")
+
+
+def test_golden_fixtures():
+    for name, data, m in cases.golden_fixtures():
+        r, out = EM.oneshot(data, m["out_len"] + 64, -16)
+        assert (r.ret, r.msg_id, r.total_in, r.total_out) == (1, 0, m["in_len"], m["out_len"]), (name, r)
+        assert hashlib.sha256(out).hexdigest() == m["out_sha256"], name
+        same(name, data, -16, m["out_len"])
+        same(name, data, -15, m["out_len"])      # Deflate64 data read as deflate: error parity
+
+
+def test_probe_vectors():
+    for name, data, wb, cap, want in cases.probe_vectors():
+        r, out = EM.oneshot(data, cap, wb)
+        assert (r.ret, r.msg_id, r.total_in, r.total_out) == want, (name, r)
+        same(name, data, wb, cap)
+
+
+def test_valid_streams():
+    for name, data, wb, plain in cases.valid_streams():
+        for cap in (len(plain) + 16, len(plain), max(len(plain) - 1, 0)):
+            same(name, data, wb, cap)
+
+
+def test_damaged_streams():
+    for name, data, wb, cap in cases.damaged_streams(1500):
+        same(name, data, wb, cap)

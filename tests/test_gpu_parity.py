@@ -1,0 +1,122 @@
+"""GPU tier: the CUDA path through the C ABI (libzsb.so) against the oracle, bit for bit: output bytes,
+ret, msg, total_in, total_out, check (strm->adler) and data_type.  Every group width is exercised."""
+import hashlib
+
+import pytest
+
+import cases
+import orclib
+import zsblib
+
+pytestmark = pytest.mark.gpu
+CHK = orclib.ref() or orclib.orc()
+LANES = [32, 1, 4, 8, 2, 16]
+
+
+@pytest.fixture(scope="module")
+def eng():
+    e = zsblib.Zsb()
+    yield e
+    e.close()
+
+
+def run_cases(eng, lanes, items):
+    """items: (name, data, wbits, cap).  One batch call for all of them."""
+    eng.set_option("lanes_per_member", lanes)
+    got = eng.inflate_batch([d for _, d, _, _ in items], [w for _, _, w, _ in items], [c for _, _, _, c in items])
+    for (name, data, wb, cap), (r, out) in zip(items, got):
+        a, ao = CHK.oneshot(data, cap, wb)
+        assert a.astuple() == r.astuple(), (lanes, name, wb, cap, a, r)
+        assert ao == out, (lanes, name, "output differs")
+
+
+@pytest.mark.parametrize("lanes", LANES)
+def test_golden_fixtures(eng, lanes):
+    items = []
+    for name, data, m in cases.golden_fixtures():
+        items.append((name, data, -16, m["out_len"] + 64))
+        items.append((name + "_exact", data, -16, m["out_len"]))
+        items.append((name + "_as_deflate", data, -15, m["out_len"]))
+    eng.set_option("lanes_per_member", lanes)
+    got = eng.inflate_batch([d for _, d, _, _ in items], [w for _, _, w, _ in items], [c for _, _, _, c in items])
+    for (name, data, m), (r, out) in zip(cases.golden_fixtures(), got[::3]):
+        assert (r.ret, r.total_in, r.total_out) == (1, m["in_len"], m["out_len"]), (name, r)
+        assert hashlib.sha256(out).hexdigest() == m["out_sha256"], name
+    run_cases(eng, lanes, items)
+
+
+@pytest.mark.parametrize("lanes", LANES)
+def test_probe_vectors(eng, lanes):
+    items = [(n, d, w, c) for n, d, w, c, _ in cases.probe_vectors()]
+    eng.set_option("lanes_per_member", lanes)
+    got = eng.inflate_batch([d for _, d, _, _ in items], [w for _, _, w, _ in items], [c for _, _, _, c in items])
+    for (name, _, _, _, want), (r, _) in zip(cases.probe_vectors(), got):
+        assert (r.ret, r.msg_id, r.total_in, r.total_out) == want, (name, r)
+    run_cases(eng, lanes, items)
+
+
+@pytest.mark.parametrize("lanes", LANES)
+def test_valid_streams(eng, lanes):
+    items = []
+    for name, data, wb, plain in cases.valid_streams():
+        for cap in (len(plain) + 16, len(plain), max(len(plain) - 1, 0)):
+            items.append((name, data, wb, cap))
+    run_cases(eng, lanes, items)
+
+
+@pytest.mark.parametrize("lanes", LANES)
+def test_damaged_streams(eng, lanes):
+    run_cases(eng, lanes, cases.damaged_streams(400 if lanes in (1, 32) else 120))
+
+
+def test_device_pointer_batch(eng):
+    """Members already resident in HBM (torch tensors as plain device memory)."""
+    import ctypes
+    import torch
+    eng.set_option("lanes_per_member", 32)
+    vs = cases.valid_streams()[:60]
+    blob = b"".join(d + b"\0" * (-len(d) % 16) for _, d, _, _ in vs)
+    t_in = torch.frombuffer(bytearray(blob), dtype=torch.uint8).cuda()
+    caps = [len(p) + 16 for _, _, _, p in vs]
+    t_out = torch.zeros(sum((c + 15) // 16 * 16 for c in caps), dtype=torch.uint8, device="cuda")
+    arr = (zsblib.Member * len(vs))()
+    io = oo = 0
+    offs = []
+    for i, (name, d, wb, p) in enumerate(vs):
+        arr[i].inp = t_in.data_ptr() + io
+        arr[i].in_len = len(d)
+        arr[i].out = t_out.data_ptr() + oo
+        arr[i].out_cap = caps[i]
+        arr[i].window_bits = wb
+        offs.append(oo)
+        io += len(d) + (-len(d) % 16)
+        oo += (caps[i] + 15) // 16 * 16
+    res = (zsblib.Result * len(vs))()
+    torch.cuda.synchronize()
+    rc = eng.lib.zsb_inflate_batch(eng.ctx, len(vs), arr, res)
+    assert rc == 0, eng.error()
+    host = t_out.cpu().numpy().tobytes()
+    for i, (name, d, wb, p) in enumerate(vs):
+        a, ao = CHK.oneshot(d, caps[i], wb)
+        assert a.astuple() == res[i].astuple(), (name, a, res[i])
+        assert host[offs[i]:offs[i] + len(p)] == p, name
+
+
+def test_many_small_and_unaligned(eng):
+    """Ragged batch: thousands of tiny members at odd host addresses, empty members included."""
+    import random
+    rnd = random.Random(1)
+    items = []
+    for k in range(3000):
+        n = rnd.choice([0, 1, 5, 40, 200, 1500])
+        plain = rnd.randbytes(n) if k % 3 else bytes([k & 255]) * n
+        wb = rnd.choice([-15, 15, 31, -16])
+        enc = -15 if wb == -16 else wb
+        items.append(("tiny%d" % k, b"" if k % 97 == 0 else zsblib_gen().deflate(plain, rnd.choice([0, 1, 6, 9]), enc), wb, n + rnd.choice([0, 3])))
+    for lanes in (1, 8, 32):
+        run_cases(eng, lanes, items)
+
+
+def zsblib_gen():
+    import gen
+    return gen

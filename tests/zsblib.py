@@ -1,0 +1,169 @@
+"""ctypes bindings used by the tests and bench.py.
+
+`Zsb`  = the product: zlib-streams_b200/libzsb.so (CUDA, C ABI of include/zsb.h).
+`emul` = TEST TOOL: the decoder's device source compiled for the host with a group width of one lane
+         (tests/emul/), so the CPU-only test tier can exercise the decoder's control logic.
+"""
+import ctypes
+import os
+import subprocess
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+PKG = os.path.join(ROOT, "zlib-streams_b200")
+LIB = os.path.join(PKG, "libzsb.so")
+EMUL_DIR = os.path.join(ROOT, "tests", "emul")
+
+API_SYMBOLS = ["zsb_create", "zsb_destroy", "zsb_create_error", "zsb_last_error", "zsb_num_devices",
+               "zsb_inflate_batch", "zsb_inflate_batch_device", "zsb_set_option", "zsb_get_option",
+               "zsb_last_launches", "zsb_plan_shards", "zsb_host_alloc", "zsb_host_free", "zsb_message"]
+ZLIB_SYMBOLS = ["inflateInit_", "inflateInit2_", "inflate", "inflateEnd", "inflateReset", "inflateReset2",
+                "inflateResetKeep"]
+
+ZSB_RAW_ONLY = 4
+ZSB_HAS_WRAPPED = 1
+
+
+class Member(ctypes.Structure):
+    _fields_ = [("inp", ctypes.c_void_p), ("in_len", ctypes.c_size_t), ("out", ctypes.c_void_p),
+                ("out_cap", ctypes.c_size_t), ("window_bits", ctypes.c_int32), ("reserved", ctypes.c_int32)]
+
+
+class Result(ctypes.Structure):
+    _fields_ = [("ret", ctypes.c_int32), ("msg_id", ctypes.c_int32), ("total_in", ctypes.c_uint64),
+                ("total_out", ctypes.c_uint64), ("check", ctypes.c_uint32), ("data_type", ctypes.c_int32)]
+
+    def astuple(self):
+        return (self.ret, self.msg_id, self.total_in, self.total_out, self.check, self.data_type)
+
+    def __repr__(self):
+        return "Result(ret=%d msg=%d in=%d out=%d check=%08x dt=%d)" % self.astuple()
+
+
+def build_product():
+    subprocess.run(["make", "-s", "-C", os.path.join(PKG, "csrc")], check=True)
+
+
+def load_product():
+    if not os.path.exists(LIB):
+        build_product()
+    lib = ctypes.CDLL(LIB)
+    lib.zsb_create.restype = ctypes.c_void_p
+    lib.zsb_create.argtypes = [ctypes.POINTER(ctypes.c_int), ctypes.c_int]
+    lib.zsb_destroy.argtypes = [ctypes.c_void_p]
+    lib.zsb_create_error.restype = ctypes.c_char_p
+    lib.zsb_last_error.restype = ctypes.c_char_p
+    lib.zsb_last_error.argtypes = [ctypes.c_void_p]
+    lib.zsb_num_devices.argtypes = [ctypes.c_void_p]
+    lib.zsb_inflate_batch.argtypes = [ctypes.c_void_p, ctypes.c_size_t, ctypes.c_void_p, ctypes.c_void_p]
+    lib.zsb_inflate_batch_device.argtypes = [ctypes.c_void_p, ctypes.c_int, ctypes.c_size_t, ctypes.c_void_p,
+                                             ctypes.c_void_p, ctypes.c_void_p, ctypes.c_uint, ctypes.c_void_p]
+    lib.zsb_set_option.argtypes = [ctypes.c_void_p, ctypes.c_char_p, ctypes.c_long]
+    lib.zsb_get_option.argtypes = [ctypes.c_void_p, ctypes.c_char_p]
+    lib.zsb_get_option.restype = ctypes.c_long
+    lib.zsb_last_launches.argtypes = [ctypes.c_void_p]
+    lib.zsb_last_launches.restype = ctypes.c_long
+    lib.zsb_plan_shards.argtypes = [ctypes.c_size_t, ctypes.c_void_p, ctypes.c_int, ctypes.c_void_p, ctypes.c_void_p]
+    lib.zsb_host_alloc.restype = ctypes.c_void_p
+    lib.zsb_host_alloc.argtypes = [ctypes.c_size_t]
+    lib.zsb_host_free.argtypes = [ctypes.c_void_p]
+    lib.zsb_message.restype = ctypes.c_char_p
+    lib.zsb_message.argtypes = [ctypes.c_int]
+    return lib
+
+
+def plan_shards(lib, costs, nshards):
+    n = len(costs)
+    c = (ctypes.c_uint64 * n)(*costs)
+    so = (ctypes.c_int32 * n)()
+    load = (ctypes.c_uint64 * nshards)()
+    rc = lib.zsb_plan_shards(n, c, nshards, so, load)
+    if rc:
+        raise RuntimeError("zsb_plan_shards rc=%d" % rc)
+    return list(so), list(load)
+
+
+class Zsb:
+    """The engine through its C ABI.  Raises when no CUDA device is usable: there is no CPU path."""
+
+    def __init__(self, devices=None, lanes=None):
+        self.lib = load_product()
+        if devices:
+            arr = (ctypes.c_int * len(devices))(*devices)
+            self.ctx = self.lib.zsb_create(arr, len(devices))
+        else:
+            self.ctx = self.lib.zsb_create(None, 0)
+        if not self.ctx:
+            raise RuntimeError("zsb_create failed: " + self.lib.zsb_create_error().decode())
+        if lanes:
+            self.set_option("lanes_per_member", lanes)
+
+    def close(self):
+        if self.ctx:
+            self.lib.zsb_destroy(self.ctx)
+            self.ctx = None
+
+    def set_option(self, name, value):
+        rc = self.lib.zsb_set_option(self.ctx, name.encode(), value)
+        if rc:
+            raise ValueError("zsb_set_option(%s,%r) rc=%d" % (name, value, rc))
+
+    def get_option(self, name):
+        return self.lib.zsb_get_option(self.ctx, name.encode())
+
+    def error(self):
+        return self.lib.zsb_last_error(self.ctx).decode()
+
+    def inflate_batch(self, members, wbits, out_caps):
+        """members: list of bytes; host buffers.  Returns [(Result, output bytes)]."""
+        n = len(members)
+        if n == 0:
+            return []
+        ins = [ctypes.create_string_buffer(m, max(len(m), 1)) for m in members]
+        outs = [ctypes.create_string_buffer(max(c, 1)) for c in out_caps]
+        arr = (Member * n)()
+        for i in range(n):
+            arr[i].inp = ctypes.addressof(ins[i]) if len(members[i]) else (ctypes.addressof(ins[i]))
+            arr[i].in_len = len(members[i])
+            arr[i].out = ctypes.addressof(outs[i])
+            arr[i].out_cap = out_caps[i]
+            arr[i].window_bits = wbits[i]
+        res = (Result * n)()
+        rc = self.lib.zsb_inflate_batch(self.ctx, n, arr, res)
+        if rc:
+            raise RuntimeError("zsb_inflate_batch rc=%d: %s" % (rc, self.error()))
+        return [(res[i], outs[i].raw[:min(res[i].total_out, out_caps[i])]) for i in range(n)]
+
+
+class Emul:
+    def __init__(self):
+        path = os.path.join(EMUL_DIR, "libemul.so")
+        subprocess.run(["make", "-s", "-C", EMUL_DIR], check=True)
+        self.lib = ctypes.CDLL(path)
+        self.lib.emul_decode.argtypes = [ctypes.c_char_p, ctypes.c_size_t, ctypes.c_void_p, ctypes.c_size_t,
+                                         ctypes.c_int, ctypes.POINTER(Result), ctypes.c_void_p]
+        self.lib.emul_finish.argtypes = [ctypes.c_char_p, ctypes.c_size_t, ctypes.POINTER(Result),
+                                         ctypes.c_void_p, ctypes.c_uint32]
+
+    def oneshot(self, data, out_cap, wbits):
+        import zlib
+        # copy the input to a word-aligned buffer (the decoder reads whole aligned words)
+        buf_in = ctypes.create_string_buffer(data, max(len(data), 1))
+        buf = ctypes.create_string_buffer(max(out_cap, 1))
+        r = Result()
+        aux = (ctypes.c_uint32 * 4)()
+        self.lib.emul_decode(buf_in, len(data), buf if out_cap else None, out_cap, wbits, ctypes.byref(r), aux)
+        out = buf.raw[:min(r.total_out, out_cap)]
+        if aux[0]:
+            chk = (zlib.adler32(out) if aux[0] == 1 else zlib.crc32(out)) & 0xffffffff
+            self.lib.emul_finish(buf_in, len(data), ctypes.byref(r), aux, chk)
+        return r, out
+
+
+_emul = None
+
+
+def emul():
+    global _emul
+    if _emul is None:
+        _emul = Emul()
+    return _emul
