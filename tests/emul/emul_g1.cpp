@@ -19,8 +19,14 @@ static inline uint32_t __brev(uint32_t x) {
     return (x >> 16) | (x << 16);
 }
 template <class T> static inline T __ldg(const T *p) { return *p; }
-static inline uint32_t __shfl_sync(unsigned, uint32_t v, int, int) { return v; }
-static inline void __syncwarp(unsigned) {}
+static inline uint32_t __shfl_sync(unsigned, uint32_t v, int, int = 32) { return v; }
+static inline void __syncwarp(unsigned = 0xffffffffu) {}
+static inline bool __any_sync(unsigned, bool p) { return p; }
+static inline bool __all_sync(unsigned, bool p) { return p; }
+#define ZSB_FETCH_SLOT(counter) ((*(counter))++)
+static inline uint32_t __shfl_up_sync(unsigned, uint32_t v, int, int) { return v; }
+static inline unsigned __ballot_sync(unsigned, bool p) { return p; }
+static inline int __ffs(unsigned x) { return __builtin_ffs((int)x); }
 #include "../../zlib-streams_b200/csrc/zsb_device.cuh"
 
 extern "C" int emul_decode(const uint8_t *in, size_t in_len, uint8_t *out, size_t out_cap, int wbits,
@@ -38,7 +44,8 @@ extern "C" int emul_decode(const uint8_t *in, size_t in_len, uint8_t *out, size_
     zsb_member m;
     m.in = in; m.in_len = in_len; m.out = out; m.out_cap = out_cap; m.window_bits = wbits; m.reserved = 0;
     zsb::Aux a;
-    zsb::decode_member<1>(m, res, &a, T, lut, fixed, 0, 1u);
+    uint32_t counter = 0;
+    zsb::warp_inflate<1>(&m, res, &a, nullptr, 1, &counter, T, lut, fixed, 0, 1u);
     aux4[0] = a.kind; aux4[1] = a.trailer_pos; aux4[2] = a.need_trailer; aux4[3] = a.init_check;
     return res->ret;
 }

@@ -19,7 +19,7 @@ namespace zsb {
 
 // ---- events produced by the decoder leader lane ----
 enum : int { EV_NONE = 0, EV_MATCH = 1, EV_EOB = 2, EV_ERR = 3, EV_STARVE = 4, EV_OUTFULL = 5,
-             EV_DONE = 6, EV_NEEDDICT = 7, EV_INITERR = 8 };
+             EV_DONE = 6, EV_NEEDDICT = 7, EV_INITERR = 8, EV_LIT = 9 };
 
 // ---- message ids (index into zsb_message(); same order as the reference's strm->msg strings) ----
 enum : int { M_HDRCHECK = 1, M_METHOD = 2, M_WINDOW = 3, M_GZFLAGS = 4, M_HCRC = 5, M_BTYPE = 6,
@@ -126,7 +126,7 @@ struct Dec {
     uint32_t at_type;    // stopped exactly at a block boundary reached through mode TYPE (+128 in data_type)
     int msg;
     uint32_t extent;     // bits looked at beyond the bit position when an error fired between need and drop
-    uint32_t mlen, mdist;
+    uint32_t mlen, mdist, mtrunc;
 };
 
 // ---- group helpers -------------------------------------------------------------------------------
@@ -421,12 +421,21 @@ ZSB_DEV int dynamic_header(Dec &d, uint16_t *T, const uint32_t *lut) {
 }
 
 // ------------------------------------------------------------------------------------------------
-// Symbol decoding (leader lane).  literal_run() decodes up to `budget` literals and stops at the
-// first non-literal symbol; a match is returned decoded (d.mlen, d.mdist) but not yet copied.
-// Symbols that start with at least two whole input words still unread take the unchecked path;
-// the last few bytes of a member go through tail_symbol(), which checks availability before every
-// step exactly where the reference would wait for input (src/inflate.c:1046-1142).
+// Symbol decoding (leader lane).  decode_burst() turns symbols into TOKENS in a small shared-memory
+// queue without touching the output: the group then executes the queued tokens together
+// (run_tokens), so the latency of reading earlier output is paid once per burst instead of once per
+// match.  A token is  literal: TOK_LIT | byte   or   match: (dist-1) | len<<16  (len <= TOK_MAXLEN).
+// The leader keeps the output position, so capacity and "distance too far back" are decided here,
+// at the symbol where the reference decides them (src/inflate.c:1143-1153, src/inffast.c:166-175).
+// Symbols that start with at least two whole input words still unread take the unchecked path; the
+// last bytes of a member go through tail_symbol(), which checks availability before every step
+// exactly where the reference would wait for input (src/inflate.c:1046-1142).
 // ------------------------------------------------------------------------------------------------
+constexpr uint32_t TOK_LIT = 0x80000000u;
+constexpr uint32_t TOK_MAXLEN = 511;
+constexpr int QCAP = 24;                  // tokens per burst; the queue overlays T_DL..T_NXT (idle then)
+constexpr int T_Q = T_DL;                 // 25 words of the member slot
+
 ZSB_DEV int tail_symbol(Dec &d, const uint16_t *T, const uint32_t *lut) {
     BitIn &b = d.b;
     bi_fill(b);
@@ -436,9 +445,8 @@ ZSB_DEV int tail_symbol(Dec &d, const uint16_t *T, const uint32_t *lut) {
     bi_drop(b, nb);
     uint32_t kind = e & 0x30u, v = e >> 6;
     if (kind == K_LIT) {
-        if (d.pos >= d.cap) return EV_OUTFULL;
-        d.out[d.pos++] = (uint8_t)v;
-        return EV_NONE;
+        d.mdist = v;
+        return EV_LIT;
     }
     if (kind == K_SPECIAL) {
         if (v == 0) return EV_EOB;
@@ -470,57 +478,81 @@ ZSB_DEV int tail_symbol(Dec &d, const uint16_t *T, const uint32_t *lut) {
     return EV_MATCH;
 }
 
-ZSB_DEV int literal_run(Dec &d, const uint16_t *T, const uint32_t *lut, int budget) {
+// One symbol -> one token.  Returns EV_NONE after queueing a token, EV_MATCH for a match too long for
+// a token (d.mlen bytes to copy now, d.mtrunc set when the capacity cut it), else the stop event.
+// Called in lock step by all leader lanes of a warp (the caller reconverges after every step).
+ZSB_DEV int decode_step(Dec &d, const uint16_t *T, const uint32_t *lut, uint32_t *q, uint32_t &nt) {
     BitIn &b = d.b;
     const uint16_t *L = T + T_L;
     const uint32_t lutoff = d.d64 * 32;
-#pragma unroll 1
-    for (int it = 0; it < budget; it++) {
+    {
         if (b.next + 8 > b.len) {
             int ev = tail_symbol(d, T, lut);
-            if (ev != EV_NONE) return ev;
-            continue;
+            if (ev == EV_LIT) {
+                if (d.pos >= d.cap) return EV_OUTFULL;
+                q[nt++] = TOK_LIT | d.mdist;
+                d.pos++;
+                return EV_NONE;
+            }
+            if (ev != EV_MATCH) return ev;
+        } else {
+            if (b.nbits < 32) bi_loadword(b);
+            uint32_t e = L[(uint32_t)b.hold & 511u];
+            if ((e & 0x30u) == K_LINK) {
+                uint32_t curr = e & 15u;
+                e = L[(e >> 6) + (((uint32_t)(b.hold >> LROOT)) & ((1u << curr) - 1u))];
+                bi_drop(b, LROOT);
+            }
+            bi_drop(b, e & 15u);
+            uint32_t kind = e & 0x30u, v = e >> 6;
+            if (kind == K_LIT) {
+                if (d.pos >= d.cap) return EV_OUTFULL;
+                q[nt++] = TOK_LIT | v;
+                d.pos++;
+                return EV_NONE;
+            }
+            if (kind == K_SPECIAL) {
+                if (v == 0) return EV_EOB;
+                d.msg = M_LITCODE;
+                return EV_ERR;
+            }
+            uint32_t lw = lut[LUT_LEN + lutoff + v];
+            uint32_t xb = lw >> 16;
+            d.mlen = (lw & 0xffffu) + ((uint32_t)b.hold & ((1u << xb) - 1u));
+            bi_drop(b, xb);
+            if (b.nbits < 32) bi_loadword(b);
+            uint32_t nb;
+            e = lookup_dist(T, b.hold, nb);
+            bi_drop(b, nb);
+            if ((e & 0x30u) == K_SPECIAL) {
+                d.msg = M_DISTCODE;
+                return EV_ERR;
+            }
+            uint32_t dw = lut[LUT_DIST + lutoff + (e >> 6)];
+            if (dw >> 31) {
+                d.msg = M_DISTCODE;
+                return EV_ERR;
+            }
+            xb = (dw >> 16) & 15u;
+            d.mdist = (dw & 0xffffu) + ((uint32_t)b.hold & ((1u << xb) - 1u));
+            bi_drop(b, xb);
         }
-        if (b.nbits < 32) bi_loadword(b);
-        uint32_t e = L[(uint32_t)b.hold & 511u];
-        if ((e & 0x30u) == K_LINK) {
-            uint32_t curr = e & 15u;
-            e = L[(e >> 6) + (((uint32_t)(b.hold >> LROOT)) & ((1u << curr) - 1u))];
-            bi_drop(b, LROOT);
-        }
-        bi_drop(b, e & 15u);
-        uint32_t kind = e & 0x30u, v = e >> 6;
-        if (kind == K_LIT) {
-            if (d.pos >= d.cap) return EV_OUTFULL;
-            d.out[d.pos++] = (uint8_t)v;
-            continue;
-        }
-        if (kind == K_SPECIAL) {
-            if (v == 0) return EV_EOB;
-            d.msg = M_LITCODE;
+        // a match: capacity first, then the distance (src/inflate.c:1144-1153)
+        if (d.pos >= d.cap) return EV_OUTFULL;
+        if (d.mdist > d.pos) {
+            d.msg = M_TOOFAR;
             return EV_ERR;
         }
-        uint32_t lw = lut[LUT_LEN + lutoff + v];
-        uint32_t xb = lw >> 16;
-        d.mlen = (lw & 0xffffu) + ((uint32_t)b.hold & ((1u << xb) - 1u));
-        bi_drop(b, xb);
-        if (b.nbits < 32) bi_loadword(b);
-        uint32_t nb;
-        e = lookup_dist(T, b.hold, nb);
-        bi_drop(b, nb);
-        if ((e & 0x30u) == K_SPECIAL) {
-            d.msg = M_DISTCODE;
-            return EV_ERR;
+        uint32_t n = d.cap - d.pos;
+        d.mtrunc = n < d.mlen;
+        if (n > d.mlen) n = d.mlen;
+        if (n > TOK_MAXLEN) {
+            d.mlen = n;
+            return EV_MATCH;
         }
-        uint32_t dw = lut[LUT_DIST + lutoff + (e >> 6)];
-        if (dw >> 31) {
-            d.msg = M_DISTCODE;
-            return EV_ERR;
-        }
-        xb = (dw >> 16) & 15u;
-        d.mdist = (dw & 0xffffu) + ((uint32_t)b.hold & ((1u << xb) - 1u));
-        bi_drop(b, xb);
-        return EV_MATCH;
+        q[nt++] = (d.mdist - 1u) | (n << 16);
+        d.pos += n;
+        if (d.mtrunc) return EV_OUTFULL;
     }
     return EV_NONE;
 }
@@ -529,27 +561,32 @@ ZSB_DEV int literal_run(Dec &d, const uint16_t *T, const uint32_t *lut, int budg
 // LZ77 copy: out[pos+i] = out[pos-dist + (i mod dist)], i < n.  Every source byte lies before pos, so
 // lanes never depend on each other's stores of this copy.
 // ------------------------------------------------------------------------------------------------
+// one lane, serial: loads of a step are issued before its stores so they overlap
+ZSB_DEV void lane_copy(uint8_t *out, uint32_t pos, uint32_t dist, uint32_t n) {
+    uint8_t *dst = out + pos;
+    const uint8_t *src = dst - dist;
+    if (dist >= 4) {
+        while (n >= 4) {
+            uint8_t a = src[0], bb = src[1], c = src[2], e = src[3];
+            dst[0] = a; dst[1] = bb; dst[2] = c; dst[3] = e;
+            src += 4; dst += 4; n -= 4;
+        }
+        while (n--) *dst++ = *src++;
+    } else {
+        uint8_t p0 = src[0], p1 = dist > 1 ? src[1] : p0, p2 = dist > 2 ? src[2] : p0;
+        uint32_t ph = 0;                      // pattern of period dist (1..3)
+        for (uint32_t i = 0; i < n; i++) {
+            dst[i] = ph == 0 ? p0 : ph == 1 ? p1 : p2;
+            if (++ph == dist) ph = 0;
+        }
+    }
+}
+
+// all G lanes on one (long) match
 template <int G>
 ZSB_DEV void grp_copy_match(uint8_t *out, uint32_t pos, uint32_t dist, uint32_t n, int sub) {
     if (G == 1) {
-        uint8_t *dst = out + pos;
-        const uint8_t *src = dst - dist;
-        if (dist >= 4) {
-            while (n >= 4) {
-                uint8_t a = src[0], bb = src[1], c = src[2], e = src[3];
-                dst[0] = a; dst[1] = bb; dst[2] = c; dst[3] = e;
-                src += 4; dst += 4; n -= 4;
-            }
-            while (n--) *dst++ = *src++;
-        } else {
-            uint8_t p0 = src[0], p1 = dist > 1 ? src[1] : p0, p2 = dist > 2 ? src[2] : p0;
-            // pattern of period dist (1..3)
-            uint32_t ph = 0;
-            for (uint32_t i = 0; i < n; i++) {
-                dst[i] = ph == 0 ? p0 : ph == 1 ? p1 : p2;
-                if (++ph == dist) ph = 0;
-            }
-        }
+        lane_copy(out, pos, dist, n);
         return;
     }
     const uint8_t *src = out + pos - dist;
@@ -562,6 +599,59 @@ ZSB_DEV void grp_copy_match(uint8_t *out, uint32_t pos, uint32_t dist, uint32_t 
             dst[i] = src[off];
             off += step;
             if (off >= dist) off -= dist;
+        }
+    }
+}
+
+// Execute a burst of nt queued tokens starting at output position pos0.  G tokens at a time, one per
+// lane: positions by a prefix sum over the group, literals stored at once, a match copied as soon as
+// every token before its source range's end is finished (the first unfinished token always is), so
+// independent matches of a chunk overlap their memory latency.
+template <int G>
+ZSB_DEV void run_tokens(uint8_t *out, uint32_t pos0, const uint32_t *q, uint32_t nt, int sub, unsigned gmask) {
+    if (G == 1) {
+        uint32_t pos = pos0;
+        for (uint32_t t = 0; t < nt; t++) {
+            uint32_t tok = q[t];
+            if (tok & TOK_LIT) {
+                out[pos++] = (uint8_t)tok;
+            } else {
+                uint32_t n = tok >> 16;
+                lane_copy(out, pos, (tok & 0xffffu) + 1u, n);
+                pos += n;
+            }
+        }
+        return;
+    }
+    uint32_t base = pos0;
+    for (uint32_t c = 0; c < nt; c += G) {
+        const uint32_t t = c + sub;
+        const bool have = t < nt;
+        const uint32_t tok = have ? q[t] : TOK_LIT;
+        const bool lit = (tok & TOK_LIT) != 0;
+        const uint32_t n = have ? (lit ? 1u : tok >> 16) : 0u;
+        const uint32_t dist = (tok & 0xffffu) + 1u;
+        uint32_t incl = n;
+#pragma unroll
+        for (int o = 1; o < G; o <<= 1) {
+            uint32_t v = __shfl_up_sync(gmask, incl, o, G);
+            if (sub >= o) incl += v;
+        }
+        const uint32_t mypos = base + incl - n;
+        base += __shfl_sync(gmask, incl, G - 1, G);
+        if (have && lit) out[mypos] = (uint8_t)tok;
+        bool done = lit;
+        const uint32_t src_hi = dist >= n ? mypos - dist + n : mypos;   // end of the bytes this match reads
+        __syncwarp(gmask);
+        for (;;) {
+            const unsigned pending = __ballot_sync(gmask, !done) & gmask;
+            if (!pending) break;
+            const uint32_t frontier = __shfl_sync(gmask, mypos, __ffs(pending) - 1);
+            if (!done && src_hi <= frontier) {
+                lane_copy(out, mypos, dist, n);
+                done = true;
+            }
+            __syncwarp(gmask);
         }
     }
 }
@@ -753,205 +843,262 @@ __host__ __device__ inline bool wbits_valid(int wb) {
     return !(wb && (wb < 8 || wb > (d64 ? 16 : 15)));
 }
 
-template <int G>
-__device__ __forceinline__ void decode_member(const zsb_member &m, zsb_result *res, Aux *aux, uint16_t *T,
-                                              const uint32_t *lut, const uint16_t *fixed_tab, int sub,
-                                              unsigned gmask) {
-    Dec d;
-    int ev = EV_NONE;
-    uint32_t hdr_tin = 0, hdr_bits = 0, kind = 0, adler0 = 0;
-    bool hdr_stop = false;
-    const uint8_t *in = (const uint8_t *)m.in;
-    uint8_t *out = (uint8_t *)m.out;
+// what the leader keeps about its member besides the decoder state
+struct Mem {
+    uint32_t idx, kind, adler0;
+    uint32_t hdr_tin, hdr_bits;
+    bool hdr_stop;
+};
 
-    if (sub == 0) {
-        d.b.p = in;
-        d.b.len = (uint32_t)m.in_len;
-        d.b.next = 0; d.b.nbits = 0; d.b.hold = 0;
-        d.out = out;
-        d.pos = 0;
-        d.cap = (uint32_t)m.out_cap;
-        d.d64 = m.window_bits == -16;
-        d.last = 0; d.at_type = 0; d.msg = 0; d.extent = 0; d.mlen = 0; d.mdist = 0;
-        if (!wbits_valid(m.window_bits) || (in == nullptr && m.in_len != 0) || (out == nullptr && m.out_cap != 0)) {
-            ev = EV_INITERR;
-        } else {
-            HeadOut h = parse_wrapper(in, d.b.len, m.window_bits);
-            kind = h.kind;
-            adler0 = h.adler;
-            ev = h.ev;
-            if (ev == EV_NONE) {
-                bi_seek(d.b, h.pos);
-                d.at_type = kind != 0;
+// member ended (for this kernel): write the result and what k_check needs
+ZSB_DEV void write_result(const Dec &d, const Mem &mm, int ev, zsb_result *res, Aux *aux) {
+    zsb_result r;
+    Aux a;
+    a.kind = mm.kind; a.trailer_pos = 0; a.need_trailer = 0; a.init_check = mm.adler0;
+    r.msg_id = d.msg;
+    r.total_out = d.pos;
+    r.check = mm.adler0;
+    const BitIn &b = d.b;
+    uint32_t tin = b.next - (b.nbits >> 3), bits = b.nbits & 7u;
+    int extra128 = 0;
+    switch (ev) {
+    case EV_INITERR:
+        r.ret = -2; tin = 0; bits = 0; r.total_out = 0; r.msg_id = 0; r.check = 0; a.kind = 0;
+        break;
+    case EV_NEEDDICT:                          // src/inflate.c:817-827: returns before the exit bookkeeping
+        r.ret = 2; tin = 0; bits = 0; a.kind = 0;
+        break;
+    case EV_DONE:
+        if (mm.kind == 0) r.ret = 1;
+        else { r.ret = 0; a.need_trailer = 1; a.trailer_pos = tin; }
+        bits = 0;
+        break;
+    case EV_ERR:
+        r.ret = -3;
+        if (mm.hdr_stop) { tin = mm.hdr_tin; bits = mm.hdr_bits; }
+        else {
+            uint64_t bp = bi_bitpos(b);
+            tin = (uint32_t)((bp + d.extent + 7) >> 3);
+            bits = (uint32_t)(8ull * tin - bp);
+        }
+        break;
+    case EV_STARVE:
+        r.ret = -5;
+        if (mm.hdr_stop) { tin = mm.hdr_tin; bits = mm.hdr_bits; }
+        else { tin = b.len; bits = b.nbits; extra128 = d.at_type ? 128 : 0; }
+        break;
+    default:                                   // EV_OUTFULL
+        r.ret = -5;
+        break;
+    }
+    r.total_in = tin;
+    r.data_type = (ev == EV_INITERR || ev == EV_NEEDDICT) ? 0 : (int)(bits + (d.last ? 64 : 0) + extra128);
+    *res = r;
+    *aux = a;
+}
+
+#ifndef ZSB_FETCH_SLOT
+#define ZSB_FETCH_SLOT(counter) atomicAdd((counter), 1u)
+#endif
+
+enum : int { ST_FETCH = 0, ST_BLOCK = 1, ST_SYM = 2, ST_IDLE = 3 };
+
+// ------------------------------------------------------------------------------------------------
+// The decoder as a warp-synchronous state machine.  A warp holds 32/G groups of G lanes; every group
+// owns one member at a time and carries a state (fetch a member / read a block header / decode
+// symbols / no more work).  The warp walks through the phases together so that the lanes stay in
+// lock step where it pays: all leaders decode one symbol per step into their token queues
+// (reconverging after every step), then all groups execute their queued tokens.  Member start-up
+// and block headers are done per group between bursts.
+// ------------------------------------------------------------------------------------------------
+template <int G>
+__device__ __forceinline__ void warp_inflate(const zsb_member *members, zsb_result *results, Aux *aux,
+                                             const uint32_t *order, uint32_t n, uint32_t *counter, uint16_t *T,
+                                             const uint32_t *lut, const uint16_t *fixed_tab, int sub,
+                                             unsigned gmask) {
+    Dec d;
+    Mem mm;
+    d.pos = 0; d.mlen = 0; d.mdist = 0; d.mtrunc = 0; d.out = nullptr; d.b.p = nullptr;
+    mm.idx = 0;
+    int st = ST_FETCH;
+    const uint8_t *in = nullptr;
+    uint8_t *out = nullptr;
+    uint32_t *q = (uint32_t *)(T + T_Q);
+    const bool leader = sub == 0;
+
+    for (;;) {
+        int ev = EV_NONE;
+        // ---------------- a new member: descriptor, wrapper header ----------------
+        if (st == ST_FETCH) {
+            uint32_t slot = 0;
+            if (leader) slot = ZSB_FETCH_SLOT(counter);
+            slot = grp_bcast<G>(slot, gmask);
+            if (slot >= n) {
+                st = ST_IDLE;
             } else {
-                hdr_stop = true;
-                d.msg = h.msg;
-                hdr_tin = ev == EV_STARVE ? d.b.len : h.pulled;
-                hdr_bits = h.bits;
+                const uint32_t idx = order ? order[slot] : slot;
+                const zsb_member m = members[idx];
+                in = (const uint8_t *)m.in;
+                out = (uint8_t *)m.out;
+                if (leader) {
+                    mm.idx = idx; mm.kind = 0; mm.adler0 = 0; mm.hdr_stop = false; mm.hdr_tin = 0; mm.hdr_bits = 0;
+                    d.b.p = in;
+                    d.b.len = (uint32_t)m.in_len;
+                    d.b.next = 0; d.b.nbits = 0; d.b.hold = 0;
+                    d.out = out;
+                    d.pos = 0;
+                    d.cap = (uint32_t)m.out_cap;
+                    d.d64 = m.window_bits == -16;
+                    d.last = 0; d.at_type = 0; d.msg = 0; d.extent = 0; d.mlen = 0; d.mdist = 0; d.mtrunc = 0;
+                    if (!wbits_valid(m.window_bits) || (in == nullptr && m.in_len != 0) ||
+                        (out == nullptr && m.out_cap != 0)) {
+                        ev = EV_INITERR;
+                    } else {
+                        HeadOut h = parse_wrapper(in, d.b.len, m.window_bits);
+                        mm.kind = h.kind;
+                        mm.adler0 = h.adler;
+                        ev = h.ev;
+                        if (ev == EV_NONE) {
+                            bi_seek(d.b, h.pos);
+                            d.at_type = mm.kind != 0;
+                        } else {
+                            mm.hdr_stop = true;
+                            d.msg = h.msg;
+                            mm.hdr_tin = ev == EV_STARVE ? d.b.len : h.pulled;
+                            mm.hdr_bits = h.bits;
+                        }
+                    }
+                    if (ev != EV_NONE) write_result(d, mm, ev, results + idx, aux + idx);
+                }
+                ev = (int)grp_bcast<G>((uint32_t)ev, gmask);
+                st = ev == EV_NONE ? ST_BLOCK : ST_FETCH;
+                ev = EV_NONE;
             }
         }
-    }
-    ev = (int)grp_bcast<G>((uint32_t)ev, gmask);
-
-    while (ev == EV_NONE) {                       // one block per turn
-        uint32_t btype = 0, slen = 0, spos = 0;
-        if (sub == 0) {
-            BitIn &b = d.b;
-            if (d.last) {
-                ev = EV_DONE;
-            } else if (!bi_need(b, 3)) {
-                ev = EV_STARVE;
-            } else {
-                d.last = bi_peek(b, 1);
-                bi_drop(b, 1);
-                btype = bi_peek(b, 2);
-                bi_drop(b, 2);
-                d.at_type = 0;
-                if (btype == 3) {
-                    d.msg = M_BTYPE;
-                    ev = EV_ERR;
-                } else if (btype == 2) {
-                    ev = dynamic_header(d, T, lut);
-                } else if (btype == 0) {
-                    bi_drop(b, b.nbits & 7);
-                    uint32_t bytepos = b.next - (b.nbits >> 3);
-                    if (b.len - bytepos < 4) {
-                        b.nbits = 8 * (b.len - bytepos);
-                        b.next = b.len;
-                        ev = EV_STARVE;
-                    } else {
-                        uint32_t v = in[bytepos] | ((uint32_t)in[bytepos + 1] << 8) |
-                                     ((uint32_t)in[bytepos + 2] << 16) | ((uint32_t)in[bytepos + 3] << 24);
-                        if ((v & 0xffffu) != ((v >> 16) ^ 0xffffu)) {
-                            d.msg = M_STORED;
-                            d.extent = 32;
-                            ev = EV_ERR;
+        // ---------------- block header (one block per turn) ----------------
+        if (st == ST_BLOCK) {
+            uint32_t btype = 0, slen = 0, spos = 0;
+            if (leader) {
+                BitIn &b = d.b;
+                if (d.last) {
+                    ev = EV_DONE;
+                } else if (!bi_need(b, 3)) {
+                    ev = EV_STARVE;
+                } else {
+                    d.last = bi_peek(b, 1);
+                    bi_drop(b, 1);
+                    btype = bi_peek(b, 2);
+                    bi_drop(b, 2);
+                    d.at_type = 0;
+                    if (btype == 3) {
+                        d.msg = M_BTYPE;
+                        ev = EV_ERR;
+                    } else if (btype == 2) {
+                        ev = dynamic_header(d, T, lut);
+                    } else if (btype == 0) {
+                        bi_drop(b, b.nbits & 7);
+                        uint32_t bytepos = b.next - (b.nbits >> 3);
+                        if (b.len - bytepos < 4) {
+                            b.nbits = 8 * (b.len - bytepos);
+                            b.next = b.len;
+                            ev = EV_STARVE;
                         } else {
-                            spos = bytepos + 4;
-                            slen = v & 0xffffu;
-                            uint32_t have = b.len - spos, left = d.cap - d.pos;
-                            if (slen > have) slen = have, btype |= 4;
-                            if (slen > left) slen = left, btype |= 4;
+                            uint32_t v = le32(in + bytepos);
+                            if ((v & 0xffffu) != ((v >> 16) ^ 0xffffu)) {
+                                d.msg = M_STORED;
+                                d.extent = 32;
+                                ev = EV_ERR;
+                            } else {
+                                spos = bytepos + 4;
+                                slen = v & 0xffffu;
+                                uint32_t have = b.len - spos, left = d.cap - d.pos;
+                                if (slen > have) slen = have, btype |= 4;
+                                if (slen > left) slen = left, btype |= 4;
+                            }
                         }
                     }
                 }
             }
-        }
-        uint32_t w0 = grp_bcast<G>((uint32_t)ev | (btype << 8), gmask);
-        ev = (int)(w0 & 0xffu);
-        btype = w0 >> 8;
-        if (ev != EV_NONE) break;
-
-        if ((btype & 3) == 0) {                   // stored block (reference src/inflate.c:870-904)
-            slen = grp_bcast<G>(slen, gmask);
-            spos = grp_bcast<G>(spos, gmask);
-            uint32_t pos = grp_bcast<G>(d.pos, gmask);
-            grp_copy_stored<G>(out + pos, in + spos, slen, sub);
-            grp_sync<G>(gmask);
-            if (sub == 0) {
-                d.pos += slen;
-                bi_seek(d.b, spos + slen);
-                d.at_type = 1;
-                if (btype & 4) {                  // input or output ran out inside the block
-                    d.b.next = spos + slen;
-                    d.b.nbits = 0;
-                    d.at_type = 0;
-                }
-            }
-            if (btype & 4) ev = EV_OUTFULL;
-            continue;
-        }
-        if (btype == 1) {                         // fixed code: copy the context's prebuilt tables
-            uint32_t *t32 = (uint32_t *)T;
-            const uint32_t *f32 = (const uint32_t *)fixed_tab;
-            for (int i = sub; i < 256; i += G) t32[i] = f32[i];
-            for (int i = T_D / 2 + sub; i < T_DL / 2; i += G) t32[i] = f32[i];
-            grp_sync<G>(gmask);
-        }
-        for (;;) {                                // symbols of this block
-            uint32_t n = 0;
-            if (sub == 0) {
-                ev = literal_run(d, T, lut, 64);
-                if (ev == EV_MATCH) {
-                    if (d.pos >= d.cap) ev = EV_OUTFULL;
-                    else if (d.mdist > d.pos) {
-                        d.msg = M_TOOFAR;
-                        ev = EV_ERR;
-                    } else {
-                        n = d.cap - d.pos;
-                        if (n >= d.mlen) n = d.mlen;
-                        else ev = EV_MATCH | 0x80;            // truncated by the output capacity
+            uint32_t w0 = grp_bcast<G>((uint32_t)ev | (btype << 8), gmask);
+            ev = (int)(w0 & 0xffu);
+            btype = w0 >> 8;
+            if (ev != EV_NONE) {
+                if (leader) write_result(d, mm, ev, results + mm.idx, aux + mm.idx);
+                st = ST_FETCH;
+            } else if ((btype & 3) == 0) {            // stored block (reference src/inflate.c:870-904)
+                slen = grp_bcast<G>(slen, gmask);
+                spos = grp_bcast<G>(spos, gmask);
+                uint32_t pos = grp_bcast<G>(d.pos, gmask);
+                grp_copy_stored<G>(out + pos, in + spos, slen, sub);
+                grp_sync<G>(gmask);
+                if (leader) {
+                    d.pos += slen;
+                    bi_seek(d.b, spos + slen);
+                    d.at_type = 1;
+                    if (btype & 4) {                  // input or output ran out inside the block
+                        d.b.next = spos + slen;
+                        d.b.nbits = 0;
+                        d.at_type = 0;
+                        write_result(d, mm, EV_OUTFULL, results + mm.idx, aux + mm.idx);
                     }
                 }
-            }
-            ev = (int)grp_bcast<G>((uint32_t)ev, gmask);
-            if ((ev & 0x7f) == EV_MATCH) {
-                n = grp_bcast<G>(n, gmask);
-                uint32_t dist = grp_bcast<G>(d.mdist, gmask);
-                uint32_t pos = grp_bcast<G>(d.pos, gmask);
-                grp_sync<G>(gmask);
-                grp_copy_match<G>(out, pos, dist, n, sub);
-                grp_sync<G>(gmask);
-                if (sub == 0) d.pos += n;
-                if (ev & 0x80) {
-                    ev = EV_OUTFULL;
-                    break;
+                if (btype & 4) st = ST_FETCH;
+            } else {
+                if (btype == 1) {                     // fixed code: copy the context's prebuilt tables
+                    uint32_t *t32 = (uint32_t *)T;
+                    const uint32_t *f32 = (const uint32_t *)fixed_tab;
+                    for (int i = sub; i < 256; i += G) t32[i] = f32[i];
+                    for (int i = T_D / 2 + sub; i < T_DL / 2; i += G) t32[i] = f32[i];
+                    grp_sync<G>(gmask);
                 }
-                continue;
+                st = ST_SYM;
             }
-            if (ev == EV_NONE) continue;
-            break;
-        }
-        if (ev == EV_EOB) {
             ev = EV_NONE;
-            if (sub == 0) d.at_type = 1;
         }
-    }
-
-    if (sub == 0) {
-        zsb_result r;
-        Aux a;
-        a.kind = kind; a.trailer_pos = 0; a.need_trailer = 0; a.init_check = adler0;
-        r.msg_id = d.msg;
-        r.total_out = d.pos;
-        r.check = adler0;
-        const BitIn &b = d.b;
-        uint32_t tin = b.next - (b.nbits >> 3), bits = b.nbits & 7u;
-        int extra128 = 0;
-        switch (ev) {
-        case EV_INITERR:
-            r.ret = -2; tin = 0; bits = 0; r.total_out = 0; r.msg_id = 0; r.check = 0; a.kind = 0;
-            break;
-        case EV_NEEDDICT:                          // src/inflate.c:817-827: returns before the exit bookkeeping
-            r.ret = 2; tin = 0; bits = 0; a.kind = 0;
-            break;
-        case EV_DONE:
-            if (kind == 0) r.ret = 1;
-            else { r.ret = 0; a.need_trailer = 1; a.trailer_pos = tin; }
-            bits = 0;
-            break;
-        case EV_ERR:
-            r.ret = -3;
-            if (hdr_stop) { tin = hdr_tin; bits = hdr_bits; }
-            else {
-                uint64_t bp = bi_bitpos(b);
-                tin = (uint32_t)((bp + d.extent + 7) >> 3);
-                bits = (uint32_t)(8ull * tin - bp);
+        __syncwarp();
+        // ---------------- decode burst: every leader, one symbol per step, in lock step ----------------
+        uint32_t nt = 0, pos0 = d.pos;
+        {
+            const bool dec = leader && st == ST_SYM;
+#pragma unroll 1
+            for (int it = 0; it < QCAP; it++) {
+                const bool go = dec && ev == EV_NONE;
+                if (!__any_sync(0xffffffffu, go)) break;
+                if (go) ev = decode_step(d, T, lut, q, nt);
+                __syncwarp();
             }
-            break;
-        case EV_STARVE:
-            r.ret = -5;
-            if (hdr_stop) { tin = hdr_tin; bits = hdr_bits; }
-            else { tin = b.len; bits = b.nbits; extra128 = d.at_type ? 128 : 0; }
-            break;
-        default:                                   // EV_OUTFULL
-            r.ret = -5;
-            break;
         }
-        r.total_in = tin;
-        r.data_type = (ev == EV_INITERR || ev == EV_NEEDDICT) ? 0 : (int)(bits + (d.last ? 64 : 0) + extra128);
-        *res = r;
-        *aux = a;
+        // ---------------- execute the queued tokens ----------------
+        if (G > 1) {
+            uint32_t w = grp_bcast<G>((uint32_t)ev | (nt << 8), gmask);
+            ev = (int)(w & 0xffu);
+            nt = w >> 8;
+            pos0 = grp_bcast<G>(pos0, gmask);
+        }
+        grp_sync<G>(gmask);                   // queue and earlier output visible to the group
+        if (nt) run_tokens<G>(out, pos0, q, nt, sub, gmask);
+        if (ev == EV_MATCH) {                 // match longer than a token holds (Deflate64): all lanes copy
+            grp_sync<G>(gmask);
+            uint32_t nn = grp_bcast<G>(d.mlen, gmask);
+            uint32_t dist = grp_bcast<G>(d.mdist, gmask);
+            uint32_t pos = grp_bcast<G>(d.pos, gmask);
+            uint32_t trunc = grp_bcast<G>(d.mtrunc, gmask);
+            grp_copy_match<G>(out, pos, dist, nn, sub);
+            if (leader) d.pos += nn;
+            ev = trunc ? EV_OUTFULL : EV_NONE;
+        }
+        grp_sync<G>(gmask);
+        // ---------------- events ----------------
+        if (st == ST_SYM && ev != EV_NONE) {
+            if (ev == EV_EOB) {
+                st = ST_BLOCK;
+                if (leader) d.at_type = 1;
+            } else {
+                if (leader) write_result(d, mm, ev, results + mm.idx, aux + mm.idx);
+                st = ST_FETCH;
+            }
+        }
+        if (__all_sync(0xffffffffu, st == ST_IDLE)) break;
     }
 }
 

@@ -279,71 +279,55 @@ template <typename T> static int grow(zsb_ctx *ctx, T *&p, size_t &cap, size_t n
     return 0;
 }
 
+// A run = consecutive members whose host buffers follow each other closely enough to be moved with one
+// copy; the device arena mirrors the host layout inside a run.  Inputs may be merged across small gaps
+// (a gap shorter than a page only touches pages that hold member bytes, so reading it is safe);
+// outputs only when exactly adjacent, because the gap is not ours to write.
+struct Run {
+    uintptr_t host;
+    size_t dev_off, len;
+};
 struct Shard {
-    std::vector<uint32_t> idx;       // members of this shard, in address order of their inputs
-    bool dense_in = false, dense_out = false;
-    const uint8_t *hin_base = nullptr;
-    uint8_t *hout_base = nullptr;
-    size_t in_span = 0, out_span = 0;
+    std::vector<uint32_t> idx;
     std::vector<size_t> in_off, out_off;
+    std::vector<Run> in_runs, out_runs;
+    size_t in_span = 0, out_span = 0;
 };
 
+static size_t layout_runs(const zsb_member *m, const std::vector<uint32_t> &idx, bool out, size_t gap_limit,
+                          std::vector<size_t> &off, std::vector<Run> &runs) {
+    const size_t k = idx.size();
+    off.assign(k, 0);
+    runs.clear();
+    size_t total = 0;
+    bool open = false;
+    uintptr_t host_base = 0, end = 0;
+    size_t dev_base = 0;
+    for (size_t j = 0; j < k; j++) {
+        const zsb_member &x = m[idx[j]];
+        uintptr_t p = out ? (uintptr_t)x.out : (uintptr_t)x.in;
+        size_t len = out ? x.out_cap : x.in_len;
+        if (len == 0 || p == 0) continue;
+        if (open && p >= end && p - end <= gap_limit) {
+            off[j] = dev_base + (p - host_base);
+        } else {
+            if (open) runs.push_back({host_base, dev_base, (size_t)(end - host_base)});
+            dev_base = (total + 255) & ~(size_t)255;
+            dev_base += p & 15;               // keep the host's 16-byte phase
+            host_base = p;
+            off[j] = dev_base;
+            open = true;
+        }
+        end = p + len;
+        total = dev_base + (end - host_base);
+    }
+    if (open) runs.push_back({host_base, dev_base, (size_t)(end - host_base)});
+    return total;
+}
+
 static void plan_layout(const zsb_member *m, Shard &sh) {
-    const size_t k = sh.idx.size();
-    sh.in_off.resize(k);
-    sh.out_off.resize(k);
-    // dense test: ascending, non-overlapping, and the span is not much larger than the payload
-    auto dense = [&](bool out) {
-        size_t sum = 0;
-        uintptr_t lo = ~(uintptr_t)0, hi = 0, prev_end = 0;
-        for (size_t j = 0; j < k; j++) {
-            const zsb_member &x = m[sh.idx[j]];
-            uintptr_t p = out ? (uintptr_t)x.out : (uintptr_t)x.in;
-            size_t len = out ? x.out_cap : x.in_len;
-            if (len == 0) continue;
-            if (p < prev_end) return false;
-            prev_end = p + len;
-            lo = std::min(lo, p);
-            hi = std::max(hi, p + len);
-            sum += len;
-        }
-        if (sum == 0) return false;
-        return (hi - lo) <= sum + sum / 4 + (64u << 10);
-    };
-    sh.dense_in = dense(false);
-    sh.dense_out = dense(true);
-    size_t off = 0;
-    if (sh.dense_in) {
-        uintptr_t lo = ~(uintptr_t)0, hi = 0;
-        for (uint32_t i : sh.idx)
-            if (m[i].in_len) lo = std::min(lo, (uintptr_t)m[i].in), hi = std::max(hi, (uintptr_t)m[i].in + m[i].in_len);
-        uintptr_t base = lo & ~(uintptr_t)255;
-        sh.hin_base = (const uint8_t *)base;
-        sh.in_span = hi - base;
-        for (size_t j = 0; j < k; j++) sh.in_off[j] = m[sh.idx[j]].in_len ? (uintptr_t)m[sh.idx[j]].in - base : 0;
-    } else {
-        for (size_t j = 0; j < k; j++) {
-            sh.in_off[j] = off;
-            off += (m[sh.idx[j]].in_len + 15) & ~(size_t)15;
-        }
-        sh.in_span = off;
-    }
-    off = 0;
-    if (sh.dense_out) {
-        uintptr_t lo = ~(uintptr_t)0, hi = 0;
-        for (uint32_t i : sh.idx)
-            if (m[i].out_cap) lo = std::min(lo, (uintptr_t)m[i].out), hi = std::max(hi, (uintptr_t)m[i].out + m[i].out_cap);
-        uintptr_t base = lo & ~(uintptr_t)255;
-        sh.hout_base = (uint8_t *)base;
-        sh.out_span = hi - base;
-        for (size_t j = 0; j < k; j++) sh.out_off[j] = m[sh.idx[j]].out_cap ? (uintptr_t)m[sh.idx[j]].out - base : 0;
-    } else {
-        for (size_t j = 0; j < k; j++) {
-            sh.out_off[j] = off;
-            off += (m[sh.idx[j]].out_cap + 15) & ~(size_t)15;
-        }
-        sh.out_span = off;
-    }
+    sh.in_span = layout_runs(m, sh.idx, false, 4095, sh.in_off, sh.in_runs);
+    sh.out_span = layout_runs(m, sh.idx, true, 0, sh.out_off, sh.out_runs);
 }
 
 static int batch_host(zsb_ctx *ctx, size_t n, const zsb_member *m, zsb_result *r) {
@@ -401,30 +385,13 @@ static int batch_host(zsb_ctx *ctx, size_t n, const zsb_member *m, zsb_result *r
         cudaStream_t st = dv.stream;
         CK(ctx, cudaMemcpyAsync(dm, hm, k * sizeof(zsb_member), cudaMemcpyHostToDevice, st));
         CK(ctx, cudaMemcpyAsync(dord, ho, k * sizeof(uint32_t), cudaMemcpyHostToDevice, st));
-        if (sh.dense_in) {
-            const uint8_t *src = sh.hin_base;
-            // the 256-byte align-down may reach below the first member: start at the first real byte
-            size_t first = ~(size_t)0;
-            for (size_t j = 0; j < k; j++)
-                if (m[sh.idx[j]].in_len) first = std::min(first, sh.in_off[j]);
-            if (first != ~(size_t)0)
-                CK(ctx, cudaMemcpyAsync(dv.d_in + first, src + first, sh.in_span - first, cudaMemcpyHostToDevice, st));
-        } else {
-            for (size_t j = 0; j < k; j++)
-                if (m[sh.idx[j]].in_len)
-                    CK(ctx, cudaMemcpyAsync(dv.d_in + sh.in_off[j], m[sh.idx[j]].in, m[sh.idx[j]].in_len,
-                                            cudaMemcpyHostToDevice, st));
-        }
+        for (const Run &rn : sh.in_runs)
+            CK(ctx, cudaMemcpyAsync(dv.d_in + rn.dev_off, (const void *)rn.host, rn.len, cudaMemcpyHostToDevice, st));
         if ((rc = run_device(ctx, dv, k, dm, dr, dord, flags, st))) return rc;
         CK(ctx, cudaMemcpyAsync(hr, dr, k * sizeof(zsb_result), cudaMemcpyDeviceToHost, st));
-        if (sh.dense_out) {
-            size_t first = ~(size_t)0;
-            for (size_t j = 0; j < k; j++)
-                if (m[sh.idx[j]].out_cap) first = std::min(first, sh.out_off[j]);
-            if (first != ~(size_t)0)
-                CK(ctx, cudaMemcpyAsync(sh.hout_base + first, dv.d_out + first, sh.out_span - first,
-                                        cudaMemcpyDeviceToHost, st));
-        }
+        // whole buffers come back (bytes past total_out are unspecified by contract): no host sync needed
+        for (const Run &rn : sh.out_runs)
+            CK(ctx, cudaMemcpyAsync((void *)rn.host, dv.d_out + rn.dev_off, rn.len, cudaMemcpyDeviceToHost, st));
     }
     for (int s = 0; s < nd; s++) {
         Shard &sh = shards[s];
@@ -435,15 +402,6 @@ static int batch_host(zsb_ctx *ctx, size_t n, const zsb_member *m, zsb_result *r
         CK(ctx, cudaStreamSynchronize(dv.stream));
         zsb_result *hr = (zsb_result *)((zsb_member *)dv.h_desc + k);
         for (size_t j = 0; j < k; j++) r[sh.idx[j]] = hr[j];
-        if (!sh.dense_out) {
-            for (size_t j = 0; j < k; j++) {
-                const zsb_member &x = m[sh.idx[j]];
-                size_t nb = std::min<size_t>(hr[j].total_out, x.out_cap);
-                if (nb && x.out)
-                    CK(ctx, cudaMemcpyAsync(x.out, dv.d_out + sh.out_off[j], nb, cudaMemcpyDeviceToHost, dv.stream));
-            }
-            CK(ctx, cudaStreamSynchronize(dv.stream));
-        }
     }
     return 0;
 }

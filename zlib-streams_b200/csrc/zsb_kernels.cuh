@@ -33,14 +33,7 @@ __global__ void __launch_bounds__(Geo<G>::threads, Geo<G>::min_ctas) k_inflate(c
     const int sub = lane % G, grp = lane / G;
     uint16_t *T = (uint16_t *)(smem + LUT_BYTES) + (size_t)(warp * S + grp) * STREAM_U16;
     const unsigned gmask = G == 32 ? 0xffffffffu : (((1u << G) - 1u) << (grp * G));
-    for (;;) {
-        uint32_t slot = 0;
-        if (sub == 0) slot = atomicAdd(counter, 1u);
-        slot = grp_bcast<G>(slot, gmask);
-        if (slot >= n) break;
-        uint32_t idx = order ? order[slot] : slot;
-        decode_member<G>(members[idx], results + idx, aux + idx, T, lut, fixed_tab, sub, gmask);
-    }
+    warp_inflate<G>(members, results, aux, order, n, counter, T, lut, fixed_tab, sub, gmask);
 }
 
 __global__ void k_build_fixed(uint16_t *fixed_tab) {
