@@ -119,7 +119,7 @@ def main():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--members", type=int, default=65536)
     ap.add_argument("--distinct", type=int, default=1024)
-    ap.add_argument("--lanes", type=int, default=0, help="lanes per member (0 = library default)")
+    ap.add_argument("--lanes", type=int, default=0, help="0 = lane path (k_lane + k_lz); else group path k_inflate<G>")
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-cpu", action="store_true")
     args = ap.parse_args()
@@ -179,7 +179,12 @@ def main():
     out_off = np.arange(n, dtype=np.int64) * MEMBER_BYTES
     sum_in, sum_out = int(in_len.sum()), n * MEMBER_BYTES
 
-    eng = zsblib.Zsb(devices=[local_rank], lanes=args.lanes or None)
+    eng = zsblib.Zsb(devices=[local_rank])
+    if args.lanes:
+        eng.set_option("path", 2)
+        eng.set_option("lanes_per_member", args.lanes)
+    else:
+        eng.set_option("path", 1)
     lib = eng.lib
 
     def descriptors(in_base, out_base):
@@ -202,7 +207,7 @@ def main():
     stream = torch.cuda.current_stream()
 
     def step():
-        rc = lib.zsb_inflate_batch_device(eng.ctx, 0, n, t_desc.data_ptr(), t_res.data_ptr(), None,
+        rc = lib.zsb_inflate_batch_device(eng.ctx, 0, n, t_desc.data_ptr(), desc.ctypes.data, t_res.data_ptr(), None,
                                           zsblib.ZSB_RAW_ONLY, ctypes.c_void_p(stream.cuda_stream))
         if rc:
             raise RuntimeError("zsb_inflate_batch_device rc=%d %s" % (rc, eng.error()))
@@ -243,6 +248,7 @@ def main():
     if not ok:
         raise SystemExit("bench.py: GPU results differ from expectation (ret/total_out/bytes)")
 
+    kernel_name = ("k_inflate<%d>" % eng.get_option("lanes_per_member")) if args.lanes else "k_lane+k_lz"
     value = world * sum_out / (ms_per_step * 1e-3) / 1e9
     peak, peak_src = peaks()
     achieved = (sum_in + sum_out) / (ms_per_step * 1e-3) / 1e9
@@ -250,10 +256,10 @@ def main():
            "warmup": args.warmup, "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "weak",
            "vs_baseline": None, "dtype": "u8", "data": "synthetic", "config": config,
            "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
-                        "traffic": None, "peak_source": peak_src, "kernel": "k_inflate<%d>" % eng.get_option("lanes_per_member"),
+                        "traffic": None, "peak_source": peak_src, "kernel": kernel_name,
                         "algorithmic_bytes_per_launch": sum_in + sum_out},
            "clocks": sampler.summary(), "gpu_launches": int(launches_per_step * args.steps),
-           "lanes_per_member": int(eng.get_option("lanes_per_member"))}
+           "path": "group" if args.lanes else "lane", "lanes_per_member": int(args.lanes)}
     del t_in, t_out, t_blob
     torch.cuda.empty_cache()
 

@@ -75,21 +75,25 @@ ZSB_API int zsb_num_devices(const zsb_ctx *ctx);
  * (ZSB_E_*) for failures of the call itself (per-member outcomes are in r[i].ret). */
 ZSB_API int zsb_inflate_batch(zsb_ctx *ctx, size_t n, const zsb_member *m, zsb_result *r);
 
-/* Device-resident, asynchronous form (the kernel-only path): `d_members` and `d_results` are device
- * arrays on device `dev_index` of the context, all in/out pointers are device pointers on it.
- * `d_order` (optional, device, n x uint32) is the order in which members are handed to the decoder
- * groups (largest first balances best; NULL = identity).  `wbits_summary` = ZSB_HAS_* flags telling
- * which optional kernels are needed (0 = derive by inspecting the descriptors, costs a host sync).
- * Work is enqueued on `cuda_stream` (a cudaStream_t, NULL = default stream); no host sync. */
+/* Device-resident form (the kernel-only path): `d_members` and `d_results` are device arrays on device
+ * `dev_index` of the context, all in/out pointers are device pointers on it.  `h_members` is a host
+ * copy of the same descriptors (only in_len / out_cap / window_bits are read: the host sizes the
+ * decoder's scratch from them without a device round trip).  `h_order` (optional, host, n x uint32)
+ * is the order in which members are handed to the decoder (largest first balances best; NULL =
+ * identity).  `flags` = ZSB_RAW_ONLY when every member has window_bits < 0, else ZSB_HAS_WRAPPED.
+ * Work is enqueued on `cuda_stream` (a cudaStream_t, NULL = default stream); the call does not wait
+ * for the GPU.  One call at a time per device of a context. */
 ZSB_API int zsb_inflate_batch_device(zsb_ctx *ctx, int dev_index, size_t n, const zsb_member *d_members,
-                             zsb_result *d_results, const uint32_t *d_order, unsigned flags,
-                             void *cuda_stream);
+                             const zsb_member *h_members, zsb_result *d_results, const uint32_t *h_order,
+                             unsigned flags, void *cuda_stream);
 
 #define ZSB_HAS_WRAPPED 1u /* some member has window_bits >= 0 (header/trailer + checksum kernels needed) */
 #define ZSB_HAS_LARGE   2u /* reserved */
 #define ZSB_RAW_ONLY    4u /* every member has window_bits < 0: skip checksum/trailer kernels */
 
-/* Tuning knobs (0 keeps the default): lanes of a warp that cooperate on one member (1,2,4,8,16,32). */
+/* Tuning knobs: "path" 0 auto / 1 lane path (one member per lane, k_lane + k_lz) / 2 group path
+ * (k_inflate<G>); "lanes_per_member" G of the group path (1,2,4,8,16,32); "seq_arena_bytes" most
+ * sequence scratch the lane path may hold at once (larger batches are decoded in slices). */
 ZSB_API int zsb_set_option(zsb_ctx *ctx, const char *name, long value);
 ZSB_API long zsb_get_option(const zsb_ctx *ctx, const char *name);
 

@@ -24,10 +24,15 @@ static inline void __syncwarp(unsigned = 0xffffffffu) {}
 static inline bool __any_sync(unsigned, bool p) { return p; }
 static inline bool __all_sync(unsigned, bool p) { return p; }
 #define ZSB_FETCH_SLOT(counter) ((*(counter))++)
-static inline uint32_t __shfl_up_sync(unsigned, uint32_t v, int, int) { return v; }
+static inline uint32_t __shfl_up_sync(unsigned, uint32_t v, int, int = 32) { return v; }
 static inline unsigned __ballot_sync(unsigned, bool p) { return p; }
 static inline int __ffs(unsigned x) { return __builtin_ffs((int)x); }
+static inline unsigned __match_any_sync(unsigned, uint32_t) { return 1u; }
+static inline int __popc(unsigned x) { return __builtin_popcount(x); }
+#define ZSB_FETCH_ADD(p, v) ((*(p) += (v)) - (v))
+#define ZSB_SMEM_ADD(p, v) (*(p) += (v))
 #include "../../zlib-streams_b200/csrc/zsb_device.cuh"
+#include "../../zlib-streams_b200/csrc/zsb_lz.cuh"
 
 extern "C" int emul_decode(const uint8_t *in, size_t in_len, uint8_t *out, size_t out_cap, int wbits,
                            zsb_result *res, uint32_t *aux4) {
@@ -48,6 +53,44 @@ extern "C" int emul_decode(const uint8_t *in, size_t in_len, uint8_t *out, size_
     zsb::warp_inflate<1>(&m, res, &a, nullptr, 1, &counter, T, lut, fixed, 0, 1u);
     aux4[0] = a.kind; aux4[1] = a.trailer_pos; aux4[2] = a.need_trailer; aux4[3] = a.init_check;
     return res->ret;
+}
+
+// the lane path with a warp of one lane: k_lane's decoder, then k_lz's resolver
+extern "C" int emul_decode_lane(const uint8_t *in, size_t in_len, uint8_t *out, size_t out_cap, int wbits,
+                                zsb_result *res, uint32_t *aux4, uint64_t seq_cap, uint32_t *nseq_out) {
+    using namespace zsb;
+    static uint8_t fixed[lane::SLOT];
+    static uint32_t lut[LUT_WORDS];
+    static bool init = false;
+    alignas(16) static uint8_t scr[lane::WSCR];
+    if (!init) {
+        init_lut(lut, 0, 1);
+        alignas(16) uint8_t T0[lane::SLOT];
+        for (int i = 0; i < 288; i++) T0[lane::H_LENS + i] = i < 144 ? 8 : i < 256 ? 9 : i < 280 ? 7 : 8;
+        for (int i = 0; i < 32; i++) T0[lane::H_LENS + 288 + i] = 5;
+        lane::build_tables<1>(T0, scr, 288, 32, false, 0);
+        memcpy(fixed, T0, sizeof fixed);
+        init = true;
+    }
+    alignas(16) uint8_t T[lane::SLOT];
+    memset(T, 0xA5, sizeof T);
+    zsb_member m;
+    m.in = in; m.in_len = in_len; m.out = out; m.out_cap = out_cap; m.window_bits = wbits; m.reserved = 0;
+    Aux a;
+    uint32_t counter = 0, order = 0;
+    uint64_t seq_off = 0;
+    lane::seq_t *seq = (lane::seq_t *)malloc((seq_cap + 1) * sizeof(lane::seq_t));
+    lane::Batch B;
+    B.members = &m; B.results = res; B.aux = &a; B.order = &order; B.seq_off = &seq_off; B.seq_base = seq;
+    B.hist = nullptr; B.n = 1; B.counter = &counter; B.fixed_tab = fixed;
+    lane::warp_lanes<1>(B, T, scr, lut, 0);
+    if (nseq_out) *nseq_out = a.nseq;
+    int rc = res->ret;
+    if (a.nseq > seq_cap) rc = -1000;               // the host's scratch bound was too small
+    else if (a.nseq) lz::resolve_member<1>(out, in, seq, a.nseq, 0);
+    free(seq);
+    aux4[0] = a.kind; aux4[1] = a.trailer_pos; aux4[2] = a.need_trailer; aux4[3] = a.init_check;
+    return rc;
 }
 
 // second half of the pipeline: what k_check does once the checksum of the output is known

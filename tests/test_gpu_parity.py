@@ -10,7 +10,16 @@ import zsblib
 
 pytestmark = pytest.mark.gpu
 CHK = orclib.ref() or orclib.orc()
-LANES = [32, 1, 4, 8, 2, 16]
+# decoder configurations: 0 = the lane path (k_lane + k_lz), else the group path with that many lanes
+LANES = [0, 32, 1, 4, 8, 2, 16]
+
+
+def select(eng, lanes):
+    if lanes == 0:
+        eng.set_option("path", 1)
+    else:
+        eng.set_option("path", 2)
+        eng.set_option("lanes_per_member", lanes)
 
 
 @pytest.fixture(scope="module")
@@ -22,7 +31,7 @@ def eng():
 
 def run_cases(eng, lanes, items):
     """items: (name, data, wbits, cap).  One batch call for all of them."""
-    eng.set_option("lanes_per_member", lanes)
+    select(eng, lanes)
     got = eng.inflate_batch([d for _, d, _, _ in items], [w for _, _, w, _ in items], [c for _, _, _, c in items])
     for (name, data, wb, cap), (r, out) in zip(items, got):
         a, ao = CHK.oneshot(data, cap, wb)
@@ -37,7 +46,7 @@ def test_golden_fixtures(eng, lanes):
         items.append((name, data, -16, m["out_len"] + 64))
         items.append((name + "_exact", data, -16, m["out_len"]))
         items.append((name + "_as_deflate", data, -15, m["out_len"]))
-    eng.set_option("lanes_per_member", lanes)
+    select(eng, lanes)
     got = eng.inflate_batch([d for _, d, _, _ in items], [w for _, _, w, _ in items], [c for _, _, _, c in items])
     for (name, data, m), (r, out) in zip(cases.golden_fixtures(), got[::3]):
         assert (r.ret, r.total_in, r.total_out) == (1, m["in_len"], m["out_len"]), (name, r)
@@ -48,7 +57,7 @@ def test_golden_fixtures(eng, lanes):
 @pytest.mark.parametrize("lanes", LANES)
 def test_probe_vectors(eng, lanes):
     items = [(n, d, w, c) for n, d, w, c, _ in cases.probe_vectors()]
-    eng.set_option("lanes_per_member", lanes)
+    select(eng, lanes)
     got = eng.inflate_batch([d for _, d, _, _ in items], [w for _, _, w, _ in items], [c for _, _, _, c in items])
     for (name, _, _, _, want), (r, _) in zip(cases.probe_vectors(), got):
         assert (r.ret, r.msg_id, r.total_in, r.total_out) == want, (name, r)
@@ -66,14 +75,14 @@ def test_valid_streams(eng, lanes):
 
 @pytest.mark.parametrize("lanes", LANES)
 def test_damaged_streams(eng, lanes):
-    run_cases(eng, lanes, cases.damaged_streams(400 if lanes in (1, 32) else 120))
+    run_cases(eng, lanes, cases.damaged_streams(400 if lanes in (0, 1, 32) else 120))
 
 
 def test_device_pointer_batch(eng):
     """Members already resident in HBM (torch tensors as plain device memory)."""
     import ctypes
     import torch
-    eng.set_option("lanes_per_member", 32)
+    select(eng, 0)
     vs = cases.valid_streams()[:60]
     blob = b"".join(d + b"\0" * (-len(d) % 16) for _, d, _, _ in vs)
     t_in = torch.frombuffer(bytearray(blob), dtype=torch.uint8).cuda()
@@ -113,8 +122,22 @@ def test_many_small_and_unaligned(eng):
         wb = rnd.choice([-15, 15, 31, -16])
         enc = -15 if wb == -16 else wb
         items.append(("tiny%d" % k, b"" if k % 97 == 0 else zsblib_gen().deflate(plain, rnd.choice([0, 1, 6, 9]), enc), wb, n + rnd.choice([0, 3])))
-    for lanes in (1, 8, 32):
+    for lanes in (0, 1, 8, 32):
         run_cases(eng, lanes, items)
+
+
+def test_lane_path_slices(eng):
+    """A sequence arena smaller than the batch needs: the lane path decodes it in slices."""
+    items = []
+    for name, data, wb, plain in cases.valid_streams()[::5]:
+        items.append((name, data, wb, len(plain) + 16))
+    select(eng, 0)
+    old = eng.get_option("seq_arena_bytes")
+    eng.set_option("seq_arena_bytes", 1 << 20)
+    try:
+        run_cases(eng, 0, items)
+    finally:
+        eng.set_option("seq_arena_bytes", old)
 
 
 def zsblib_gen():

@@ -56,7 +56,8 @@ def load_product():
     lib.zsb_num_devices.argtypes = [ctypes.c_void_p]
     lib.zsb_inflate_batch.argtypes = [ctypes.c_void_p, ctypes.c_size_t, ctypes.c_void_p, ctypes.c_void_p]
     lib.zsb_inflate_batch_device.argtypes = [ctypes.c_void_p, ctypes.c_int, ctypes.c_size_t, ctypes.c_void_p,
-                                             ctypes.c_void_p, ctypes.c_void_p, ctypes.c_uint, ctypes.c_void_p]
+                                             ctypes.c_void_p, ctypes.c_void_p, ctypes.c_void_p, ctypes.c_uint,
+                                             ctypes.c_void_p]
     lib.zsb_set_option.argtypes = [ctypes.c_void_p, ctypes.c_char_p, ctypes.c_long]
     lib.zsb_get_option.argtypes = [ctypes.c_void_p, ctypes.c_char_p]
     lib.zsb_get_option.restype = ctypes.c_long
@@ -141,17 +142,31 @@ class Emul:
         self.lib = ctypes.CDLL(path)
         self.lib.emul_decode.argtypes = [ctypes.c_char_p, ctypes.c_size_t, ctypes.c_void_p, ctypes.c_size_t,
                                          ctypes.c_int, ctypes.POINTER(Result), ctypes.c_void_p]
+        self.lib.emul_decode_lane.argtypes = [ctypes.c_char_p, ctypes.c_size_t, ctypes.c_void_p, ctypes.c_size_t,
+                                              ctypes.c_int, ctypes.POINTER(Result), ctypes.c_void_p,
+                                              ctypes.c_uint64, ctypes.POINTER(ctypes.c_uint32)]
         self.lib.emul_finish.argtypes = [ctypes.c_char_p, ctypes.c_size_t, ctypes.POINTER(Result),
                                          ctypes.c_void_p, ctypes.c_uint32]
 
-    def oneshot(self, data, out_cap, wbits):
+    @staticmethod
+    def seq_bound(in_len, out_cap):
+        """zsb_host.cu seq_bound(): most LZ sequences a member can produce."""
+        return min(out_cap // 3 + in_len // 2 + 6, 8 * in_len + 4, out_cap + 2)
+
+    def oneshot(self, data, out_cap, wbits, lane=False):
         import zlib
         # copy the input to a word-aligned buffer (the decoder reads whole aligned words)
         buf_in = ctypes.create_string_buffer(data, max(len(data), 1))
         buf = ctypes.create_string_buffer(max(out_cap, 1))
         r = Result()
         aux = (ctypes.c_uint32 * 4)()
-        self.lib.emul_decode(buf_in, len(data), buf if out_cap else None, out_cap, wbits, ctypes.byref(r), aux)
+        if lane:
+            nseq = ctypes.c_uint32(0)
+            rc = self.lib.emul_decode_lane(buf_in, len(data), buf if out_cap else None, out_cap, wbits,
+                                           ctypes.byref(r), aux, self.seq_bound(len(data), out_cap), ctypes.byref(nseq))
+            assert rc != -1000, "sequence bound too small: %d > %d" % (nseq.value, self.seq_bound(len(data), out_cap))
+        else:
+            self.lib.emul_decode(buf_in, len(data), buf if out_cap else None, out_cap, wbits, ctypes.byref(r), aux)
         out = buf.raw[:min(r.total_out, out_cap)]
         if aux[0]:
             chk = (zlib.adler32(out) if aux[0] == 1 else zlib.crc32(out)) & 0xffffffff

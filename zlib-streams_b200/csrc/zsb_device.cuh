@@ -61,6 +61,8 @@ struct Aux {
     uint32_t trailer_pos;  // byte offset of the trailer when need_trailer
     uint32_t need_trailer; // 1: all blocks decoded, trailer still to be checked
     uint32_t init_check;   // strm->adler if no output byte is produced
+    uint32_t nseq;         // lane path: LZ sequences k_lz has to execute for this member
+    uint32_t pad[3];
 };
 
 // ------------------------------------------------------------------------------------------------
@@ -855,6 +857,7 @@ ZSB_DEV void write_result(const Dec &d, const Mem &mm, int ev, zsb_result *res, 
     zsb_result r;
     Aux a;
     a.kind = mm.kind; a.trailer_pos = 0; a.need_trailer = 0; a.init_check = mm.adler0;
+    a.nseq = 0; a.pad[0] = a.pad[1] = a.pad[2] = 0;
     r.msg_id = d.msg;
     r.total_out = d.pos;
     r.check = mm.adler0;

@@ -119,21 +119,115 @@ static int ensure_aux(zsb_ctx *ctx, zsb_dev &dv, size_t n) {
     return 0;
 }
 
+// sequences a member can produce at most (zsb_lane.cuh): every sequence but a few carries at least
+// three output bytes; stored blocks add at most two short ones each; each costs at least one input bit
+static inline uint64_t seq_bound(const zsb_member &m) {
+    const uint64_t a = (uint64_t)m.out_cap / 3 + (uint64_t)m.in_len / 2 + 6;
+    const uint64_t b = 8 * (uint64_t)m.in_len + 4;
+    const uint64_t c = (uint64_t)m.out_cap + 2;
+    return std::min(a, std::min(b, c));
+}
+
+template <typename T> static int grow(zsb_ctx *ctx, T *&p, size_t &cap, size_t need);
+
+static int run_group(zsb_ctx *ctx, zsb_dev &dv, size_t n, const zsb_member *dm, zsb_result *dr,
+                     const uint32_t *dorder, cudaStream_t st) {
+    CK(ctx, cudaMemsetAsync(dv.counters, 0, 4 * sizeof(uint32_t), st));
+    switch (ctx->lanes) {
+    case 1: return launch_inflate<1>(ctx, dv, n, dm, dr, dorder, st);
+    case 2: return launch_inflate<2>(ctx, dv, n, dm, dr, dorder, st);
+    case 4: return launch_inflate<4>(ctx, dv, n, dm, dr, dorder, st);
+    case 8: return launch_inflate<8>(ctx, dv, n, dm, dr, dorder, st);
+    case 16: return launch_inflate<16>(ctx, dv, n, dm, dr, dorder, st);
+    default: return launch_inflate<32>(ctx, dv, n, dm, dr, dorder, st);
+    }
+}
+
+// lane path: k_lane + k_lz over slices of the slot order whose sequence scratch fits the arena
+static int run_lane(zsb_ctx *ctx, zsb_dev &dv, size_t n, const zsb_member *dm, zsb_result *dr,
+                    const zsb_member *hm, const uint32_t *horder, const uint32_t *dorder, uint64_t *dseqoff,
+                    cudaStream_t st) {
+    if (!dv.lane_configured) {
+        CK(ctx, cudaFuncSetAttribute(k_lane, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)lane::SMEM));
+        int occ = 0;
+        CK(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, k_lane, lane::WARPS * 32, lane::SMEM));
+        if (occ < 1) {
+            snprintf(ctx->err, sizeof ctx->err, "k_lane does not fit an SM");
+            return ZSB_E_CUDA;
+        }
+        CK(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&dv.lz_occ, k_lz, LZ_THREADS, 0));
+        if (dv.lz_occ < 1) dv.lz_occ = 1;
+        dv.lane_configured = true;
+    }
+    // per-slot sequence offsets, slices cut where the arena would overflow
+    std::vector<uint64_t> off(n);
+    std::vector<size_t> cuts;          // slice = [cuts[k], cuts[k+1])
+    const uint64_t arena_seqs = std::max<uint64_t>(ctx->seq_arena_bytes / sizeof(lane::seq_t), 1);
+    uint64_t run = 0, most = 0;
+    cuts.push_back(0);
+    for (size_t s = 0; s < n; s++) {
+        const uint64_t b = seq_bound(hm[horder ? horder[s] : s]);
+        if (run && run + b > arena_seqs) {
+            cuts.push_back(s);
+            run = 0;
+        }
+        off[s] = run;
+        run += b;
+        most = std::max(most, run);
+    }
+    cuts.push_back(n);
+    int rc;
+    if ((rc = grow(ctx, dv.d_seq, dv.d_seq_cap, (size_t)most * sizeof(lane::seq_t)))) return rc;
+    CK(ctx, cudaMemcpyAsync(dseqoff, off.data(), n * sizeof(uint64_t), cudaMemcpyHostToDevice, st));
+    for (size_t k = 0; k + 1 < cuts.size(); k++) {
+        const size_t first = cuts[k], cnt = cuts[k + 1] - cuts[k];
+        CK(ctx, cudaMemsetAsync(dv.counters, 0, 4 * sizeof(uint32_t), st));
+        lane::Batch B;
+        B.members = dm;
+        B.results = dr;
+        B.aux = dv.aux;
+        B.order = dorder + first;
+        B.seq_off = dseqoff + first;
+        B.seq_base = (lane::seq_t *)dv.d_seq;
+        B.hist = nullptr;
+        B.n = (uint32_t)cnt;
+        B.counter = dv.counters;
+        B.fixed_tab = dv.fixed_lane;
+        const size_t per_cta = (size_t)lane::WARPS * 32;
+        unsigned grid = (unsigned)std::max<size_t>(1, std::min((cnt + per_cta - 1) / per_cta, (size_t)dv.sm_count));
+        k_lane<<<grid, lane::WARPS * 32, lane::SMEM, st>>>(B);
+        ctx->launches++;
+        CK(ctx, cudaGetLastError());
+        const size_t wpc = LZ_THREADS / 32;
+        grid = (unsigned)std::max<size_t>(1, std::min((cnt + wpc - 1) / wpc, (size_t)dv.sm_count * dv.lz_occ));
+        k_lz<<<grid, LZ_THREADS, 0, st>>>(B, dv.counters + 2);
+        ctx->launches++;
+        CK(ctx, cudaGetLastError());
+    }
+    return 0;
+}
+
+// dm/dr: device arrays; hm: host copy of the descriptors; horder: host slot order (NULL = identity)
 static int run_device(zsb_ctx *ctx, zsb_dev &dv, size_t n, const zsb_member *dm, zsb_result *dr,
-                      const uint32_t *dorder, unsigned flags, cudaStream_t st) {
+                      const zsb_member *hm, const uint32_t *horder, unsigned flags, cudaStream_t st) {
     if (n == 0) return 0;
     if (n > 0xffffff00ull) return ZSB_E_ARG;
     int rc = ensure_aux(ctx, dv, n);
     if (rc) return rc;
-    CK(ctx, cudaMemsetAsync(dv.counters, 0, 2 * sizeof(uint32_t), st));
-    switch (ctx->lanes) {
-    case 1: rc = launch_inflate<1>(ctx, dv, n, dm, dr, dorder, st); break;
-    case 2: rc = launch_inflate<2>(ctx, dv, n, dm, dr, dorder, st); break;
-    case 4: rc = launch_inflate<4>(ctx, dv, n, dm, dr, dorder, st); break;
-    case 8: rc = launch_inflate<8>(ctx, dv, n, dm, dr, dorder, st); break;
-    case 16: rc = launch_inflate<16>(ctx, dv, n, dm, dr, dorder, st); break;
-    default: rc = launch_inflate<32>(ctx, dv, n, dm, dr, dorder, st); break;
+    // slot order and sequence offsets travel in one per-call plan buffer
+    const size_t plan_bytes = n * (sizeof(uint64_t) + sizeof(uint32_t)) + 64;
+    if ((rc = grow(ctx, dv.d_plan, dv.d_plan_cap, plan_bytes))) return rc;
+    uint64_t *dseqoff = (uint64_t *)dv.d_plan;
+    uint32_t *dorder = (uint32_t *)(dseqoff + n);
+    std::vector<uint32_t> ident;
+    if (!horder) {
+        ident.resize(n);
+        for (size_t i = 0; i < n; i++) ident[i] = (uint32_t)i;
     }
+    CK(ctx, cudaMemcpyAsync(dorder, horder ? horder : ident.data(), n * sizeof(uint32_t), cudaMemcpyHostToDevice, st));
+    const bool use_lane = ctx->path == 1 || (ctx->path == 0);
+    if (use_lane) rc = run_lane(ctx, dv, n, dm, dr, hm, horder, dorder, dseqoff, st);
+    else rc = run_group(ctx, dv, n, dm, dr, dorder, st);
     if (rc) return rc;
     if (!(flags & ZSB_RAW_ONLY)) {
         unsigned grid = (unsigned)std::min<size_t>(n, (size_t)dv.sm_count * 8);
@@ -159,6 +253,7 @@ static int init_device(zsb_ctx *ctx, zsb_dev &dv, int device) {
     CK(ctx, cudaStreamCreateWithFlags(&dv.stream, cudaStreamNonBlocking));
     CK(ctx, cudaStreamCreateWithFlags(&dv.copy_stream, cudaStreamNonBlocking));
     CK(ctx, cudaMalloc(&dv.fixed, STREAM_BYTES));
+    CK(ctx, cudaMalloc(&dv.fixed_lane, lane::SLOT));
     CK(ctx, cudaMalloc(&dv.counters, 4 * sizeof(uint32_t)));
     CrcConsts cc;
     cc.x2n[0] = 0x40000000u;
@@ -174,6 +269,8 @@ static int init_device(zsb_ctx *ctx, zsb_dev &dv, int device) {
     CK(ctx, cudaMemcpyToSymbol(c_crc, &cc, sizeof cc));
     k_build_fixed<<<1, 128, 0, dv.stream>>>(dv.fixed);
     CK(ctx, cudaGetLastError());
+    k_build_fixed_lane<<<1, 32, 0, dv.stream>>>(dv.fixed_lane);
+    CK(ctx, cudaGetLastError());
     CK(ctx, cudaStreamSynchronize(dv.stream));
     return 0;
 }
@@ -183,6 +280,9 @@ static void free_device(zsb_dev &dv) {
     if (dv.stream) cudaStreamDestroy(dv.stream);
     if (dv.copy_stream) cudaStreamDestroy(dv.copy_stream);
     cudaFree(dv.fixed);
+    cudaFree(dv.fixed_lane);
+    cudaFree(dv.d_seq);
+    cudaFree(dv.d_plan);
     cudaFree(dv.counters);
     cudaFree(dv.aux);
     cudaFree(dv.d_in);
@@ -242,27 +342,39 @@ extern "C" int zsb_set_option(zsb_ctx *ctx, const char *name, long value) {
         ctx->slab_bytes = (size_t)value;
         return 0;
     }
+    if (!strcmp(name, "path")) {
+        if (value < 0 || value > 2) return ZSB_E_ARG;
+        ctx->path = (int)value;
+        return 0;
+    }
+    if (!strcmp(name, "seq_arena_bytes")) {
+        if (value < 4096) return ZSB_E_ARG;
+        ctx->seq_arena_bytes = (size_t)value;
+        return 0;
+    }
     return ZSB_E_ARG;
 }
 extern "C" long zsb_get_option(const zsb_ctx *ctx, const char *name) {
     if (!ctx || !name) return ZSB_E_ARG;
     if (!strcmp(name, "lanes_per_member")) return ctx->lanes;
     if (!strcmp(name, "slab_bytes")) return (long)ctx->slab_bytes;
+    if (!strcmp(name, "path")) return ctx->path;
+    if (!strcmp(name, "seq_arena_bytes")) return (long)ctx->seq_arena_bytes;
     if (!strcmp(name, "sm_count")) return ctx->devs.empty() ? 0 : ctx->devs[0].sm_count;
     return ZSB_E_ARG;
 }
 
 extern "C" int zsb_inflate_batch_device(zsb_ctx *ctx, int dev_index, size_t n, const zsb_member *d_members,
-                                        zsb_result *d_results, const uint32_t *d_order, unsigned flags,
-                                        void *cuda_stream) {
-    if (!ctx || dev_index < 0 || dev_index >= (int)ctx->devs.size() || (n && (!d_members || !d_results)))
+                                        const zsb_member *h_members, zsb_result *d_results,
+                                        const uint32_t *h_order, unsigned flags, void *cuda_stream) {
+    if (!ctx || dev_index < 0 || dev_index >= (int)ctx->devs.size() || (n && (!d_members || !d_results || !h_members)))
         return ZSB_E_ARG;
     zsb_dev &dv = ctx->devs[dev_index];
     int cur = 0;
     cudaGetDevice(&cur);
     if (cur != dv.device) CK(ctx, cudaSetDevice(dv.device));
     ctx->launches = 0;
-    int rc = run_device(ctx, dv, n, d_members, d_results, d_order, flags, (cudaStream_t)cuda_stream);
+    int rc = run_device(ctx, dv, n, d_members, d_results, h_members, h_order, flags, (cudaStream_t)cuda_stream);
     if (cur != dv.device) cudaSetDevice(cur);
     return rc;
 }
@@ -369,7 +481,6 @@ static int batch_host(zsb_ctx *ctx, size_t n, const zsb_member *m, zsb_result *r
         uint32_t *ho = (uint32_t *)(hr + k);
         zsb_member *dm = (zsb_member *)dv.d_desc;
         zsb_result *dr = (zsb_result *)(dm + k);
-        uint32_t *dord = (uint32_t *)(dr + k);
         for (size_t j = 0; j < k; j++) {
             const zsb_member &x = m[sh.idx[j]];
             hm[j] = x;
@@ -384,10 +495,9 @@ static int batch_host(zsb_ctx *ctx, size_t n, const zsb_member *m, zsb_result *r
         });
         cudaStream_t st = dv.stream;
         CK(ctx, cudaMemcpyAsync(dm, hm, k * sizeof(zsb_member), cudaMemcpyHostToDevice, st));
-        CK(ctx, cudaMemcpyAsync(dord, ho, k * sizeof(uint32_t), cudaMemcpyHostToDevice, st));
         for (const Run &rn : sh.in_runs)
             CK(ctx, cudaMemcpyAsync(dv.d_in + rn.dev_off, (const void *)rn.host, rn.len, cudaMemcpyHostToDevice, st));
-        if ((rc = run_device(ctx, dv, k, dm, dr, dord, flags, st))) return rc;
+        if ((rc = run_device(ctx, dv, k, dm, dr, hm, ho, flags, st))) return rc;
         CK(ctx, cudaMemcpyAsync(hr, dr, k * sizeof(zsb_result), cudaMemcpyDeviceToHost, st));
         // whole buffers come back (bytes past total_out are unspecified by contract): no host sync needed
         for (const Run &rn : sh.out_runs)
@@ -414,7 +524,6 @@ static int batch_device_ptrs(zsb_ctx *ctx, size_t n, const zsb_member *m, zsb_re
     if ((rc = grow(ctx, dv.d_desc, dv.d_desc_cap, desc_bytes))) return rc;
     zsb_member *dm = (zsb_member *)dv.d_desc;
     zsb_result *dr = (zsb_result *)(dm + n);
-    uint32_t *dord = (uint32_t *)(dr + n);
     std::vector<uint32_t> ord(n);
     bool raw_only = true;
     for (size_t i = 0; i < n; i++) {
@@ -429,9 +538,8 @@ static int batch_device_ptrs(zsb_ctx *ctx, size_t n, const zsb_member *m, zsb_re
         if (x.in_len > 0xfffffff0ull || x.out_cap > 0xfffffff0ull) x.window_bits = 1000;
     cudaStream_t st = dv.stream;
     CK(ctx, cudaMemcpyAsync(dm, mm.data(), n * sizeof(zsb_member), cudaMemcpyHostToDevice, st));
-    CK(ctx, cudaMemcpyAsync(dord, ord.data(), n * sizeof(uint32_t), cudaMemcpyHostToDevice, st));
     ctx->launches = 0;
-    if ((rc = run_device(ctx, dv, n, dm, dr, dord, raw_only ? ZSB_RAW_ONLY : ZSB_HAS_WRAPPED, st))) return rc;
+    if ((rc = run_device(ctx, dv, n, dm, dr, mm.data(), ord.data(), raw_only ? ZSB_RAW_ONLY : ZSB_HAS_WRAPPED, st))) return rc;
     CK(ctx, cudaMemcpyAsync(r, dr, n * sizeof(zsb_result), cudaMemcpyDeviceToHost, st));
     CK(ctx, cudaStreamSynchronize(st));
     return 0;

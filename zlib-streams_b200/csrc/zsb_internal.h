@@ -11,7 +11,14 @@ struct zsb_dev {
     int device = 0;
     int sm_count = 0;
     cudaStream_t stream = nullptr, copy_stream = nullptr;
-    uint16_t *fixed = nullptr;         // prebuilt fixed-code tables (one member slot)
+    uint16_t *fixed = nullptr;         // prebuilt fixed-code tables (one member slot, group path)
+    uint8_t *fixed_lane = nullptr;     // the same in the lane path's slot format
+    uint8_t *d_seq = nullptr;          // LZ sequence arena of the lane path
+    size_t d_seq_cap = 0;
+    uint8_t *d_plan = nullptr;         // per call: slot order (u32) + per-slot sequence offsets (u64)
+    size_t d_plan_cap = 0;
+    bool lane_configured = false;
+    int lz_occ = 0;
     uint32_t *counters = nullptr;      // [0] decode work counter, [1] check work counter
     zsb::Aux *aux = nullptr;
     size_t aux_cap = 0;
@@ -26,7 +33,9 @@ struct zsb_dev {
 
 struct zsb_ctx {
     std::vector<zsb_dev> devs;
-    int lanes = 32;                    // lanes of a warp that cooperate on one member
+    int lanes = 16;                    // group path: lanes of a warp that cooperate on one member
+    int path = 0;                      // 0 auto, 1 lane path (k_lane + k_lz), 2 group path (k_inflate<G>)
+    size_t seq_arena_bytes = 32ull << 30;   // most sequence scratch one slice of a batch may use
     size_t slab_bytes = 256u << 20;
     long launches = 0;
     char err[256] = "";

@@ -205,3 +205,53 @@ k_check(const zsb_member *__restrict__ members, zsb_result *__restrict__ results
 }
 
 }  // namespace zsb
+
+// ------------------------------------------------------------------------------------------------
+// Lane path: k_lane (one member per lane, symbols -> LZ sequences) then k_lz (one warp per member,
+// sequences -> bytes).  See zsb_lane.cuh / zsb_lz.cuh.
+// ------------------------------------------------------------------------------------------------
+#include "zsb_lz.cuh"
+
+namespace zsb {
+
+__global__ void __launch_bounds__(lane::WARPS * 32, 1) k_lane(lane::Batch B) {
+    extern __shared__ __align__(16) uint8_t smem[];
+    uint32_t *lut = (uint32_t *)smem;
+    init_lut(lut, threadIdx.x, blockDim.x);
+    __syncthreads();
+    const int ln = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    uint8_t *scr = smem + LUT_BYTES + (size_t)warp * lane::WSCR;
+    uint8_t *slots = smem + LUT_BYTES + (size_t)lane::WARPS * lane::WSCR + (size_t)warp * 32 * lane::SLOT;
+    lane::warp_lanes<32>(B, slots, scr, lut, ln);
+}
+
+constexpr int LZ_THREADS = 256;
+__global__ void __launch_bounds__(LZ_THREADS) k_lz(lane::Batch B, uint32_t *counter) {
+    const int ln = threadIdx.x & 31;
+    for (;;) {
+        uint32_t slot = 0;
+        if (ln == 0) slot = atomicAdd(counter, 1u);
+        slot = __shfl_sync(0xffffffffu, slot, 0);
+        if (slot >= B.n) break;
+        const uint32_t idx = B.order[slot];
+        const uint32_t nseq = B.aux[idx].nseq;
+        if (!nseq) continue;
+        const zsb_member m = B.members[idx];
+        lz::resolve_member<32>((uint8_t *)m.out, (const uint8_t *)m.in, B.seq_base + B.seq_off[slot], nseq, ln);
+    }
+}
+
+// tables of the fixed code (reference src/inflate.c:260-298) in the lane path's slot format
+__global__ void k_build_fixed_lane(uint8_t *fixed_tab) {
+    __shared__ __align__(16) uint8_t T[lane::SLOT];
+    __shared__ __align__(16) uint8_t scr[lane::WSCR];
+    const int ln = threadIdx.x;
+    for (int i = ln; i < 288; i += 32) T[lane::H_LENS + i] = i < 144 ? 8 : i < 256 ? 9 : i < 280 ? 7 : 8;
+    for (int i = ln; i < 32; i += 32) T[lane::H_LENS + 288 + i] = 5;
+    __syncwarp();
+    lane::build_tables<32>(T, scr, 288, 32, false, ln);
+    __syncwarp();
+    for (int i = ln; i < lane::SLOT; i += 32) fixed_tab[i] = T[i];
+}
+
+}  // namespace zsb

@@ -1,0 +1,832 @@
+// zsb_lane.cuh — the lane-per-member decoder ("phase A") of the batched inflate engine, sm_100a.
+//
+// Why: the decode loop is bound by instruction issue, not by HBM.  With a group of lanes per member
+// only the leader lane decodes, so a warp instruction yields at most 32/G symbols.  Here every lane of
+// a warp owns one member and decodes one symbol per loop trip, so a warp instruction works on 32
+// symbols.  To keep the 32 lanes in lock step the loop never touches the output: symbols are turned
+// into 8-byte LZ SEQUENCES (up to three literals + one match) in a per-member scratch array, and
+// k_lz (zsb_lz.cuh, one warp per member, coalesced) turns the sequences into bytes afterwards.
+//
+// Shared memory is what limits the number of resident members, so the per-member tables are compact
+// (976 bytes): an 8-bit literal/length root of 16-bit entries, a 6-bit distance root of 8-bit entries,
+// and canonical-code side arrays (left-aligned limits + symbols in code order) for longer codes.
+// Per-lane work that is rare and long (block headers, the last bytes of a member, wrapper headers) is
+// done in a service section between runs of the lock-step symbol loop; Huffman tables are built by
+// the whole warp together, one member after the other.
+//
+// Behavioural contract: identical to zsb_device.cuh (reference src/inflate.c:597-1275,
+// src/inffast.c:50-304, src/inftrees.c:33-321) — same order of checks, same consumed-input
+// accounting at every stop, same accept/reject decisions of the table builder.
+#pragma once
+#include "zsb_device.cuh"
+
+namespace zsb {
+namespace lane {
+
+// ---- per-member table slot (bytes) ----
+constexpr int LRB = 8;                    // literal/length root bits
+constexpr int DRB = 6;                    // distance root bits
+constexpr int S_LR = 0;                   // u16[256]  litlen root: same entry format as zsb_device.cuh
+constexpr int S_LS = 512;                 // u8[288]   low byte of the symbols with codes longer than LRB, code order
+constexpr int S_DS = 800;                 // u8[32]    distance symbols with codes longer than DRB, code order
+constexpr int S_DR = 832;                 // u8[64]    distance root: sym<<3 | len (1..6), 0 = longer code, 7 = invalid
+constexpr int S_LLIM = 896;               // u16[8]    litlen left-aligned (15 bit) code limits for lengths 9..15
+constexpr int S_LBASE = 912;              // u16[8]    index bias into S_LS for lengths 9..15
+constexpr int S_LT256 = 928;              // u16[8]    first S_LS index holding a symbol >= 256, per length 9..15
+constexpr int S_DLIM = 944;               // u16[9]    distance limits for lengths 7..15
+constexpr int S_DBASE = 962;              // u8[9]     index bias into S_DS for lengths 7..15
+constexpr int SLOT = 976;                 // bytes per member
+// while a block header is read the slot holds (the tables are built over it afterwards):
+constexpr int H_LENS = 0;                 // u8[320]   code lengths of the litlen + distance codes
+constexpr int H_CL = 512;                 // u8[128]   code-length code root (7 bits): sym<<3 | len
+constexpr int H_CLL = 640;                // u8[19]    code-length code lengths
+
+// ---- per-warp scratch (bytes) for the cooperative table build ----
+constexpr int W_SORT = 0;                 // u16[288]  symbols in code order
+constexpr int W_CNT = 576;                // u32[16]   codes per length
+constexpr int W_LIT = 640;                // u32[16]   codes per length whose symbol is < 256
+constexpr int W_OFF = 704;                // u32[16]   running sort offset per length
+constexpr int W_DL = 768;                 // u8[32]    distance code lengths
+constexpr int WSCR = 1024;
+
+constexpr int WARPS = 7;                  // warps per CTA, one CTA per SM: 224 members in flight per SM
+constexpr size_t SMEM = LUT_BYTES + (size_t)WARPS * WSCR + (size_t)WARPS * 32 * SLOT;
+
+// ---- LZ sequence (8 bytes): lo = lit0 | lit1<<8 | lit2<<16 | flags, hi = payload ----
+constexpr uint32_t Q_NLIT_SHIFT = 24;     // bits 24,25: number of literals (0..3)
+constexpr uint32_t Q_MATCH = 1u << 26;    // hi = (len-3)<<16 | (dist-1)
+constexpr uint32_t Q_RAW = 1u << 27;      // stored bytes: hi = offset in the member's input, lo[15:0] = count
+constexpr uint32_t Q_ABSLEN = 1u << 28;   // with Q_MATCH: hi>>16 is the length itself (capacity-cut 1 or 2)
+
+struct seq_t {
+    uint32_t lo, hi;
+};
+
+// ---- warp primitives, W = 32 on the device, 1 in the host emulation of the test tier ----
+template <int W> struct Wp {
+    static ZSB_DEV unsigned ballot(bool p) { return __ballot_sync(0xffffffffu, p); }
+    static ZSB_DEV bool any(bool p) { return __any_sync(0xffffffffu, p); }
+    static ZSB_DEV uint32_t shfl(uint32_t v, int src) { return __shfl_sync(0xffffffffu, v, src); }
+    static ZSB_DEV uint32_t shfl_up(uint32_t v, int d) { return __shfl_up_sync(0xffffffffu, v, d); }
+    static ZSB_DEV unsigned match(uint32_t v) { return __match_any_sync(0xffffffffu, v); }
+    static ZSB_DEV void sync() { __syncwarp(); }
+};
+template <> struct Wp<1> {
+    static ZSB_DEV unsigned ballot(bool p) { return p ? 1u : 0u; }
+    static ZSB_DEV bool any(bool p) { return p; }
+    static ZSB_DEV uint32_t shfl(uint32_t v, int) { return v; }
+    static ZSB_DEV uint32_t shfl_up(uint32_t v, int) { return v; }
+    static ZSB_DEV unsigned match(uint32_t) { return 1u; }
+    static ZSB_DEV void sync() {}
+};
+
+// per-lane decoder state
+struct Lane {
+    Dec d;               // bit input, output accounting, stop bookkeeping (zsb_device.cuh)
+    Mem mm;
+    uint32_t wnext;      // the input word at d.b.next, loaded ahead of its use
+    seq_t *seq;          // this member's sequence array
+    uint32_t ns;         // sequences written
+    uint32_t lw, nl;     // literals waiting for their sequence
+    uint32_t hist;       // valid bytes of history before out[0] (0 for one-shot members)
+    uint32_t nlen, ndist;
+};
+
+ZSB_DEV void emit(Lane &L, uint32_t lo, uint32_t hi) {
+    seq_t s;
+    s.lo = lo;
+    s.hi = hi;
+    L.seq[L.ns++] = s;
+}
+ZSB_DEV void flush_literals(Lane &L) {
+    if (L.nl) emit(L, L.lw | (L.nl << Q_NLIT_SHIFT), 0);
+    L.lw = 0;
+    L.nl = 0;
+}
+ZSB_DEV void push_literal(Lane &L, uint32_t v) {
+    if (L.nl == 3) flush_literals(L);
+    L.lw |= v << (8 * L.nl);
+    L.nl++;
+    L.d.pos++;
+}
+// a match of n bytes (already cut to the capacity) at the current position
+ZSB_DEV void push_match(Lane &L, uint32_t n, uint32_t dist) {
+    uint32_t lo = L.lw | (L.nl << Q_NLIT_SHIFT) | Q_MATCH;
+    uint32_t hi = dist - 1u;
+    if (n < 3) {
+        lo |= Q_ABSLEN;
+        hi |= n << 16;
+    } else {
+        hi |= (n - 3u) << 16;
+    }
+    emit(L, lo, hi);
+    L.lw = 0;
+    L.nl = 0;
+    L.d.pos += n;
+}
+ZSB_DEV void push_raw(Lane &L, uint32_t in_off, uint32_t n) {
+    flush_literals(L);
+    if (n) emit(L, Q_RAW | n, in_off);
+    L.d.pos += n;
+}
+
+ZSB_DEV void prime(Lane &L) {
+    const BitIn &b = L.d.b;
+    L.wnext = (b.next < b.len && (((uintptr_t)(b.p + b.next)) & 3) == 0) ? __ldg((const uint32_t *)(b.p + b.next)) : 0u;
+}
+
+// ------------------------------------------------------------------------------------------------
+// Code lookups on the compact tables.  `h` holds the next input bits (zero padded past the end of the
+// input); nb receives the code length.  Entries are in the format of zsb_device.cuh.
+// ------------------------------------------------------------------------------------------------
+ZSB_DEV uint32_t sym_entry(uint32_t sym) {        // symbol -> entry without the length field
+    if (sym < 256) return K_LIT | (sym << 6);
+    if (sym == 256) return E_EOB;
+    if (sym < 286) return K_LEN | ((sym - 257) << 6);
+    return E_INVALID;
+}
+
+ZSB_DEV uint32_t litlen_long(const uint8_t *T, uint32_t h32, uint32_t &nb) {
+    const uint32_t c15 = __brev(h32) >> 17;
+    const uint16_t *lim = (const uint16_t *)(T + S_LLIM);
+    uint32_t k = 0;                                  // limits do not decrease: count those at or below c15
+#pragma unroll
+    for (int j = 0; j < 6; j++) k += c15 >= lim[j] ? 1u : 0u;
+    const uint32_t l = 9 + k;
+    const uint32_t idx = (((const uint16_t *)(T + S_LBASE))[k] + (c15 >> (15 - l))) & 0x1ffu;
+    uint32_t sym = T[S_LS + idx];
+    if (idx >= ((const uint16_t *)(T + S_LT256))[k]) sym += 256;
+    nb = l;
+    return sym_entry(sym);
+}
+ZSB_DEV uint32_t lookup_litlen(const uint8_t *T, uint32_t h32, uint32_t &nb) {
+    uint32_t e = ((const uint16_t *)(T + S_LR))[h32 & 255u];
+    if ((e & 0x30u) == K_LINK) return litlen_long(T, h32, nb);
+    nb = e & 15u;
+    return e;
+}
+// distance code: returns the symbol, 32 for an invalid code
+ZSB_DEV uint32_t lookup_dist(const uint8_t *T, uint32_t h32, uint32_t &nb) {
+    uint32_t e = T[S_DR + (h32 & 63u)];
+    if (e == 0) {
+        const uint32_t c15 = __brev(h32) >> 17;
+        const uint16_t *lim = (const uint16_t *)(T + S_DLIM);
+        uint32_t k = 0;
+#pragma unroll
+        for (int j = 0; j < 8; j++) k += c15 >= lim[j] ? 1u : 0u;
+        const uint32_t l = 7 + k;
+        const uint32_t idx = (T[S_DBASE + k] + (c15 >> (15 - l))) & 31u;
+        nb = l;
+        return T[S_DS + idx];
+    }
+    nb = e & 7u;
+    if (nb == 7) {
+        nb = 1;
+        return 32;
+    }
+    return e >> 3;
+}
+
+// ------------------------------------------------------------------------------------------------
+// One symbol with every input step checked (the last bytes of a member): stops exactly where the
+// reference would wait for input (src/inflate.c:1046-1142).  Returns EV_LIT (byte in d.mdist),
+// EV_MATCH (d.mlen, d.mdist), EV_EOB, EV_ERR or EV_STARVE.
+// ------------------------------------------------------------------------------------------------
+ZSB_DEV int careful_symbol(Dec &d, const uint8_t *T, const uint32_t *lut) {
+    BitIn &b = d.b;
+    bi_fill(b);
+    uint32_t nb;
+    uint32_t e = lookup_litlen(T, (uint32_t)b.hold, nb);
+    if (nb > b.nbits) return EV_STARVE;
+    bi_drop(b, nb);
+    uint32_t kind = e & 0x30u, v = e >> 6;
+    if (kind == K_LIT) {
+        d.mdist = v;
+        return EV_LIT;
+    }
+    if (kind == K_SPECIAL) {
+        if (v == 0) return EV_EOB;
+        d.msg = M_LITCODE;
+        return EV_ERR;
+    }
+    uint32_t lw = lut[LUT_LEN + d.d64 * 32 + v];
+    uint32_t xb = lw >> 16;
+    if (!bi_need(b, xb)) return EV_STARVE;
+    d.mlen = (lw & 0xffffu) + (xb ? bi_peek(b, xb) : 0u);
+    bi_drop(b, xb);
+    bi_fill(b);
+    uint32_t s = lookup_dist(T, (uint32_t)b.hold, nb);
+    if (nb > b.nbits) return EV_STARVE;
+    bi_drop(b, nb);
+    if (s >= 32) {
+        d.msg = M_DISTCODE;
+        return EV_ERR;
+    }
+    uint32_t dw = lut[LUT_DIST + d.d64 * 32 + s];
+    if (dw >> 31) {
+        d.msg = M_DISTCODE;
+        return EV_ERR;
+    }
+    xb = (dw >> 16) & 15u;
+    if (!bi_need(b, xb)) return EV_STARVE;
+    d.mdist = (dw & 0xffffu) + (xb ? bi_peek(b, xb) : 0u);
+    bi_drop(b, xb);
+    return EV_MATCH;
+}
+
+// capacity / distance checks of a decoded match, then the sequence (src/inflate.c:1143-1153)
+ZSB_DEV int accept_match(Lane &L) {
+    Dec &d = L.d;
+    if (d.pos >= d.cap) return EV_OUTFULL;
+    if (d.mdist > d.pos + L.hist) {
+        d.msg = M_TOOFAR;
+        return EV_ERR;
+    }
+    uint32_t n = d.cap - d.pos;
+    const bool cut = n < d.mlen;
+    if (!cut) n = d.mlen;
+    push_match(L, n, d.mdist);
+    return cut ? EV_OUTFULL : EV_NONE;
+}
+
+// ------------------------------------------------------------------------------------------------
+// One symbol on the unchecked path: the caller guarantees that two whole input words are still
+// unread (b.next + 8 <= b.len), so nothing can run dry.  Returns EV_NONE or the stop event.
+// ------------------------------------------------------------------------------------------------
+ZSB_DEV void refill(Lane &L) {
+    BitIn &b = L.d.b;
+    b.hold |= (uint64_t)L.wnext << b.nbits;
+    b.nbits += 32;
+    b.next += 4;
+    L.wnext = b.next < b.len ? __ldg((const uint32_t *)(b.p + b.next)) : 0u;
+}
+
+ZSB_DEV int fast_symbol(Lane &L, const uint8_t *T, const uint32_t *lut) {
+    Dec &d = L.d;
+    BitIn &b = d.b;
+    if (b.nbits < 32) refill(L);
+    uint32_t nb;
+    uint32_t e = ((const uint16_t *)(T + S_LR))[(uint32_t)b.hold & 255u];
+    if ((e & 0x30u) == K_LINK) e = litlen_long(T, (uint32_t)b.hold, nb);
+    else nb = e & 15u;
+    bi_drop(b, nb);
+    const uint32_t kind = e & 0x30u, v = e >> 6;
+    if (kind == K_LIT) {
+        if (d.pos >= d.cap) return EV_OUTFULL;
+        push_literal(L, v);
+        return EV_NONE;
+    }
+    if (kind == K_SPECIAL) {
+        if (v == 0) return EV_EOB;
+        d.msg = M_LITCODE;
+        return EV_ERR;
+    }
+    const uint32_t lutoff = d.d64 * 32;
+    uint32_t lw = lut[LUT_LEN + lutoff + v];
+    uint32_t xb = lw >> 16;
+    d.mlen = (lw & 0xffffu) + ((uint32_t)b.hold & ((1u << xb) - 1u));
+    bi_drop(b, xb);
+    if (b.nbits < 32) refill(L);
+    uint32_t s = lookup_dist(T, (uint32_t)b.hold, nb);
+    bi_drop(b, nb);
+    if (s >= 32) {
+        d.msg = M_DISTCODE;
+        return EV_ERR;
+    }
+    uint32_t dw = lut[LUT_DIST + lutoff + s];
+    if (dw >> 31) {
+        d.msg = M_DISTCODE;
+        return EV_ERR;
+    }
+    xb = (dw >> 16) & 15u;
+    d.mdist = (dw & 0xffffu) + ((uint32_t)b.hold & ((1u << xb) - 1u));
+    bi_drop(b, xb);
+    return accept_match(L);
+}
+
+// ------------------------------------------------------------------------------------------------
+// Dynamic block header, per lane (reference src/inflate.c:905-1004): the counts, the code-length
+// code and the code lengths of both codes, left as bytes at T[H_LENS..].  The two decoding tables
+// are built afterwards by the whole warp (build_tables).  Returns EV_NONE, EV_ERR or EV_STARVE.
+// ------------------------------------------------------------------------------------------------
+constexpr int H_CNT = 672;                // u16[16] scratch of the code-length code census
+constexpr int H_NXT = 704;                // u16[16]
+
+ZSB_DEV bool build_clen8(uint8_t *T, bool d64) {
+    const uint8_t *lens = T + H_CLL;
+    uint16_t *cnt = (uint16_t *)(T + H_CNT), *nxt = (uint16_t *)(T + H_NXT);
+    uint8_t *C = T + H_CL;
+    uint32_t maxl;
+    int k = code_census(lens, 19, cnt, nxt, false, maxl);
+    if (k < 0) return false;
+    if (k == 1) {                    // no codes: every lookup reads "length 0, one bit" (src/inftrees.c:131-139)
+        if (d64) return false;
+        for (int i = 0; i < 128; i++) C[i] = 1;
+        return true;
+    }
+    for (uint32_t s = 0; s < 19; s++) {
+        uint32_t l = lens[s];
+        if (!l) continue;
+        uint32_t c = nxt[l]++;
+        uint32_t e = l | (s << 3);
+        for (uint32_t i = rev_bits(c, l); i < 128; i += 1u << l) C[i] = (uint8_t)e;
+    }
+    return true;
+}
+
+ZSB_DEV int lane_dynamic_header(Lane &L, uint8_t *T, const uint32_t *lut) {
+    Dec &d = L.d;
+    BitIn &b = d.b;
+    uint8_t *lens = T + H_LENS;
+    if (!bi_need(b, 14)) return EV_STARVE;
+    uint32_t nlen = bi_peek(b, 5) + 257;
+    bi_drop(b, 5);
+    uint32_t ndist = bi_peek(b, 5) + 1;
+    bi_drop(b, 5);
+    uint32_t ncode = bi_peek(b, 4) + 4;
+    bi_drop(b, 4);
+    if (nlen > 286 || (!d.d64 && ndist > 30)) {
+        d.msg = M_TOOMANY;
+        return EV_ERR;
+    }
+    const uint8_t *order = (const uint8_t *)(lut + LUT_ORDER);
+    for (uint32_t i = 0; i < 19; i++) {
+        uint32_t v = 0;
+        if (i < ncode) {
+            if (!bi_need(b, 3)) return EV_STARVE;
+            v = bi_peek(b, 3);
+            bi_drop(b, 3);
+        }
+        T[H_CLL + order[i]] = (uint8_t)v;
+    }
+    if (!build_clen8(T, d.d64)) {
+        d.msg = M_CLENS;
+        return EV_ERR;
+    }
+    const uint8_t *C = T + H_CL;
+    uint32_t have = 0, total = nlen + ndist;
+    while (have < total) {
+        if (b.nbits < 32) bi_fill(b);
+        uint32_t e = C[(uint32_t)b.hold & 127u];
+        uint32_t nb = e & 7u, sym = e >> 3;
+        if (nb > b.nbits) return EV_STARVE;
+        if (sym < 16) {
+            bi_drop(b, nb);
+            lens[have++] = (uint8_t)sym;
+            continue;
+        }
+        uint32_t xb = sym == 16 ? 2u : sym == 17 ? 3u : 7u;
+        if (nb + xb > b.nbits) return EV_STARVE;
+        bi_drop(b, nb);
+        uint32_t val = 0;
+        if (sym == 16) {
+            if (have == 0) {
+                d.msg = M_REPEAT;
+                d.extent = 2;         // the two repeat bits were pulled but not dropped (src/inflate.c:959-966)
+                return EV_ERR;
+            }
+            val = lens[have - 1];
+        }
+        uint32_t rep = (sym == 18 ? 11u : 3u) + bi_peek(b, xb);
+        bi_drop(b, xb);
+        if (have + rep > total) {
+            d.msg = M_REPEAT;
+            return EV_ERR;
+        }
+        while (rep--) lens[have++] = (uint8_t)val;
+    }
+    if (lens[256] == 0) {
+        d.msg = M_NOEOB;
+        return EV_ERR;
+    }
+    L.nlen = nlen;
+    L.ndist = ndist;
+    return EV_NONE;
+}
+
+// ------------------------------------------------------------------------------------------------
+// Table construction by the whole warp for ONE member (reference src/inftrees.c:33-321 decides what
+// is accepted; the tables themselves are ours).  `lens` = n code lengths in shared memory, `scr` =
+// the warp's scratch.  All lanes call with the same arguments and get the same return value.
+// ------------------------------------------------------------------------------------------------
+#ifndef ZSB_FETCH_ADD
+#define ZSB_FETCH_ADD(p, v) atomicAdd((p), (v))
+#endif
+#ifndef ZSB_SMEM_ADD
+#define ZSB_SMEM_ADD(p, v) atomicAdd((p), (v))
+#endif
+constexpr int W_FIRST = 832;              // u32[16] first canonical code per length
+constexpr int W_LIM = 896;                // u32[16] (first+count) left-aligned to 15 bits
+constexpr int W_OFF0 = 960;               // u32[16] index of the first symbol of each length in code order
+
+// Table space the reference's two-level builder would use with `root` index bits: the root plus one
+// sub-table per root prefix that carries longer codes, sized by the longest code under the prefix
+// (src/inftrees.c:222-228, 275-297).  cnt/first are per-length arrays.
+ZSB_DEV uint32_t ref_table_space(const uint32_t *cnt, const uint32_t *first, uint32_t root, uint32_t maxl) {
+    uint32_t used = 1u << root, last_p = 0xffffffffu, last_curr = 0;
+    for (uint32_t l = root + 1; l <= maxl; l++) {
+        if (!cnt[l]) continue;
+        uint32_t lo = first[l] >> (l - root), hi = (first[l] + cnt[l] - 1u) >> (l - root);
+        if (lo == last_p) {
+            used += (1u << (l - root)) - (1u << last_curr);
+            lo++;
+        }
+        if (hi + 1 > lo) used += (hi + 1 - lo) << (l - root);
+        last_p = hi;
+        last_curr = l - root;
+    }
+    return used;
+}
+
+// Census + code-order sort.  Returns 0 complete, 1 no codes, 2 a single 1-bit code, -1 invalid set.
+template <int W>
+ZSB_DEV int census_sort(const uint8_t *lens, uint32_t n, uint8_t *scr, int lane, uint32_t &maxl) {
+    uint32_t *cnt = (uint32_t *)(scr + W_CNT), *lit = (uint32_t *)(scr + W_LIT), *off = (uint32_t *)(scr + W_OFF);
+    uint32_t *first = (uint32_t *)(scr + W_FIRST), *lim = (uint32_t *)(scr + W_LIM), *off0 = (uint32_t *)(scr + W_OFF0);
+    uint16_t *sorted = (uint16_t *)(scr + W_SORT);
+    for (int i = lane; i < 48; i += W) cnt[i] = 0;          // cnt, lit, off are contiguous
+    Wp<W>::sync();
+    for (uint32_t s = lane; s < n; s += W) {
+        uint32_t l = lens[s];
+        if (l) {
+            ZSB_SMEM_ADD(&cnt[l], 1u);
+            if (s < 256) ZSB_SMEM_ADD(&lit[l], 1u);
+        }
+    }
+    Wp<W>::sync();
+    // every lane walks the 15 lengths (same values everywhere); lane 0 records the per-length arrays
+    int left = 1, bad = 0;
+    uint32_t code = 0, o = 0;
+    maxl = 0;
+    for (uint32_t l = 1; l <= 15; l++) {
+        const uint32_t c = cnt[l];
+        left = (left << 1) - (int)c;
+        if (left < 0) bad = 1;
+        if (c) maxl = l;
+        if (lane == 0) {
+            first[l] = code;
+            lim[l] = (code + c) << (15 - l);
+            off0[l] = o;
+            off[l] = o;
+        }
+        code = (code + c) << 1;
+        o += c;
+    }
+    Wp<W>::sync();
+    if (bad) return -1;
+    if (maxl == 0) return 1;
+    int k = 0;
+    if (left > 0) {
+        if (maxl != 1) return -1;
+        k = 2;
+    }
+    // symbols in code order: by length, then by symbol value
+    for (uint32_t s0 = 0; s0 < n; s0 += W) {
+        const uint32_t s = s0 + lane;
+        const uint32_t l = s < n ? lens[s] : 0u;
+        const unsigned m = Wp<W>::match(l);
+        const uint32_t rank = __popc(m & ((1u << lane) - 1u));
+        uint32_t at = 0;
+        if (l) at = off[l] + rank;
+        Wp<W>::sync();
+        if (l) {
+            sorted[at] = (uint16_t)s;
+            if (rank == 0) off[l] += __popc(m);
+        }
+        Wp<W>::sync();
+    }
+    return k;
+}
+
+// literal/length code: lens[0..nlen).  false -> "invalid literal/lengths set"
+template <int W>
+ZSB_DEV bool build_litlen_tab(uint8_t *T, uint8_t *scr, const uint8_t *lens, uint32_t nlen, bool d64, int lane) {
+    uint32_t maxl;
+    const int k = census_sort<W>(lens, nlen, scr, lane, maxl);
+    if (k < 0 || k == 1) return false;
+    const uint32_t *cnt = (const uint32_t *)(scr + W_CNT), *lit = (const uint32_t *)(scr + W_LIT);
+    const uint32_t *first = (const uint32_t *)(scr + W_FIRST), *lim = (const uint32_t *)(scr + W_LIM);
+    const uint32_t *off0 = (const uint32_t *)(scr + W_OFF0);
+    const uint16_t *sorted = (const uint16_t *)(scr + W_SORT);
+    if (maxl > 9 && ref_table_space(cnt, first, 9, maxl) > (d64 ? 851u : 852u)) return false;
+    uint16_t *LR = (uint16_t *)(T + S_LR);
+    for (uint32_t i = lane; i < 256; i += W) {
+        const uint32_t c15 = __brev(i) >> 17;
+        uint32_t l = 1;
+#pragma unroll
+        for (int j = 1; j <= LRB; j++) l += c15 >= lim[j] ? 1u : 0u;
+        uint32_t e;
+        if (l > LRB) {
+            e = k == 2 ? (E_INVALID | 1u) : K_LINK;
+        } else {
+            const uint32_t s = sorted[off0[l] + (c15 >> (15 - l)) - first[l]];
+            e = sym_entry(s) | l;
+        }
+        LR[i] = (uint16_t)e;
+    }
+    const uint32_t total = off0[15] + cnt[15];
+    const uint32_t nroot = maxl > LRB ? off0[LRB + 1] : total;
+    for (uint32_t j = lane; j + nroot < total; j += W) T[S_LS + j] = (uint8_t)sorted[nroot + j];
+    for (int j = lane; j < 7; j += W) {
+        const uint32_t l = 9 + j;
+        ((uint16_t *)(T + S_LLIM))[j] = (uint16_t)lim[l];
+        ((uint16_t *)(T + S_LBASE))[j] = (uint16_t)(off0[l] - nroot - first[l]);
+        ((uint16_t *)(T + S_LT256))[j] = (uint16_t)(off0[l] - nroot + lit[l]);
+    }
+    Wp<W>::sync();
+    return true;
+}
+
+// distance code: lens[0..ndist).  false -> "invalid distances set"
+template <int W>
+ZSB_DEV bool build_dist_tab(uint8_t *T, uint8_t *scr, const uint8_t *lens, uint32_t ndist, bool d64, int lane) {
+    uint32_t maxl;
+    const int k = census_sort<W>(lens, ndist, scr, lane, maxl);
+    if (k < 0) return false;
+    if (k == 1) {                                           // src/inftrees.c:131-139
+        if (d64) return false;
+        for (int i = lane; i < 64; i += W) T[S_DR + i] = 7;
+        Wp<W>::sync();
+        return true;
+    }
+    const uint32_t *cnt = (const uint32_t *)(scr + W_CNT);
+    const uint32_t *first = (const uint32_t *)(scr + W_FIRST), *lim = (const uint32_t *)(scr + W_LIM);
+    const uint32_t *off0 = (const uint32_t *)(scr + W_OFF0);
+    const uint16_t *sorted = (const uint16_t *)(scr + W_SORT);
+    if (d64 && maxl > 6 && ref_table_space(cnt, first, 6, maxl) > 593u) return false;
+    for (uint32_t i = lane; i < 64; i += W) {
+        const uint32_t c15 = __brev(i) >> 17;
+        uint32_t l = 1;
+#pragma unroll
+        for (int j = 1; j <= DRB; j++) l += c15 >= lim[j] ? 1u : 0u;
+        uint32_t e;
+        if (l > DRB) e = k == 2 ? 7u : 0u;
+        else e = ((uint32_t)sorted[off0[l] + (c15 >> (15 - l)) - first[l]] << 3) | l;
+        T[S_DR + i] = (uint8_t)e;
+    }
+    const uint32_t total = off0[15] + cnt[15];
+    const uint32_t nroot = maxl > DRB ? off0[DRB + 1] : total;
+    for (uint32_t j = lane; j + nroot < total; j += W) T[S_DS + j] = (uint8_t)sorted[nroot + j];
+    for (int j = lane; j < 9; j += W) {
+        const uint32_t l = 7 + j;
+        ((uint16_t *)(T + S_DLIM))[j] = (uint16_t)lim[l];
+        T[S_DBASE + j] = (uint8_t)(off0[l] - nroot - first[l]);
+    }
+    Wp<W>::sync();
+    return true;
+}
+
+// both tables of a dynamic block from T[H_LENS..]: returns 0 or the message id
+template <int W>
+ZSB_DEV int build_tables(uint8_t *T, uint8_t *scr, uint32_t nlen, uint32_t ndist, bool d64, int lane) {
+    uint8_t *dl = scr + W_DL;
+    for (uint32_t i = lane; i < ndist; i += W) dl[i] = T[H_LENS + nlen + i];
+    Wp<W>::sync();
+    if (!build_litlen_tab<W>(T, scr, T + H_LENS, nlen, d64, lane)) return M_LITLENS;
+    if (!build_dist_tab<W>(T, scr, dl, ndist, d64, lane)) return M_DISTS;
+    return 0;
+}
+
+// ------------------------------------------------------------------------------------------------
+// The warp: 32 members in flight, one per lane.
+// ------------------------------------------------------------------------------------------------
+enum : int { LS_FETCH = 0, LS_BLOCK = 1, LS_SYM = 2, LS_TAIL = 3, LS_IDLE = 4, LS_BUILD = 5, LS_FIXED = 6, LS_EVENT = 7 };
+
+struct Batch {
+    const zsb_member *members;
+    zsb_result *results;
+    Aux *aux;
+    const uint32_t *order;       // slot -> member index
+    const uint64_t *seq_off;     // per slot: first sequence of the member's array in seq_base
+    seq_t *seq_base;
+    const uint32_t *hist;        // optional: valid history bytes before each member's out
+    uint32_t n;
+    uint32_t *counter;
+    const uint8_t *fixed_tab;    // SLOT bytes: tables of the fixed code
+};
+
+ZSB_DEV void finish(Lane &L, int ev, const Batch &B) {
+    flush_literals(L);
+    write_result(L.d, L.mm, ev, B.results + L.mm.idx, B.aux + L.mm.idx);
+    B.aux[L.mm.idx].nseq = L.ns;
+}
+
+// descriptor + wrapper header of a new member; returns the lane's next state
+ZSB_DEV int start_member(Lane &L, uint32_t slot, const Batch &B) {
+    const uint32_t idx = B.order[slot];
+    const zsb_member m = B.members[idx];
+    Dec &d = L.d;
+    Mem &mm = L.mm;
+    const uint8_t *in = (const uint8_t *)m.in;
+    mm.idx = idx; mm.kind = 0; mm.adler0 = 0; mm.hdr_stop = false; mm.hdr_tin = 0; mm.hdr_bits = 0;
+    d.b.p = in;
+    d.b.len = (uint32_t)m.in_len;
+    d.b.next = 0; d.b.nbits = 0; d.b.hold = 0;
+    d.out = (uint8_t *)m.out;
+    d.pos = 0;
+    d.cap = (uint32_t)m.out_cap;
+    d.d64 = m.window_bits == -16;
+    d.last = 0; d.at_type = 0; d.msg = 0; d.extent = 0; d.mlen = 0; d.mdist = 0; d.mtrunc = 0;
+    L.seq = B.seq_base + B.seq_off[slot];
+    L.ns = 0; L.lw = 0; L.nl = 0; L.wnext = 0;
+    L.hist = B.hist ? B.hist[idx] : 0u;
+    int ev = EV_NONE;
+    if (!wbits_valid(m.window_bits) || (in == nullptr && m.in_len != 0) || (m.out == nullptr && m.out_cap != 0)) {
+        ev = EV_INITERR;
+    } else {
+        HeadOut h = parse_wrapper(in, d.b.len, m.window_bits);
+        mm.kind = h.kind;
+        mm.adler0 = h.adler;
+        ev = h.ev;
+        if (ev == EV_NONE) {
+            bi_seek(d.b, h.pos);
+            d.at_type = mm.kind != 0;
+        } else {
+            mm.hdr_stop = true;
+            d.msg = h.msg;
+            mm.hdr_tin = ev == EV_STARVE ? d.b.len : h.pulled;
+            mm.hdr_bits = h.bits;
+        }
+    }
+    if (ev != EV_NONE) {
+        finish(L, ev, B);
+        return LS_FETCH;
+    }
+    return LS_BLOCK;
+}
+
+// block headers of one lane until a block with symbols starts (reference src/inflate.c:831-1004);
+// stored blocks become raw sequences on the way.  Returns the lane's next state.
+ZSB_DEV int lane_block(Lane &L, uint8_t *T, const uint32_t *lut, const Batch &B) {
+    Dec &d = L.d;
+    BitIn &b = d.b;
+    for (;;) {
+        if (d.last) {
+            finish(L, EV_DONE, B);
+            return LS_FETCH;
+        }
+        if (!bi_need(b, 3)) {
+            finish(L, EV_STARVE, B);
+            return LS_FETCH;
+        }
+        d.last = bi_peek(b, 1);
+        bi_drop(b, 1);
+        const uint32_t btype = bi_peek(b, 2);
+        bi_drop(b, 2);
+        d.at_type = 0;
+        if (btype == 3) {
+            d.msg = M_BTYPE;
+            finish(L, EV_ERR, B);
+            return LS_FETCH;
+        }
+        if (btype == 2) {
+            const int ev = lane_dynamic_header(L, T, lut);
+            if (ev != EV_NONE) {
+                finish(L, ev, B);
+                return LS_FETCH;
+            }
+            return LS_BUILD;
+        }
+        if (btype == 1) return LS_FIXED;
+        // stored block (src/inflate.c:870-904)
+        bi_drop(b, b.nbits & 7);
+        const uint32_t bytepos = b.next - (b.nbits >> 3);
+        if (b.len - bytepos < 4) {
+            b.nbits = 8 * (b.len - bytepos);
+            b.next = b.len;
+            finish(L, EV_STARVE, B);
+            return LS_FETCH;
+        }
+        const uint32_t v = le32(b.p + bytepos);
+        if ((v & 0xffffu) != ((v >> 16) ^ 0xffffu)) {
+            d.msg = M_STORED;
+            d.extent = 32;
+            finish(L, EV_ERR, B);
+            return LS_FETCH;
+        }
+        const uint32_t spos = bytepos + 4;
+        uint32_t slen = v & 0xffffu;
+        const uint32_t have = b.len - spos, left = d.cap - d.pos;
+        bool cut = false;
+        if (slen > have) slen = have, cut = true;
+        if (slen > left) slen = left, cut = true;
+        push_raw(L, spos, slen);
+        bi_seek(b, spos + slen);
+        d.at_type = 1;
+        if (cut) {                             // input or output ran out inside the block
+            b.next = spos + slen;
+            b.nbits = 0;
+            b.hold = 0;
+            d.at_type = 0;
+            finish(L, EV_OUTFULL, B);
+            return LS_FETCH;
+        }
+    }
+}
+
+template <int W>
+__device__ __forceinline__ void warp_lanes(const Batch &B, uint8_t *slots, uint8_t *scr, const uint32_t *lut, int lane) {
+    Lane L;
+    L.d.pos = 0; L.d.cap = 0; L.d.b.p = nullptr; L.d.b.len = 0; L.d.b.next = 0; L.d.b.nbits = 0; L.d.b.hold = 0;
+    L.d.d64 = 0; L.d.msg = 0; L.ns = 0; L.nl = 0; L.lw = 0; L.seq = nullptr; L.wnext = 0; L.nlen = 0; L.ndist = 0;
+    L.mm.idx = 0;
+    uint8_t *T = slots + (size_t)lane * SLOT;
+    int st = LS_FETCH, ev = EV_NONE;
+    const unsigned lt = (1u << lane) - 1u;
+
+    for (;;) {
+        // ---------------- service: until every lane is decoding symbols or out of work ----------------
+        for (;;) {
+            if (!Wp<W>::any(st != LS_SYM && st != LS_IDLE)) break;
+            if (st == LS_EVENT) {
+                if (ev == EV_EOB) {
+                    L.d.at_type = 1;
+                    st = LS_BLOCK;
+                } else {
+                    finish(L, ev, B);
+                    st = LS_FETCH;
+                }
+                ev = EV_NONE;
+            }
+            const unsigned fm = Wp<W>::ballot(st == LS_FETCH);
+            if (fm) {
+                const int leader = __ffs(fm) - 1;
+                uint32_t base = 0;
+                if (lane == leader) base = ZSB_FETCH_ADD(B.counter, (uint32_t)__popc(fm));
+                base = Wp<W>::shfl(base, leader);
+                if (st == LS_FETCH) {
+                    const uint32_t slot = base + __popc(fm & lt);
+                    if (slot >= B.n) st = LS_IDLE;
+                    else st = start_member(L, slot, B);
+                }
+            }
+            if (st == LS_BLOCK) st = lane_block(L, T, lut, B);
+            Wp<W>::sync();
+            unsigned bm = Wp<W>::ballot(st == LS_BUILD || st == LS_FIXED);
+            while (bm) {
+                const int src = __ffs(bm) - 1;
+                bm &= bm - 1;
+                const uint32_t info = Wp<W>::shfl((uint32_t)(st == LS_FIXED) | (L.d.d64 << 1) | (L.nlen << 2) | (L.ndist << 12), src);
+                uint8_t *Ts = slots + (size_t)src * SLOT;
+                int msg = 0;
+                if (info & 1u) {
+                    const uint32_t *f = (const uint32_t *)B.fixed_tab;
+                    uint32_t *t32 = (uint32_t *)Ts;
+                    for (int i = lane; i < SLOT / 4; i += W) t32[i] = f[i];
+                    Wp<W>::sync();
+                } else {
+                    msg = build_tables<W>(Ts, scr, (info >> 2) & 1023u, info >> 12, (info >> 1) & 1u, lane);
+                }
+                if (lane == src) {
+                    if (msg) {
+                        L.d.msg = msg;
+                        finish(L, EV_ERR, B);
+                        st = LS_FETCH;
+                    } else {
+                        st = LS_SYM;
+                        prime(L);
+                    }
+                }
+            }
+            if (st == LS_SYM && L.d.b.next + 8 > L.d.b.len) st = LS_TAIL;
+            while (st == LS_TAIL) {             // the last bytes of a member: every step checked
+                int e2 = careful_symbol(L.d, T, lut);
+                if (e2 == EV_LIT) {
+                    if (L.d.pos >= L.d.cap) e2 = EV_OUTFULL;
+                    else {
+                        push_literal(L, L.d.mdist);
+                        continue;
+                    }
+                } else if (e2 == EV_MATCH) {
+                    e2 = accept_match(L);
+                    if (e2 == EV_NONE) continue;
+                }
+                if (e2 == EV_EOB) {
+                    L.d.at_type = 1;
+                    st = LS_BLOCK;
+                } else {
+                    finish(L, e2, B);
+                    st = LS_FETCH;
+                }
+            }
+            Wp<W>::sync();
+        }
+        if (!Wp<W>::any(st == LS_SYM)) break;
+        // ---------------- the lock-step symbol loop ----------------
+#pragma unroll 1
+        for (;;) {
+            if (st == LS_SYM) {
+                if (L.d.b.next + 8 > L.d.b.len) {
+                    st = LS_TAIL;
+                } else {
+                    ev = fast_symbol(L, T, lut);
+                    if (ev != EV_NONE) st = LS_EVENT;
+                }
+            }
+            if (Wp<W>::any(st != LS_SYM && st != LS_IDLE)) break;
+        }
+    }
+}
+
+}  // namespace lane
+}  // namespace zsb
