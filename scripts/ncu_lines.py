@@ -30,7 +30,12 @@ for l in dis[start + 1:]:
         addr2line[int(m.group(1), 16)] = (cur, m.group(2))
 raw = subprocess.run(["ncu", "-i", rep, "--page", "source", "--csv"], capture_output=True, text=True).stdout.splitlines()
 rows = list(csv.reader(raw))
-hi = [i for i, r in enumerate(rows) if r and r[0] == "Address"][0]
+# one section per profiled launch: "Kernel Name" row, header row, instruction rows; take the LAST launch of the kernel
+want = os.environ.get("NCU_KERNEL", "")
+secs = [i for i, r in enumerate(rows) if r and r[0] == "Kernel Name" and want in r[1]]
+hi = secs[-1] + 1
+end = min([i for i, r in enumerate(rows) if r and r[0] == "Kernel Name" and i > hi] + [len(rows)])
+rows = rows[:end]
 hdr = rows[hi]
 ia, ii, isamp, ithr = hdr.index("Address"), hdr.index("Instructions Executed"), hdr.index("# Samples"), hdr.index("Thread Instructions Executed")
 stall_cols = [(i, h) for i, h in enumerate(hdr) if h.startswith("stall_") and "Not Issued" not in h]

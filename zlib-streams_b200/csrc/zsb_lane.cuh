@@ -85,8 +85,8 @@ struct Lane {
     Dec d;               // bit input, output accounting, stop bookkeeping (zsb_device.cuh)
     Mem mm;
     uint32_t wnext;      // the input word at d.b.next, loaded ahead of its use
-    seq_t *seq;          // this member's sequence array
-    uint32_t ns;         // sequences written
+    seq_t *seq;          // where this member's next sequence goes
+    seq_t *seq0;         // start of its sequence array
     uint32_t lw, nl;     // literals waiting for their sequence
     uint32_t hist;       // valid bytes of history before out[0] (0 for one-shot members)
     uint32_t nlen, ndist;
@@ -96,7 +96,7 @@ ZSB_DEV void emit(Lane &L, uint32_t lo, uint32_t hi) {
     seq_t s;
     s.lo = lo;
     s.hi = hi;
-    L.seq[L.ns++] = s;
+    *L.seq++ = s;
 }
 ZSB_DEV void flush_literals(Lane &L) {
     if (L.nl) emit(L, L.lw | (L.nl << Q_NLIT_SHIFT), 0);
@@ -146,7 +146,14 @@ ZSB_DEV uint32_t sym_entry(uint32_t sym) {        // symbol -> entry without the
     return E_INVALID;
 }
 
-ZSB_DEV uint32_t litlen_long(const uint8_t *T, uint32_t h32, uint32_t &nb) {
+// A root entry of kind K_LINK stands for all codes longer than LRB bits that start with that root
+// index.  Canonical codes that share a prefix are neighbours in code order, so when they all have the
+// same length l the symbol is LS[base + next (l - LRB) bits] with no further table: entry bits [3:0] =
+// l - LRB, bit 6 = 0, bits [15:7] = base.  Only the few prefixes that hold codes of several lengths
+// (bit 6 set) need the search through the per-length limits.
+constexpr uint32_t LINK_MIXED = 1u << 6;
+
+ZSB_DEV uint32_t litlen_mixed(const uint8_t *T, uint32_t h32, uint32_t &nb) {
     const uint32_t c15 = __brev(h32) >> 17;
     const uint16_t *lim = (const uint16_t *)(T + S_LLIM);
     uint32_t k = 0;                                  // limits do not decrease: count those at or below c15
@@ -159,9 +166,18 @@ ZSB_DEV uint32_t litlen_long(const uint8_t *T, uint32_t h32, uint32_t &nb) {
     nb = l;
     return sym_entry(sym);
 }
+ZSB_DEV uint32_t litlen_long(const uint8_t *T, uint32_t e, uint32_t h32, uint32_t &nb) {
+    if (e & LINK_MIXED) return litlen_mixed(T, h32, nb);
+    const uint32_t x = e & 15u;
+    const uint32_t idx = (e >> 7) + (__brev(h32 >> LRB) >> (32 - x));
+    const uint32_t sym = T[S_LS + idx];
+    nb = LRB + x;
+    if (idx >= ((const uint16_t *)(T + S_LT256))[x - 1]) return sym_entry(sym + 256);
+    return K_LIT | (sym << 6);
+}
 ZSB_DEV uint32_t lookup_litlen(const uint8_t *T, uint32_t h32, uint32_t &nb) {
     uint32_t e = ((const uint16_t *)(T + S_LR))[h32 & 255u];
-    if ((e & 0x30u) == K_LINK) return litlen_long(T, h32, nb);
+    if ((e & 0x30u) == K_LINK) return litlen_long(T, e, h32, nb);
     nb = e & 15u;
     return e;
 }
@@ -265,43 +281,81 @@ ZSB_DEV int fast_symbol(Lane &L, const uint8_t *T, const uint32_t *lut) {
     Dec &d = L.d;
     BitIn &b = d.b;
     if (b.nbits < 32) refill(L);
+    // the code and its extra bits (at most 31 bits) are taken from a 32-bit view of the bit buffer
+    const uint32_t w = (uint32_t)b.hold;
     uint32_t nb;
-    uint32_t e = ((const uint16_t *)(T + S_LR))[(uint32_t)b.hold & 255u];
-    if ((e & 0x30u) == K_LINK) e = litlen_long(T, (uint32_t)b.hold, nb);
+    uint32_t e = ((const uint16_t *)(T + S_LR))[w & 255u];
+    if ((e & 0x30u) == K_LINK) e = litlen_long(T, e, w, nb);
     else nb = e & 15u;
-    bi_drop(b, nb);
     const uint32_t kind = e & 0x30u, v = e >> 6;
+    int ev = EV_NONE;
+    bool put = false;                  // one sequence store at most, shared by both branches
+    uint32_t qlo = 0, qhi = 0;
     if (kind == K_LIT) {
+        bi_drop(b, nb);
         if (d.pos >= d.cap) return EV_OUTFULL;
-        push_literal(L, v);
-        return EV_NONE;
-    }
-    if (kind == K_SPECIAL) {
+        if (L.nl == 3) {
+            put = true;
+            qlo = L.lw | (3u << Q_NLIT_SHIFT);
+            L.lw = v;
+            L.nl = 1;
+        } else {
+            L.lw |= v << (8 * L.nl);
+            L.nl++;
+        }
+        d.pos++;
+    } else if (kind == K_LEN) {
+        const uint32_t lutoff = d.d64 * 32;
+        const uint32_t lw = lut[LUT_LEN + lutoff + v];
+        uint32_t xb = lw >> 16;
+        d.mlen = (lw & 0xffffu) + ((w >> nb) & ((1u << xb) - 1u));
+        bi_drop(b, nb + xb);
+        if (b.nbits < 32) refill(L);
+        const uint32_t w2 = (uint32_t)b.hold;
+        const uint32_t s = lookup_dist(T, w2, nb);
+        if (s >= 32) {
+            bi_drop(b, nb);
+            d.msg = M_DISTCODE;
+            return EV_ERR;
+        }
+        const uint32_t dw = lut[LUT_DIST + lutoff + s];
+        if (dw >> 31) {
+            bi_drop(b, nb);
+            d.msg = M_DISTCODE;
+            return EV_ERR;
+        }
+        xb = (dw >> 16) & 15u;
+        d.mdist = (dw & 0xffffu) + ((w2 >> nb) & ((1u << xb) - 1u));
+        bi_drop(b, nb + xb);
+        // capacity first, then the distance (src/inflate.c:1143-1153)
+        if (d.pos >= d.cap) return EV_OUTFULL;
+        if (d.mdist > d.pos + L.hist) {
+            d.msg = M_TOOFAR;
+            return EV_ERR;
+        }
+        uint32_t n = d.cap - d.pos;
+        if (n < d.mlen) ev = EV_OUTFULL;
+        else n = d.mlen;
+        put = true;
+        qlo = L.lw | (L.nl << Q_NLIT_SHIFT) | Q_MATCH;
+        qhi = d.mdist - 1u;
+        if (n < 3) {
+            qlo |= Q_ABSLEN;
+            qhi |= n << 16;
+        } else {
+            qhi |= (n - 3u) << 16;
+        }
+        L.lw = 0;
+        L.nl = 0;
+        d.pos += n;
+    } else {
+        bi_drop(b, nb);
         if (v == 0) return EV_EOB;
         d.msg = M_LITCODE;
         return EV_ERR;
     }
-    const uint32_t lutoff = d.d64 * 32;
-    uint32_t lw = lut[LUT_LEN + lutoff + v];
-    uint32_t xb = lw >> 16;
-    d.mlen = (lw & 0xffffu) + ((uint32_t)b.hold & ((1u << xb) - 1u));
-    bi_drop(b, xb);
-    if (b.nbits < 32) refill(L);
-    uint32_t s = lookup_dist(T, (uint32_t)b.hold, nb);
-    bi_drop(b, nb);
-    if (s >= 32) {
-        d.msg = M_DISTCODE;
-        return EV_ERR;
-    }
-    uint32_t dw = lut[LUT_DIST + lutoff + s];
-    if (dw >> 31) {
-        d.msg = M_DISTCODE;
-        return EV_ERR;
-    }
-    xb = (dw >> 16) & 15u;
-    d.mdist = (dw & 0xffffu) + ((uint32_t)b.hold & ((1u << xb) - 1u));
-    bi_drop(b, xb);
-    return accept_match(L);
+    if (put) emit(L, qlo, qhi);
+    return ev;
 }
 
 // ------------------------------------------------------------------------------------------------
@@ -510,6 +564,7 @@ ZSB_DEV bool build_litlen_tab(uint8_t *T, uint8_t *scr, const uint8_t *lens, uin
     const uint16_t *sorted = (const uint16_t *)(scr + W_SORT);
     if (maxl > 9 && ref_table_space(cnt, first, 9, maxl) > (d64 ? 851u : 852u)) return false;
     uint16_t *LR = (uint16_t *)(T + S_LR);
+    const uint32_t nroot0 = off0[LRB + 1];
     for (uint32_t i = lane; i < 256; i += W) {
         const uint32_t c15 = __brev(i) >> 17;
         uint32_t l = 1;
@@ -517,7 +572,19 @@ ZSB_DEV bool build_litlen_tab(uint8_t *T, uint8_t *scr, const uint8_t *lens, uin
         for (int j = 1; j <= LRB; j++) l += c15 >= lim[j] ? 1u : 0u;
         uint32_t e;
         if (l > LRB) {
-            e = k == 2 ? (E_INVALID | 1u) : K_LINK;
+            if (k == 2) {
+                e = E_INVALID | 1u;
+            } else {
+                // lengths of the first and of the last code under this prefix
+                const uint32_t last15 = c15 | ((1u << (15 - LRB)) - 1u);
+                uint32_t lf = LRB + 1, ll = LRB + 1;
+                for (int j = LRB + 1; j < 15; j++) {
+                    lf += c15 >= lim[j] ? 1u : 0u;
+                    ll += last15 >= lim[j] ? 1u : 0u;
+                }
+                if (lf == ll) e = K_LINK | (lf - LRB) | ((off0[lf] - nroot0 + (c15 >> (15 - lf)) - first[lf]) << 7);
+                else e = K_LINK | LINK_MIXED;
+            }
         } else {
             const uint32_t s = sorted[off0[l] + (c15 >> (15 - l)) - first[l]];
             e = sym_entry(s) | l;
@@ -608,7 +675,7 @@ struct Batch {
 ZSB_DEV void finish(Lane &L, int ev, const Batch &B) {
     flush_literals(L);
     write_result(L.d, L.mm, ev, B.results + L.mm.idx, B.aux + L.mm.idx);
-    B.aux[L.mm.idx].nseq = L.ns;
+    B.aux[L.mm.idx].nseq = (uint32_t)(L.seq - L.seq0);
 }
 
 // descriptor + wrapper header of a new member; returns the lane's next state
@@ -627,8 +694,8 @@ ZSB_DEV int start_member(Lane &L, uint32_t slot, const Batch &B) {
     d.cap = (uint32_t)m.out_cap;
     d.d64 = m.window_bits == -16;
     d.last = 0; d.at_type = 0; d.msg = 0; d.extent = 0; d.mlen = 0; d.mdist = 0; d.mtrunc = 0;
-    L.seq = B.seq_base + B.seq_off[slot];
-    L.ns = 0; L.lw = 0; L.nl = 0; L.wnext = 0;
+    L.seq = L.seq0 = B.seq_base + B.seq_off[slot];
+    L.lw = 0; L.nl = 0; L.wnext = 0;
     L.hist = B.hist ? B.hist[idx] : 0u;
     int ev = EV_NONE;
     if (!wbits_valid(m.window_bits) || (in == nullptr && m.in_len != 0) || (m.out == nullptr && m.out_cap != 0)) {
@@ -728,7 +795,7 @@ template <int W>
 __device__ __forceinline__ void warp_lanes(const Batch &B, uint8_t *slots, uint8_t *scr, const uint32_t *lut, int lane) {
     Lane L;
     L.d.pos = 0; L.d.cap = 0; L.d.b.p = nullptr; L.d.b.len = 0; L.d.b.next = 0; L.d.b.nbits = 0; L.d.b.hold = 0;
-    L.d.d64 = 0; L.d.msg = 0; L.ns = 0; L.nl = 0; L.lw = 0; L.seq = nullptr; L.wnext = 0; L.nlen = 0; L.ndist = 0;
+    L.d.d64 = 0; L.d.msg = 0; L.nl = 0; L.lw = 0; L.seq = L.seq0 = nullptr; L.wnext = 0; L.nlen = 0; L.ndist = 0;
     L.mm.idx = 0;
     uint8_t *T = slots + (size_t)lane * SLOT;
     int st = LS_FETCH, ev = EV_NONE;
