@@ -97,27 +97,111 @@ __device__ __forceinline__ uint32_t crc_span(uint32_t s, const uint8_t *p, uint3
     return s;
 }
 
-__global__ void __launch_bounds__(CHK_THREADS)
-k_check(const zsb_member *__restrict__ members, zsb_result *__restrict__ results, const Aux *__restrict__ aux,
-        uint32_t n, uint32_t *counter) {
-    __shared__ uint32_t tab[4][256];
-    __shared__ uint32_t s_idx;
-    __shared__ uint32_t red[CHK_THREADS / 32][2];
-    __shared__ unsigned long long red64[CHK_THREADS / 32][2];
-    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+struct ChkShared {
+    uint32_t tab[4][256];
+    uint32_t red[CHK_THREADS / 32][2];
+    unsigned long long red64[CHK_THREADS / 32][2];
+};
+
+__device__ __forceinline__ void chk_init(ChkShared &sh) {
+    const int tid = threadIdx.x;
     for (int i = tid; i < 256; i += CHK_THREADS) {
         uint32_t c = i;
         for (int k = 0; k < 8; k++) c = (c >> 1) ^ (CRC_POLY & (0u - (c & 1u)));
-        tab[0][i] = c;
+        sh.tab[0][i] = c;
     }
     __syncthreads();
     for (int k = 1; k < 4; k++) {
         for (int i = tid; i < 256; i += CHK_THREADS) {
-            uint32_t c = tab[k - 1][i];
-            tab[k][i] = (c >> 8) ^ tab[0][c & 0xff];
+            uint32_t c = sh.tab[k - 1][i];
+            sh.tab[k][i] = (c >> 8) ^ sh.tab[0][c & 0xff];
         }
         __syncthreads();
     }
+}
+
+// Check value of `init` continued over out[0..E) by the whole CTA (kind 2 = CRC-32, else Adler-32);
+// valid on thread 0.  init is the running value: crc32(0)=0 / adler32(0)=1 for a fresh stream.
+__device__ __forceinline__ uint32_t cta_check(ChkShared &sh, uint32_t kind, const uint8_t *out, uint32_t E, uint32_t init) {
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    uint32_t check = init;
+    if (E == 0) return check;
+    if (kind == 2) {
+        uint32_t s = 0;
+        const uint32_t ntiles = (E + CHK_TILE - 1) / CHK_TILE;
+        for (uint32_t t = ntiles; t-- > 0;) {            // t = tile index counted from the end
+            long long lo = (long long)E - (long long)(t + 1) * CHK_TILE + (long long)tid * CHK_SPAN;
+            long long hi = lo + CHK_SPAN;
+            if (hi > 0) {
+                if (lo < 0) lo = 0;
+                s = crc_span(s, out + lo, (uint32_t)(hi - lo), sh.tab);
+            }
+            if (t) s = gf2_mul(c_crc.tile_skip, s);
+        }
+        // merge lanes: value(tid) * x^(8*SPAN*(127-tid))
+        for (int k = 0; k < 5; k++) {
+            uint32_t o = __shfl_down_sync(0xffffffffu, s, 1 << k);
+            if ((lane & ((2 << k) - 1)) == 0) s = gf2_mul(c_crc.span_pow[k], s) ^ o;
+        }
+        if (lane == 0) sh.red[warp][0] = s;
+        __syncthreads();
+        if (tid == 0) {
+            uint32_t z = sh.red[0][0];
+            for (int wv = 1; wv < CHK_THREADS / 32; wv++) z = gf2_mul(c_crc.span_pow[5], z) ^ sh.red[wv][0];
+            check = ~(gf2_mul(crc_xpow(8ull * E), ~init) ^ z);
+        }
+        __syncthreads();
+    } else {
+        const uint32_t P = 65521u;
+        unsigned long long S = 0, W = 0;
+        uint32_t head = (uint32_t)((4 - ((uintptr_t)out & 3)) & 3);
+        if (head > E) head = E;
+        const uint32_t nw = (E - head) >> 2;
+        const uint32_t *w32 = (const uint32_t *)(out + head);
+        uint32_t im = (head + 4u * tid) % P;             // byte index of this thread's word, mod P
+        const uint32_t step = (4u * CHK_THREADS) % P;
+        for (uint32_t w = tid; w < nw; w += CHK_THREADS) {
+            uint32_t v = w32[w];
+            uint32_t sb = __dp4a(v, 0x01010101u, 0u);
+            uint32_t q = __dp4a(v, 0x03020100u, 0u);
+            S += sb;
+            W += (unsigned long long)im * sb + q;
+            im += step;
+            if (im >= P) im -= P;
+        }
+        if (tid == 0) {
+            for (uint32_t i = 0; i < head; i++) { S += out[i]; W += (unsigned long long)i * out[i]; }
+            for (uint32_t i = head + 4 * nw; i < E; i++) { S += out[i]; W += (unsigned long long)(i % P) * out[i]; }
+        }
+        S %= P; W %= P;
+        for (int o = 16; o; o >>= 1) {
+            S += __shfl_down_sync(0xffffffffu, S, o);
+            W += __shfl_down_sync(0xffffffffu, W, o);
+        }
+        if (lane == 0) { sh.red64[warp][0] = S; sh.red64[warp][1] = W; }
+        __syncthreads();
+        if (tid == 0) {
+            unsigned long long s = 0, wsum = 0;
+            for (int wv = 0; wv < CHK_THREADS / 32; wv++) { s += sh.red64[wv][0]; wsum += sh.red64[wv][1]; }
+            s %= P; wsum %= P;
+            // s1' = s1 + S;  s2' = s2 + E*s1 + E*S - W   (W = sum of i*b_i, i from 0)
+            const unsigned long long nm = E % P, s1 = init & 0xffffu, s2 = init >> 16;
+            const uint32_t r1 = (uint32_t)((s1 + s) % P);
+            const uint32_t r2 = (uint32_t)((s2 + nm * s1 + nm * s + (unsigned long long)P - wsum) % P);
+            check = (r2 << 16) | r1;
+        }
+        __syncthreads();
+    }
+    return check;
+}
+
+__global__ void __launch_bounds__(CHK_THREADS)
+k_check(const zsb_member *__restrict__ members, zsb_result *__restrict__ results, const Aux *__restrict__ aux,
+        uint32_t n, uint32_t *counter) {
+    __shared__ ChkShared sh;
+    __shared__ uint32_t s_idx;
+    const int tid = threadIdx.x;
+    chk_init(sh);
     for (;;) {
         if (tid == 0) s_idx = atomicAdd(counter, 1u);
         __syncthreads();
@@ -128,74 +212,7 @@ k_check(const zsb_member *__restrict__ members, zsb_result *__restrict__ results
         if (a.kind == 0) continue;
         const uint8_t *out = (const uint8_t *)members[idx].out;
         const uint32_t E = (uint32_t)results[idx].total_out;
-        uint32_t check = a.init_check;
-        if (E > 0 && a.kind == 2) {
-            // ---- CRC-32 ----
-            uint32_t s = 0;
-            const uint32_t ntiles = (E + CHK_TILE - 1) / CHK_TILE;
-            for (uint32_t t = ntiles; t-- > 0;) {            // t = tile index counted from the end
-                long long lo = (long long)E - (long long)(t + 1) * CHK_TILE + (long long)tid * CHK_SPAN;
-                long long hi = lo + CHK_SPAN;
-                if (hi > 0) {
-                    if (lo < 0) lo = 0;
-                    s = crc_span(s, out + lo, (uint32_t)(hi - lo), tab);
-                }
-                if (t) s = gf2_mul(c_crc.tile_skip, s);
-            }
-            // merge lanes: value(tid) * x^(8*SPAN*(127-tid))
-            for (int k = 0; k < 5; k++) {
-                uint32_t o = __shfl_down_sync(0xffffffffu, s, 1 << k);
-                if ((lane & ((2 << k) - 1)) == 0) s = gf2_mul(c_crc.span_pow[k], s) ^ o;
-            }
-            if (lane == 0) red[warp][0] = s;
-            __syncthreads();
-            if (tid == 0) {
-                uint32_t z = red[0][0];
-                for (int wv = 1; wv < CHK_THREADS / 32; wv++) z = gf2_mul(c_crc.span_pow[5], z) ^ red[wv][0];
-                check = ~(gf2_mul(crc_xpow(8ull * E), 0xFFFFFFFFu) ^ z);
-            }
-            __syncthreads();
-        } else if (E > 0) {
-            // ---- Adler-32 ----
-            const uint32_t P = 65521u;
-            unsigned long long S = 0, W = 0;
-            uint32_t head = (uint32_t)((4 - ((uintptr_t)out & 3)) & 3);
-            if (head > E) head = E;
-            const uint32_t nw = (E - head) >> 2;
-            const uint32_t *w32 = (const uint32_t *)(out + head);
-            uint32_t im = (head + 4u * tid) % P;             // byte index of this thread's word, mod P
-            const uint32_t step = (4u * CHK_THREADS) % P;
-            for (uint32_t w = tid; w < nw; w += CHK_THREADS) {
-                uint32_t v = w32[w];
-                uint32_t sb = __dp4a(v, 0x01010101u, 0u);
-                uint32_t q = __dp4a(v, 0x03020100u, 0u);
-                S += sb;
-                W += (unsigned long long)im * sb + q;
-                im += step;
-                if (im >= P) im -= P;
-            }
-            if (tid == 0) {
-                for (uint32_t i = 0; i < head; i++) { S += out[i]; W += (unsigned long long)i * out[i]; }
-                for (uint32_t i = head + 4 * nw; i < E; i++) { S += out[i]; W += (unsigned long long)(i % P) * out[i]; }
-            }
-            S %= P; W %= P;
-            for (int o = 16; o; o >>= 1) {
-                S += __shfl_down_sync(0xffffffffu, S, o);
-                W += __shfl_down_sync(0xffffffffu, W, o);
-            }
-            if (lane == 0) { red64[warp][0] = S; red64[warp][1] = W; }
-            __syncthreads();
-            if (tid == 0) {
-                unsigned long long s = 0, wsum = 0;
-                for (int wv = 0; wv < CHK_THREADS / 32; wv++) { s += red64[wv][0]; wsum += red64[wv][1]; }
-                s %= P; wsum %= P;
-                unsigned long long nm = E % P;
-                uint32_t s1 = (uint32_t)((1 + s) % P);
-                uint32_t s2 = (uint32_t)((nm + nm * s + (unsigned long long)P - wsum) % P);
-                check = (s2 << 16) | s1;
-            }
-            __syncthreads();
-        }
+        const uint32_t check = cta_check(sh, a.kind, out, E, a.init_check);
         if (tid == 0) {
             zsb_result r = results[idx];
             finish_member(r, a, (const uint8_t *)members[idx].in, (uint32_t)members[idx].in_len, check, E);

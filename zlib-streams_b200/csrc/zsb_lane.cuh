@@ -85,6 +85,7 @@ struct Lane {
     Dec d;               // bit input, output accounting, stop bookkeeping (zsb_device.cuh)
     Mem mm;
     uint32_t wnext;      // the input word at d.b.next, loaded ahead of its use
+    uint32_t wnext2;     // the word after it: two refills in a row never wait for memory
     seq_t *seq;          // where this member's next sequence goes
     seq_t *seq0;         // start of its sequence array
     uint32_t lw, nl;     // literals waiting for their sequence
@@ -130,9 +131,14 @@ ZSB_DEV void push_raw(Lane &L, uint32_t in_off, uint32_t n) {
     L.d.pos += n;
 }
 
+ZSB_DEV uint32_t load_ahead(const BitIn &b, uint32_t off) {
+    return off < b.len ? __ldg((const uint32_t *)(b.p + off)) : 0u;
+}
 ZSB_DEV void prime(Lane &L) {
     const BitIn &b = L.d.b;
-    L.wnext = (b.next < b.len && (((uintptr_t)(b.p + b.next)) & 3) == 0) ? __ldg((const uint32_t *)(b.p + b.next)) : 0u;
+    const bool aligned = (((uintptr_t)(b.p + b.next)) & 3) == 0;
+    L.wnext = aligned ? load_ahead(b, b.next) : 0u;
+    L.wnext2 = aligned ? load_ahead(b, b.next + 4) : 0u;
 }
 
 // ------------------------------------------------------------------------------------------------
@@ -148,9 +154,10 @@ ZSB_DEV uint32_t sym_entry(uint32_t sym) {        // symbol -> entry without the
 
 // A root entry of kind K_LINK stands for all codes longer than LRB bits that start with that root
 // index.  Canonical codes that share a prefix are neighbours in code order, so when they all have the
-// same length l the symbol is LS[base + next (l - LRB) bits] with no further table: entry bits [3:0] =
-// l - LRB, bit 6 = 0, bits [15:7] = base.  Only the few prefixes that hold codes of several lengths
-// (bit 6 set) need the search through the per-length limits.
+// same length l the symbol is LS[base + next (l - LRB) bits] with no further table: entry bits [2:0] =
+// l - LRB - 1, bits [15:7] = base.  The few prefixes that hold codes of several lengths (LINK_MIXED)
+// or a symbol >= 256 (LINK_HI) go through the search over the per-length limits instead.
+constexpr uint32_t LINK_HI = 1u << 3;
 constexpr uint32_t LINK_MIXED = 1u << 6;
 
 ZSB_DEV uint32_t litlen_mixed(const uint8_t *T, uint32_t h32, uint32_t &nb) {
@@ -167,13 +174,11 @@ ZSB_DEV uint32_t litlen_mixed(const uint8_t *T, uint32_t h32, uint32_t &nb) {
     return sym_entry(sym);
 }
 ZSB_DEV uint32_t litlen_long(const uint8_t *T, uint32_t e, uint32_t h32, uint32_t &nb) {
-    if (e & LINK_MIXED) return litlen_mixed(T, h32, nb);
-    const uint32_t x = e & 15u;
+    if (e & (LINK_MIXED | LINK_HI)) return litlen_mixed(T, h32, nb);
+    const uint32_t x = (e & 7u) + 1u;
     const uint32_t idx = (e >> 7) + (__brev(h32 >> LRB) >> (32 - x));
-    const uint32_t sym = T[S_LS + idx];
     nb = LRB + x;
-    if (idx >= ((const uint16_t *)(T + S_LT256))[x - 1]) return sym_entry(sym + 256);
-    return K_LIT | (sym << 6);
+    return K_LIT | ((uint32_t)T[S_LS + idx] << 6);
 }
 ZSB_DEV uint32_t lookup_litlen(const uint8_t *T, uint32_t h32, uint32_t &nb) {
     uint32_t e = ((const uint16_t *)(T + S_LR))[h32 & 255u];
@@ -274,88 +279,84 @@ ZSB_DEV void refill(Lane &L) {
     b.hold |= (uint64_t)L.wnext << b.nbits;
     b.nbits += 32;
     b.next += 4;
-    L.wnext = b.next < b.len ? __ldg((const uint32_t *)(b.p + b.next)) : 0u;
+    L.wnext = L.wnext2;
+    L.wnext2 = load_ahead(b, b.next + 4);
 }
 
-ZSB_DEV int fast_symbol(Lane &L, const uint8_t *T, const uint32_t *lut) {
+// Returns true when the symbol was a literal or a whole match that fits and has been committed.
+// Anything else (end of block, invalid codes, a distance too far back, the capacity reached) leaves
+// the lane at the start of the symbol (only a refill may have happened) and returns false: the
+// checked path then decodes that symbol again and stops where the reference stops.
+// Written as straight-line code: the match fields are computed for every lane and selected
+// afterwards, because with 32 members per warp every branch of a symbol is taken by some lane on
+// nearly every trip anyway.
+ZSB_DEV bool fast_symbol(Lane &L, const uint8_t *T, const uint32_t *lut) {
     Dec &d = L.d;
     BitIn &b = d.b;
     if (b.nbits < 32) refill(L);
     // the code and its extra bits (at most 31 bits) are taken from a 32-bit view of the bit buffer
     const uint32_t w = (uint32_t)b.hold;
-    uint32_t nb;
-    uint32_t e = ((const uint16_t *)(T + S_LR))[w & 255u];
-    if ((e & 0x30u) == K_LINK) e = litlen_long(T, e, w, nb);
-    else nb = e & 15u;
-    const uint32_t kind = e & 0x30u, v = e >> 6;
-    int ev = EV_NONE;
-    bool put = false;                  // one sequence store at most, shared by both branches
-    uint32_t qlo = 0, qhi = 0;
-    if (kind == K_LIT) {
-        bi_drop(b, nb);
-        if (d.pos >= d.cap) return EV_OUTFULL;
-        if (L.nl == 3) {
-            put = true;
-            qlo = L.lw | (3u << Q_NLIT_SHIFT);
-            L.lw = v;
-            L.nl = 1;
-        } else {
-            L.lw |= v << (8 * L.nl);
-            L.nl++;
-        }
-        d.pos++;
-    } else if (kind == K_LEN) {
-        const uint32_t lutoff = d.d64 * 32;
-        const uint32_t lw = lut[LUT_LEN + lutoff + v];
-        uint32_t xb = lw >> 16;
-        d.mlen = (lw & 0xffffu) + ((w >> nb) & ((1u << xb) - 1u));
-        bi_drop(b, nb + xb);
-        if (b.nbits < 32) refill(L);
-        const uint32_t w2 = (uint32_t)b.hold;
-        const uint32_t s = lookup_dist(T, w2, nb);
-        if (s >= 32) {
-            bi_drop(b, nb);
-            d.msg = M_DISTCODE;
-            return EV_ERR;
-        }
-        const uint32_t dw = lut[LUT_DIST + lutoff + s];
-        if (dw >> 31) {
-            bi_drop(b, nb);
-            d.msg = M_DISTCODE;
-            return EV_ERR;
-        }
-        xb = (dw >> 16) & 15u;
-        d.mdist = (dw & 0xffffu) + ((w2 >> nb) & ((1u << xb) - 1u));
-        bi_drop(b, nb + xb);
-        // capacity first, then the distance (src/inflate.c:1143-1153)
-        if (d.pos >= d.cap) return EV_OUTFULL;
-        if (d.mdist > d.pos + L.hist) {
-            d.msg = M_TOOFAR;
-            return EV_ERR;
-        }
-        uint32_t n = d.cap - d.pos;
-        if (n < d.mlen) ev = EV_OUTFULL;
-        else n = d.mlen;
-        put = true;
-        qlo = L.lw | (L.nl << Q_NLIT_SHIFT) | Q_MATCH;
-        qhi = d.mdist - 1u;
-        if (n < 3) {
-            qlo |= Q_ABSLEN;
-            qhi |= n << 16;
-        } else {
-            qhi |= (n - 3u) << 16;
-        }
+    const uint32_t e = ((const uint16_t *)(T + S_LR))[w & 255u];
+    const bool link = (e & 0x30u) == K_LINK;
+    const uint32_t x = (e & 7u) + 1u;
+    const uint32_t idx = link ? (e >> 7) + ((__brev(w >> LRB) >> 1) >> (31 - x)) : 0u;
+    const uint32_t ls = T[S_LS + idx];
+    uint32_t nb = link ? LRB + x : (e & 15u);
+    uint32_t kind = link ? K_LIT : (e & 0x30u);
+    uint32_t v = link ? ls : (e >> 6);
+    if (link && (e & (LINK_MIXED | LINK_HI))) {
+        const uint32_t e2 = litlen_mixed(T, w, nb);
+        kind = e2 & 0x30u;
+        v = e2 >> 6;
+    }
+    const bool islit = kind == K_LIT, islen = kind == K_LEN;
+    // ---- length extra bits, distance code and extra bits (meaningful when islen) ----
+    const uint32_t lutoff = d.d64 * 32;
+    const uint32_t lw = lut[LUT_LEN + lutoff + (v & 31u)];
+    const uint32_t xb = lw >> 16;
+    const uint32_t mlen = (lw & 0xffffu) + ((w >> nb) & ((1u << xb) - 1u));
+    const uint32_t used1 = nb + (islen ? xb : 0u);
+    uint64_t h2 = b.hold >> used1;
+    uint32_t n2 = b.nbits - used1, next2 = b.next, wn2 = L.wnext, wn3 = L.wnext2;
+    if (islen && n2 < 32) {
+        h2 |= (uint64_t)wn2 << n2;
+        n2 += 32;
+        next2 += 4;
+        wn2 = wn3;
+        wn3 = load_ahead(b, next2 + 4);
+    }
+    const uint32_t w2 = (uint32_t)h2;
+    uint32_t nb2 = 0, s = 0;
+    if (islen) s = lookup_dist(T, w2, nb2);
+    const uint32_t dw = lut[LUT_DIST + lutoff + (s & 31u)];
+    const uint32_t xb2 = (dw >> 16) & 15u;
+    const uint32_t mdist = (dw & 0xffffu) + ((w2 >> nb2) & ((1u << xb2) - 1u));
+    const uint32_t used2 = islen ? nb2 + xb2 : 0u;
+    const uint32_t n = islen ? mlen : 1u;
+    bool clean = (islit || islen) && d.pos + n <= d.cap;
+    if (islen && (s >= 32 || (dw >> 31) || mdist > d.pos + L.hist)) clean = false;
+    if (!clean) return false;
+    // ---- commit ----
+    b.hold = h2 >> used2;
+    b.nbits = n2 - used2;
+    b.next = next2;
+    L.wnext = wn2;
+    L.wnext2 = wn3;
+    d.pos += n;
+    const bool put = islen || L.nl == 3;
+    if (put) {
+        seq_t q;
+        q.lo = L.lw | (L.nl << Q_NLIT_SHIFT) | (islen ? Q_MATCH : 0u);
+        q.hi = islen ? ((mdist - 1u) | ((mlen - 3u) << 16)) : 0u;
+        *L.seq++ = q;
         L.lw = 0;
         L.nl = 0;
-        d.pos += n;
-    } else {
-        bi_drop(b, nb);
-        if (v == 0) return EV_EOB;
-        d.msg = M_LITCODE;
-        return EV_ERR;
     }
-    if (put) emit(L, qlo, qhi);
-    return ev;
+    if (islit) {
+        L.lw |= v << (8 * L.nl);
+        L.nl++;
+    }
+    return true;
 }
 
 // ------------------------------------------------------------------------------------------------
@@ -582,8 +583,13 @@ ZSB_DEV bool build_litlen_tab(uint8_t *T, uint8_t *scr, const uint8_t *lens, uin
                     lf += c15 >= lim[j] ? 1u : 0u;
                     ll += last15 >= lim[j] ? 1u : 0u;
                 }
-                if (lf == ll) e = K_LINK | (lf - LRB) | ((off0[lf] - nroot0 + (c15 >> (15 - lf)) - first[lf]) << 7);
-                else e = K_LINK | LINK_MIXED;
+                if (lf == ll) {
+                    const uint32_t at = off0[lf] + (c15 >> (15 - lf)) - first[lf];     // first code under the prefix
+                    e = K_LINK | (lf - LRB - 1u) | ((at - nroot0) << 7);
+                    if (sorted[at + (1u << (lf - LRB)) - 1u] >= 256) e |= LINK_HI;   // symbols ascend within a length
+                } else {
+                    e = K_LINK | LINK_MIXED;
+                }
             }
         } else {
             const uint32_t s = sorted[off0[l] + (c15 >> (15 - l)) - first[l]];
@@ -657,7 +663,7 @@ ZSB_DEV int build_tables(uint8_t *T, uint8_t *scr, uint32_t nlen, uint32_t ndist
 // ------------------------------------------------------------------------------------------------
 // The warp: 32 members in flight, one per lane.
 // ------------------------------------------------------------------------------------------------
-enum : int { LS_FETCH = 0, LS_BLOCK = 1, LS_SYM = 2, LS_TAIL = 3, LS_IDLE = 4, LS_BUILD = 5, LS_FIXED = 6, LS_EVENT = 7 };
+enum : int { LS_FETCH = 0, LS_BLOCK = 1, LS_SYM = 2, LS_TAIL = 3, LS_IDLE = 4, LS_BUILD = 5, LS_FIXED = 6 };
 
 struct Batch {
     const zsb_member *members;
@@ -695,7 +701,7 @@ ZSB_DEV int start_member(Lane &L, uint32_t slot, const Batch &B) {
     d.d64 = m.window_bits == -16;
     d.last = 0; d.at_type = 0; d.msg = 0; d.extent = 0; d.mlen = 0; d.mdist = 0; d.mtrunc = 0;
     L.seq = L.seq0 = B.seq_base + B.seq_off[slot];
-    L.lw = 0; L.nl = 0; L.wnext = 0;
+    L.lw = 0; L.nl = 0; L.wnext = 0; L.wnext2 = 0;
     L.hist = B.hist ? B.hist[idx] : 0u;
     int ev = EV_NONE;
     if (!wbits_valid(m.window_bits) || (in == nullptr && m.in_len != 0) || (m.out == nullptr && m.out_cap != 0)) {
@@ -795,26 +801,16 @@ template <int W>
 __device__ __forceinline__ void warp_lanes(const Batch &B, uint8_t *slots, uint8_t *scr, const uint32_t *lut, int lane) {
     Lane L;
     L.d.pos = 0; L.d.cap = 0; L.d.b.p = nullptr; L.d.b.len = 0; L.d.b.next = 0; L.d.b.nbits = 0; L.d.b.hold = 0;
-    L.d.d64 = 0; L.d.msg = 0; L.nl = 0; L.lw = 0; L.seq = L.seq0 = nullptr; L.wnext = 0; L.nlen = 0; L.ndist = 0;
+    L.d.d64 = 0; L.d.msg = 0; L.nl = 0; L.lw = 0; L.seq = L.seq0 = nullptr; L.wnext = 0; L.wnext2 = 0; L.nlen = 0; L.ndist = 0;
     L.mm.idx = 0;
     uint8_t *T = slots + (size_t)lane * SLOT;
-    int st = LS_FETCH, ev = EV_NONE;
+    int st = LS_FETCH;
     const unsigned lt = (1u << lane) - 1u;
 
     for (;;) {
         // ---------------- service: until every lane is decoding symbols or out of work ----------------
         for (;;) {
             if (!Wp<W>::any(st != LS_SYM && st != LS_IDLE)) break;
-            if (st == LS_EVENT) {
-                if (ev == EV_EOB) {
-                    L.d.at_type = 1;
-                    st = LS_BLOCK;
-                } else {
-                    finish(L, ev, B);
-                    st = LS_FETCH;
-                }
-                ev = EV_NONE;
-            }
             const unsigned fm = Wp<W>::ballot(st == LS_FETCH);
             if (fm) {
                 const int leader = __ffs(fm) - 1;
@@ -883,12 +879,7 @@ __device__ __forceinline__ void warp_lanes(const Batch &B, uint8_t *slots, uint8
 #pragma unroll 1
         for (;;) {
             if (st == LS_SYM) {
-                if (L.d.b.next + 8 > L.d.b.len) {
-                    st = LS_TAIL;
-                } else {
-                    ev = fast_symbol(L, T, lut);
-                    if (ev != EV_NONE) st = LS_EVENT;
-                }
+                if (L.d.b.next + 8 > L.d.b.len || !fast_symbol(L, T, lut)) st = LS_TAIL;
             }
             if (Wp<W>::any(st != LS_SYM && st != LS_IDLE)) break;
         }

@@ -1,0 +1,328 @@
+// zsb_stream.cuh — the resumable single-stream decoder behind the z_stream surface (inflateInit2_ /
+// inflate / inflateEnd of include/zsb.h, replacing reference src/inflate.c:186-224, 597-1287).
+//
+// One inflate() call = one launch of k_zs_decode (this file: symbols -> LZ sequences, the lane path's
+// decoder with one active lane), one of k_lz's resolver over those sequences, one of k_zs_finish
+// (running check value, trailer, sliding history).  Between calls the stream lives in device memory:
+// a State (resume point + Huffman tables), up to 64 KiB of history and a few carried input bytes.
+//
+// Resuming never re-enters the middle of a unit.  A unit is a wrapper header, a block header, one
+// symbol or one trailer word; when the input ends inside a unit the call reports what the reference
+// reports (all input consumed, the same bit count in data_type) but keeps the unit's bytes as CARRY
+// and decodes the unit again from its first bit when more input arrives.  What the reference holds
+// in its `hold`/`bits`/`mode` (src/inflate.h:83-128) is therefore {phase, bit0, carry}.
+#pragma once
+#include "zsb_lz.cuh"
+
+namespace zsb {
+namespace zs {
+
+enum : uint32_t { PH_HEAD = 0, PH_BLOCK = 1, PH_STORED = 2, PH_SYM = 3, PH_PENDLIT = 4, PH_PENDMATCH = 5,
+                  PH_CHECK = 6, PH_LENGTH = 7, PH_DONE = 8, PH_BAD = 9, PH_NEEDDICT = 10 };
+
+constexpr uint32_t HIST = 65536;          // bytes of history kept in front of every call's output
+
+// result of one launch sequence, read back by the host
+struct Call {
+    int32_t stop;          // EV_STARVE, EV_OUTFULL, EV_DONE, EV_ERR, EV_NEEDDICT
+    int32_t msg;           // message id for EV_ERR
+    uint32_t cpos;         // bytes of the (carry + new) input the reference has consumed
+    uint32_t resume_byte;  // first byte that has to be presented again (carry = [resume_byte, cpos))
+    uint32_t produced;
+    uint32_t data_type;    // strm->data_type
+    uint32_t adler;        // strm->adler
+    uint32_t nseq;
+    uint32_t trailer_pos;  // when need_trailer: byte offset of the trailer
+    uint32_t need_trailer;
+    uint32_t pad[2];
+};
+
+struct State {
+    uint32_t phase, bit0, last, d64;
+    int32_t wbits_arg;
+    uint32_t kind;         // 0 raw, 1 zlib, 2 gzip (known once the header is read)
+    uint32_t rem;          // stored bytes / match bytes still to produce
+    uint32_t mdist, plit;
+    uint32_t whave, wsize, wbits;   // history accounting as src/inflate.c:375-419 does it
+    uint32_t check;        // running Adler-32 / CRC-32 of all output
+    uint32_t total_lo;     // output so far, modulo 2^32 (gzip ISIZE)
+    uint32_t last_dt;      // data_type low bits of the last stop (for calls after the end)
+    uint32_t pad;
+    Call call;
+    alignas(16) uint8_t tables[lane::SLOT];
+};
+
+using lane::Lane;
+using lane::seq_t;
+
+struct Run {               // lane 0's bookkeeping during one call
+    uint32_t phase;
+    uint64_t unit;         // bit position where the current unit started
+    int stop;
+    bool hdr_stop;
+    uint32_t hdr_tin, hdr_bits;
+};
+
+ZSB_DEV uint64_t bitpos(const BitIn &b) { return 8ull * b.next - b.nbits; }
+
+// position the bit reader on an arbitrary bit
+ZSB_DEV void seek_bit(BitIn &b, uint64_t bp) {
+    bi_seek(b, (uint32_t)(bp >> 3));
+    const uint32_t r = (uint32_t)(bp & 7);
+    if (r) {
+        bi_fill(b);
+        bi_drop(b, r);
+    }
+}
+
+// Runs lane 0 until the call stops (returns 0), a dynamic block's tables have to be built (1) or the
+// fixed tables have to be copied (2).  R.stop is set when 0 is returned.
+ZSB_DEV int run_serial(State &S, Lane &L, Run &R, uint8_t *T, const uint32_t *lut, bool &primed) {
+    Dec &d = L.d;
+    BitIn &b = d.b;
+    for (;;) {
+        switch (R.phase) {
+        case PH_HEAD: {
+            HeadOut h = parse_wrapper(b.p, b.len, S.wbits_arg);
+            L.mm.kind = h.kind;
+            L.mm.adler0 = h.adler;
+            if (h.ev != EV_NONE) {
+                R.hdr_stop = true;
+                d.msg = h.msg;
+                R.hdr_tin = h.ev == EV_STARVE ? b.len : h.pulled;
+                R.hdr_bits = h.bits;
+                R.unit = 0;
+                R.stop = h.ev;
+                return 0;
+            }
+            S.kind = h.kind;
+            S.check = h.adler;
+            if (S.wbits == 0) S.wbits = h.kind == 1 ? (uint32_t)(b.p[0] >> 4) + 8u : 15u;
+            seek_bit(b, 8ull * h.pos);
+            d.at_type = h.kind != 0;
+            R.phase = PH_BLOCK;
+            break;
+        }
+        case PH_BLOCK: {
+            R.unit = bitpos(b);
+            if (d.last) {
+                bi_drop(b, b.nbits & 7);
+                R.unit = bitpos(b);
+                R.stop = EV_DONE;
+                return 0;
+            }
+            if (!bi_need(b, 3)) {
+                R.stop = EV_STARVE;
+                return 0;
+            }
+            d.last = bi_peek(b, 1);
+            bi_drop(b, 1);
+            const uint32_t btype = bi_peek(b, 2);
+            bi_drop(b, 2);
+            d.at_type = 0;
+            if (btype == 3) {
+                d.msg = M_BTYPE;
+                R.stop = EV_ERR;
+                return 0;
+            }
+            if (btype == 2) {
+                const int ev = lane::lane_dynamic_header(L, T, lut);
+                if (ev != EV_NONE) {
+                    R.stop = ev;
+                    return 0;
+                }
+                return 1;
+            }
+            if (btype == 1) return 2;
+            bi_drop(b, b.nbits & 7);
+            const uint32_t bytepos = b.next - (b.nbits >> 3);
+            if (b.len - bytepos < 4) {
+                b.nbits = 8 * (b.len - bytepos);
+                b.next = b.len;
+                R.stop = EV_STARVE;
+                return 0;
+            }
+            const uint32_t v = le32(b.p + bytepos);
+            if ((v & 0xffffu) != ((v >> 16) ^ 0xffffu)) {
+                d.msg = M_STORED;
+                d.extent = 32;
+                R.stop = EV_ERR;
+                return 0;
+            }
+            S.rem = v & 0xffffu;
+            seek_bit(b, 8ull * (bytepos + 4));
+            R.phase = PH_STORED;
+            break;
+        }
+        case PH_STORED: {
+            const uint32_t bytepos = b.next - (b.nbits >> 3);
+            uint32_t n = S.rem;
+            if (n > b.len - bytepos) n = b.len - bytepos;
+            if (n > d.cap - d.pos) n = d.cap - d.pos;
+            lane::push_raw(L, bytepos, n);
+            S.rem -= n;
+            seek_bit(b, 8ull * (bytepos + n));
+            R.unit = bitpos(b);
+            if (S.rem) {                          // src/inflate.c:886-890: no input or no room left
+                b.next = bytepos + n;
+                b.nbits = 0;
+                b.hold = 0;
+                R.stop = bytepos + n >= b.len ? EV_STARVE : EV_OUTFULL;
+                return 0;
+            }
+            d.at_type = 1;
+            R.phase = PH_BLOCK;
+            break;
+        }
+        case PH_PENDLIT:
+            R.unit = bitpos(b);
+            if (d.pos >= d.cap) {
+                R.stop = EV_OUTFULL;
+                return 0;
+            }
+            lane::push_literal(L, S.plit);
+            R.phase = PH_SYM;
+            break;
+        case PH_PENDMATCH: {
+            R.unit = bitpos(b);
+            if (d.pos >= d.cap) {
+                R.stop = EV_OUTFULL;
+                return 0;
+            }
+            if (S.mdist > d.pos + L.hist) {       // src/inflate.c:1146-1153
+                d.msg = M_TOOFAR;
+                R.stop = EV_ERR;
+                return 0;
+            }
+            uint32_t n = d.cap - d.pos;
+            if (n > S.rem) n = S.rem;
+            lane::push_match(L, n, S.mdist);
+            S.rem -= n;
+            if (S.rem) {
+                R.stop = EV_OUTFULL;
+                return 0;
+            }
+            R.phase = PH_SYM;
+            break;
+        }
+        case PH_SYM: {
+            R.unit = bitpos(b);
+            if (b.next + 8 <= b.len) {
+                if (!primed) {
+                    lane::prime(L);
+                    primed = true;
+                }
+                if (lane::fast_symbol(L, T, lut)) break;
+            }
+            primed = false;
+            R.unit = bitpos(b);
+            const int ev = lane::careful_symbol(d, T, lut);
+            if (ev == EV_LIT) {
+                S.plit = d.mdist;
+                R.phase = PH_PENDLIT;
+            } else if (ev == EV_MATCH) {
+                S.rem = d.mlen;
+                S.mdist = d.mdist;
+                R.phase = PH_PENDMATCH;
+            } else if (ev == EV_EOB) {
+                d.at_type = 1;
+                R.phase = PH_BLOCK;
+            } else {
+                R.stop = ev;                      // EV_ERR or EV_STARVE (the unit is decoded again later)
+                return 0;
+            }
+            break;
+        }
+        default:                                  // PH_CHECK, PH_LENGTH: the finish kernel reads the trailer
+            R.unit = bitpos(b);
+            R.stop = EV_DONE;
+            return 0;
+        }
+    }
+}
+
+// One call's decode: all W lanes enter, lane 0 owns the stream.
+template <int W>
+ZSB_DEV void stream_decode(State &S, const uint8_t *in, uint32_t in_len, uint32_t out_cap, seq_t *seq,
+                           const uint8_t *fixed_tab, uint8_t *scr, const uint32_t *lut, int ln) {
+    Lane L;
+    Run R;
+    Dec &d = L.d;
+    uint8_t *T = S.tables;
+    bool primed = false;
+    const bool active = ln == 0;
+    d.b.p = in; d.b.len = in_len; d.b.next = 0; d.b.nbits = 0; d.b.hold = 0;
+    d.out = nullptr; d.pos = 0; d.cap = out_cap; d.d64 = S.d64; d.last = S.last; d.at_type = 0; d.msg = 0;
+    d.extent = 0; d.mlen = 0; d.mdist = 0; d.mtrunc = 0;
+    L.mm.idx = 0; L.mm.kind = S.kind; L.mm.adler0 = S.check; L.mm.hdr_stop = false; L.mm.hdr_tin = 0; L.mm.hdr_bits = 0;
+    L.seq = L.seq0 = seq; L.lw = 0; L.nl = 0; L.wnext = 0; L.wnext2 = 0; L.hist = S.whave; L.nlen = 0; L.ndist = 0;
+    R.phase = S.phase; R.unit = 0; R.stop = EV_NONE; R.hdr_stop = false; R.hdr_tin = 0; R.hdr_bits = 0;
+    if (active && R.phase != PH_HEAD) seek_bit(d.b, S.bit0);
+    for (;;) {
+        int want = 0;
+        if (active) want = run_serial(S, L, R, T, lut, primed);
+        want = (int)lane::Wp<W>::shfl((uint32_t)want, 0);
+        if (want == 0) break;
+        const uint32_t info = lane::Wp<W>::shfl(L.nlen | (L.ndist << 12), 0);
+        int msg = 0;
+        if (want == 2) {
+            for (int i = ln; i < lane::SLOT / 4; i += W) ((uint32_t *)T)[i] = ((const uint32_t *)fixed_tab)[i];
+            lane::Wp<W>::sync();
+        } else {
+            msg = lane::build_tables<W>(T, scr, info & 1023u, info >> 12, S.d64 != 0, ln);
+        }
+        if (active) {
+            if (msg) {
+                d.msg = msg;
+                R.stop = EV_ERR;
+            } else {
+                R.phase = PH_SYM;
+            }
+        }
+        if (lane::Wp<W>::shfl((uint32_t)msg, 0)) break;
+    }
+    if (!active) return;
+    // ---- what the reference leaves on the stream at this stop (write_result, zsb_device.cuh) ----
+    lane::flush_literals(L);
+    zsb_result r;
+    Aux a;
+    L.mm.hdr_stop = R.hdr_stop;
+    L.mm.hdr_tin = R.hdr_tin;
+    L.mm.hdr_bits = R.hdr_bits;
+    write_result(d, L.mm, R.stop, &r, &a);
+    Call &c = S.call;
+    c.stop = R.stop;
+    c.msg = r.msg_id;
+    c.cpos = (uint32_t)r.total_in;
+    c.produced = d.pos;
+    c.data_type = (uint32_t)r.data_type;
+    c.adler = r.check;
+    c.nseq = (uint32_t)(L.seq - L.seq0);
+    c.need_trailer = a.need_trailer;
+    c.trailer_pos = a.trailer_pos;
+    if (R.phase == PH_CHECK || R.phase == PH_LENGTH) {     // resumed inside the trailer
+        c.need_trailer = 1;
+        c.trailer_pos = 0;
+    }
+    // ---- resume point ----
+    S.last = d.last;
+    if (R.stop == EV_STARVE || R.stop == EV_OUTFULL) {
+        uint64_t rb = R.unit;
+        if (R.stop == EV_STARVE && R.phase == PH_STORED) rb = 8ull * in_len;
+        c.resume_byte = (uint32_t)(rb >> 3);
+        S.bit0 = (uint32_t)(rb & 7);
+        S.phase = R.phase;
+        if (c.resume_byte > c.cpos) c.resume_byte = c.cpos;
+    } else if (R.stop == EV_DONE) {
+        c.resume_byte = c.cpos;
+        S.bit0 = 0;
+        S.phase = a.need_trailer || c.need_trailer ? (R.phase == PH_LENGTH ? PH_LENGTH : PH_CHECK) : PH_DONE;
+    } else {
+        c.resume_byte = c.cpos;
+        S.bit0 = 0;
+        S.phase = R.stop == EV_NEEDDICT ? PH_NEEDDICT : PH_BAD;
+    }
+}
+
+}  // namespace zs
+}  // namespace zsb
