@@ -29,6 +29,9 @@ static inline unsigned __ballot_sync(unsigned, bool p) { return p; }
 static inline int __ffs(unsigned x) { return __builtin_ffs((int)x); }
 static inline unsigned __match_any_sync(unsigned, uint32_t) { return 1u; }
 static inline int __popc(unsigned x) { return __builtin_popcount(x); }
+#define ZSB_CP4(sdst, gsrc) (*(sdst) = *(const uint32_t *)(gsrc))
+#define ZSB_CP_COMMIT() ((void)0)
+#define ZSB_CP_WAIT(n) ((void)0)
 #define ZSB_FETCH_ADD(p, v) ((*(p) += (v)) - (v))
 #define ZSB_SMEM_ADD(p, v) (*(p) += (v))
 #include "../../zlib-streams_b200/csrc/zsb_device.cuh"
@@ -83,7 +86,8 @@ extern "C" int emul_decode_lane(const uint8_t *in, size_t in_len, uint8_t *out, 
     lane::Batch B;
     B.members = &m; B.results = res; B.aux = &a; B.order = &order; B.seq_off = &seq_off; B.seq_base = seq;
     B.hist = nullptr; B.n = 1; B.counter = &counter; B.fixed_tab = fixed;
-    lane::warp_lanes<1>(B, T, scr, lut, 0);
+    uint32_t ring[lane::RING_WORDS] = {0, 0, 0, 0};
+    lane::warp_lanes<1>(B, T, scr, ring, lut, 0);
     if (nseq_out) *nseq_out = a.nseq;
     int rc = res->ret;
     if (a.nseq > seq_cap) rc = -1000;               // the host's scratch bound was too small
@@ -101,4 +105,148 @@ extern "C" void emul_finish(const uint8_t *in, size_t in_len, zsb_result *res, c
     if (a.kind == 0) return;
     uint32_t E = (uint32_t)res->total_out;
     zsb::finish_member(*res, a, in, (uint32_t)in_len, E ? check_of_output : a.init_check, E);
+}
+
+// ---------------------------------------------------------------------------------------------------
+// The z_stream surface's device code (zsb_stream.cuh) with a warp of one lane: open/step/close with the
+// signatures of oracle_api.h, so the streaming traces can be compared call by call with the oracle.
+// The host bookkeeping below restates inflate() of zsb_zstream.cuh for a single slice.
+// ---------------------------------------------------------------------------------------------------
+#include <vector>
+#include "../../zlib-streams_b200/csrc/zsb_stream.cuh"
+#include "../../oracle/oracle_api.h"
+
+namespace {
+struct EmulZs {
+    zsb::zs::State S;
+    std::vector<uint8_t> hist, carry;
+    uint32_t carry_len = 0, phase = 0, last_dt = 0;
+    int wrap = 0;
+    uint64_t total_in = 0, total_out = 0;
+    uint32_t adler = 0;
+    int msg = 0, data_type = 0;
+};
+uint32_t emul_crc(uint32_t crc, const uint8_t *p, size_t n) {
+    crc = ~crc;
+    for (size_t i = 0; i < n; i++) {
+        crc ^= p[i];
+        for (int k = 0; k < 8; k++) crc = (crc >> 1) ^ (0xEDB88320u & (0u - (crc & 1u)));
+    }
+    return ~crc;
+}
+uint32_t emul_adler(uint32_t ad, const uint8_t *p, size_t n) {
+    uint32_t a = ad & 0xffff, b = ad >> 16;
+    for (size_t i = 0; i < n; i++) {
+        a = (a + p[i]) % 65521u;
+        b = (b + a) % 65521u;
+    }
+    return (b << 16) | a;
+}
+}  // namespace
+
+extern "C" void *emulzs_open(int windowBits, int *init_ret) {
+    int wrap, d64 = 0, wb = windowBits, ret = 0;
+    if (wb < 0) {
+        if (wb < -16) ret = -2;
+        wrap = 0;
+        d64 = wb == -16;
+        wb = -wb;
+    } else {
+        wrap = (wb >> 4) + 5;
+        if (wb < 48) wb &= 15;
+    }
+    if (!ret && wb && (wb < 8 || wb > (d64 ? 16 : 15))) ret = -2;
+    if (init_ret) *init_ret = ret;
+    if (ret) return nullptr;
+    EmulZs *z = new EmulZs();
+    memset(&z->S, 0, sizeof z->S);
+    z->S.phase = zsb::zs::PH_HEAD;
+    z->S.d64 = (uint32_t)d64;
+    z->S.wbits_arg = windowBits;
+    z->S.wbits = (uint32_t)wb;
+    z->hist.assign(zsb::zs::HIST, 0);
+    z->carry.assign(256 << 10, 0);
+    z->wrap = wrap;
+    if (wrap) z->adler = (uint32_t)(wrap & 1);
+    return z;
+}
+
+extern "C" void emulzs_close(void *h) { delete (EmulZs *)h; }
+
+extern "C" int emulzs_step(void *hh, const uint8_t *in, size_t in_len_new, uint8_t *out, size_t out_cap, int flush,
+                           size_t *consumed, size_t *produced, orc_result *r) {
+    using namespace zsb;
+    EmulZs *z = (EmulZs *)hh;
+    static uint8_t fixed[lane::SLOT];
+    static uint32_t lut[LUT_WORDS];
+    static bool init = false;
+    alignas(16) static uint8_t scr[lane::WSCR];
+    if (!init) {
+        init_lut(lut, 0, 1);
+        alignas(16) uint8_t T0[lane::SLOT];
+        for (int i = 0; i < 288; i++) T0[lane::H_LENS + i] = i < 144 ? 8 : i < 256 ? 9 : i < 280 ? 7 : 8;
+        for (int i = 0; i < 32; i++) T0[lane::H_LENS + 288 + i] = 5;
+        lane::build_tables<1>(T0, scr, 288, 32, false, 0);
+        memcpy(fixed, T0, sizeof fixed);
+        init = true;
+    }
+    size_t used = 0, made = 0;
+    int ret = 0;
+    auto fill = [&]() {
+        r->ret = ret; r->msg_id = z->msg; r->total_in = z->total_in; r->total_out = z->total_out;
+        r->adler = z->adler; r->data_type = z->data_type;
+        if (consumed) *consumed = used;
+        if (produced) *produced = made;
+        return ret;
+    };
+    if (z->phase == zs::PH_NEEDDICT) { ret = 2; return fill(); }
+    if (z->phase == zs::PH_DONE || z->phase == zs::PH_BAD) {
+        z->data_type = (int)z->last_dt;
+        ret = z->phase == zs::PH_DONE ? 1 : -3;
+        return fill();
+    }
+    const uint32_t len = z->carry_len + (uint32_t)in_len_new;
+    std::vector<uint32_t> ibuf(len / 4 + 4);
+    uint8_t *ib = (uint8_t *)ibuf.data();
+    memcpy(ib, z->carry.data(), z->carry_len);
+    if (in_len_new) memcpy(ib + z->carry_len, in, in_len_new);
+    std::vector<uint32_t> wbuf((zs::HIST + out_cap) / 4 + 4);
+    uint8_t *w = (uint8_t *)wbuf.data();
+    memcpy(w, z->hist.data(), zs::HIST);
+    const uint64_t a = out_cap / 3 + (uint64_t)len / 2 + 6, b8 = 8ull * len + 4, c2 = (uint64_t)out_cap + 2;
+    const uint64_t bound = a < b8 ? (a < c2 ? a : c2) : (b8 < c2 ? b8 : c2);
+    std::vector<lane::seq_t> seq(bound + 2);
+    uint32_t ring[lane::RING_WORDS] = {0, 0, 0, 0};
+    zs::stream_decode<1>(z->S, ib, len, (uint32_t)out_cap, seq.data(), fixed, scr, ring, lut, 0);
+    if (z->S.call.nseq > bound) abort();
+    if (z->S.call.nseq) lz::resolve_member<1>(w + zs::HIST, ib, seq.data(), z->S.call.nseq, 0);
+    const uint32_t prod = z->S.call.produced;
+    uint32_t check = z->S.check;
+    if (z->S.kind && prod) check = z->S.kind == 2 ? emul_crc(check, w + zs::HIST, prod) : emul_adler(check, w + zs::HIST, prod);
+    zs::finish_call(z->S, ib, len, check, flush == 4);
+    const zs::Call c = z->S.call;
+    memcpy(z->hist.data(), w + prod, zs::HIST);
+    if (prod) memcpy(out, w + zs::HIST, prod);
+    uint32_t cpos = c.cpos;
+    if (c.stop == EV_NEEDDICT) cpos = len < 6 ? len : 6;
+    used = cpos > z->carry_len ? cpos - z->carry_len : 0;
+    made = prod;
+    const uint32_t ncarry = c.cpos > c.resume_byte ? c.cpos - c.resume_byte : 0;
+    memmove(z->carry.data(), ib + c.resume_byte, ncarry);
+    z->carry_len = ncarry;
+    if (c.stop == EV_NEEDDICT) {
+        z->adler = c.adler;
+        z->phase = zs::PH_NEEDDICT;
+        ret = 2;
+        return fill();
+    }
+    z->total_in += used;
+    z->total_out += made;
+    if (z->wrap) z->adler = c.adler;
+    z->data_type = (int)c.data_type;
+    if (c.stop == EV_DONE) { ret = 1; z->phase = zs::PH_DONE; }
+    else if (c.stop == EV_ERR) { ret = -3; z->msg = c.msg; z->phase = zs::PH_BAD; }
+    z->last_dt = c.data_type & 0x7fu;
+    if (((used == 0 && made == 0) || flush == 4) && ret == 0) ret = -5;
+    return fill();
 }

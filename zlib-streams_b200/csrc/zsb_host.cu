@@ -130,6 +130,13 @@ static inline uint64_t seq_bound(const zsb_member &m) {
 
 template <typename T> static int grow(zsb_ctx *ctx, T *&p, size_t &cap, size_t need);
 
+static size_t zsb_seq_bound_sizes(size_t in_len, size_t out_cap) {
+    zsb_member m;
+    m.in_len = in_len;
+    m.out_cap = out_cap;
+    return (size_t)seq_bound(m);
+}
+
 static int run_group(zsb_ctx *ctx, zsb_dev &dv, size_t n, const zsb_member *dm, zsb_result *dr,
                      const uint32_t *dorder, cudaStream_t st) {
     CK(ctx, cudaMemsetAsync(dv.counters, 0, 4 * sizeof(uint32_t), st));
@@ -566,3 +573,6 @@ extern "C" int zsb_inflate_batch(zsb_ctx *ctx, size_t n, const zsb_member *m, zs
     cudaSetDevice(cur);
     return rc;
 }
+
+// the z_stream surface (inflateInit2_ / inflate / inflateEnd): same translation unit, it shares the kernels above
+#include "zsb_zstream.cuh"

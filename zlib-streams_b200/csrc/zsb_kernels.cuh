@@ -239,7 +239,8 @@ __global__ void __launch_bounds__(lane::WARPS * 32, 1) k_lane(lane::Batch B) {
     const int ln = threadIdx.x & 31, warp = threadIdx.x >> 5;
     uint8_t *scr = smem + LUT_BYTES + (size_t)warp * lane::WSCR;
     uint8_t *slots = smem + LUT_BYTES + (size_t)lane::WARPS * lane::WSCR + (size_t)warp * 32 * lane::SLOT;
-    lane::warp_lanes<32>(B, slots, scr, lut, ln);
+    uint32_t *rings = (uint32_t *)(smem + LUT_BYTES + (size_t)lane::WARPS * lane::WSCR + (size_t)lane::WARPS * 32 * lane::SLOT) + warp * 32 * lane::RING_WORDS;
+    lane::warp_lanes<32>(B, slots, scr, rings, lut, ln);
 }
 
 constexpr int LZ_THREADS = 256;

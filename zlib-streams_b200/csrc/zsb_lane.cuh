@@ -35,7 +35,7 @@ constexpr int S_LBASE = 912;              // u16[8]    index bias into S_LS for 
 constexpr int S_LT256 = 928;              // u16[8]    first S_LS index holding a symbol >= 256, per length 9..15
 constexpr int S_DLIM = 944;               // u16[9]    distance limits for lengths 7..15
 constexpr int S_DBASE = 962;              // u8[9]     index bias into S_DS for lengths 7..15
-constexpr int SLOT = 976;                 // bytes per member
+constexpr int SLOT = 972;                 // bytes per member
 // while a block header is read the slot holds (the tables are built over it afterwards):
 constexpr int H_LENS = 0;                 // u8[320]   code lengths of the litlen + distance codes
 constexpr int H_CL = 512;                 // u8[128]   code-length code root (7 bits): sym<<3 | len
@@ -50,7 +50,7 @@ constexpr int W_DL = 768;                 // u8[32]    distance code lengths
 constexpr int WSCR = 1024;
 
 constexpr int WARPS = 7;                  // warps per CTA, one CTA per SM: 224 members in flight per SM
-constexpr size_t SMEM = LUT_BYTES + (size_t)WARPS * WSCR + (size_t)WARPS * 32 * SLOT;
+constexpr size_t SMEM = LUT_BYTES + (size_t)WARPS * WSCR + (size_t)WARPS * 32 * SLOT + (size_t)WARPS * 32 * 16;
 
 // ---- LZ sequence (8 bytes): lo = lit0 | lit1<<8 | lit2<<16 | flags, hi = payload ----
 constexpr uint32_t Q_NLIT_SHIFT = 24;     // bits 24,25: number of literals (0..3)
@@ -84,8 +84,8 @@ template <> struct Wp<1> {
 struct Lane {
     Dec d;               // bit input, output accounting, stop bookkeeping (zsb_device.cuh)
     Mem mm;
-    uint32_t wnext;      // the input word at d.b.next, loaded ahead of its use
-    uint32_t wnext2;     // the word after it: two refills in a row never wait for memory
+    uint32_t *ring;      // 4 words of shared memory: the input words at d.b.next, +4, +8 arrive here
+                         // through cp.async, so a refill never waits on a load scoreboard
     seq_t *seq;          // where this member's next sequence goes
     seq_t *seq0;         // start of its sequence array
     uint32_t lw, nl;     // literals waiting for their sequence
@@ -131,14 +131,28 @@ ZSB_DEV void push_raw(Lane &L, uint32_t in_off, uint32_t n) {
     L.d.pos += n;
 }
 
-ZSB_DEV uint32_t load_ahead(const BitIn &b, uint32_t off) {
-    return off < b.len ? __ldg((const uint32_t *)(b.p + off)) : 0u;
+// ---- asynchronous input prefetch: global -> the lane's ring in shared memory ----
+#ifndef ZSB_CP4
+#define ZSB_CP4(sdst, gsrc)                                                                             \
+    asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"((unsigned)__cvta_generic_to_shared(sdst)), "l"(gsrc))
+#define ZSB_CP_COMMIT() asm volatile("cp.async.commit_group;")
+#define ZSB_CP_WAIT(n) asm volatile("cp.async.wait_group %0;" ::"n"(n) : "memory")
+#endif
+constexpr int RING_WORDS = 4;
+
+// start the copy of the input word at byte offset `off` (one group per word, empty past the end)
+ZSB_DEV void fetch_word(const Lane &L, uint32_t off) {
+    const BitIn &b = L.d.b;
+    if (off < b.len) ZSB_CP4(&L.ring[(off >> 2) & 3u], b.p + off);
+    ZSB_CP_COMMIT();
 }
 ZSB_DEV void prime(Lane &L) {
     const BitIn &b = L.d.b;
-    const bool aligned = (((uintptr_t)(b.p + b.next)) & 3) == 0;
-    L.wnext = aligned ? load_ahead(b, b.next) : 0u;
-    L.wnext2 = aligned ? load_ahead(b, b.next + 4) : 0u;
+    ZSB_CP_WAIT(0);
+    if ((((uintptr_t)(b.p + b.next)) & 3) != 0) return;       // only at the very end of a member
+    fetch_word(L, b.next);
+    fetch_word(L, b.next + 4);
+    fetch_word(L, b.next + 8);
 }
 
 // ------------------------------------------------------------------------------------------------
@@ -276,11 +290,11 @@ ZSB_DEV int accept_match(Lane &L) {
 // ------------------------------------------------------------------------------------------------
 ZSB_DEV void refill(Lane &L) {
     BitIn &b = L.d.b;
-    b.hold |= (uint64_t)L.wnext << b.nbits;
+    ZSB_CP_WAIT(2);                                            // all but the two youngest words have arrived
+    b.hold |= (uint64_t)L.ring[(b.next >> 2) & 3u] << b.nbits;
     b.nbits += 32;
+    fetch_word(L, b.next + 12);
     b.next += 4;
-    L.wnext = L.wnext2;
-    L.wnext2 = load_ahead(b, b.next + 4);
 }
 
 // Returns true when the symbol was a literal or a whole match that fits and has been committed.
@@ -317,13 +331,12 @@ ZSB_DEV bool fast_symbol(Lane &L, const uint8_t *T, const uint32_t *lut) {
     const uint32_t mlen = (lw & 0xffffu) + ((w >> nb) & ((1u << xb) - 1u));
     const uint32_t used1 = nb + (islen ? xb : 0u);
     uint64_t h2 = b.hold >> used1;
-    uint32_t n2 = b.nbits - used1, next2 = b.next, wn2 = L.wnext, wn3 = L.wnext2;
-    if (islen && n2 < 32) {
-        h2 |= (uint64_t)wn2 << n2;
+    uint32_t n2 = b.nbits - used1;
+    const bool again = islen && n2 < 32;          // second refill: its prefetch is only issued on commit
+    if (again) {
+        ZSB_CP_WAIT(2);
+        h2 |= (uint64_t)L.ring[(b.next >> 2) & 3u] << n2;
         n2 += 32;
-        next2 += 4;
-        wn2 = wn3;
-        wn3 = load_ahead(b, next2 + 4);
     }
     const uint32_t w2 = (uint32_t)h2;
     uint32_t nb2 = 0, s = 0;
@@ -339,9 +352,10 @@ ZSB_DEV bool fast_symbol(Lane &L, const uint8_t *T, const uint32_t *lut) {
     // ---- commit ----
     b.hold = h2 >> used2;
     b.nbits = n2 - used2;
-    b.next = next2;
-    L.wnext = wn2;
-    L.wnext2 = wn3;
+    if (again) {
+        fetch_word(L, b.next + 12);
+        b.next += 4;
+    }
     d.pos += n;
     const bool put = islen || L.nl == 3;
     if (put) {
@@ -701,7 +715,7 @@ ZSB_DEV int start_member(Lane &L, uint32_t slot, const Batch &B) {
     d.d64 = m.window_bits == -16;
     d.last = 0; d.at_type = 0; d.msg = 0; d.extent = 0; d.mlen = 0; d.mdist = 0; d.mtrunc = 0;
     L.seq = L.seq0 = B.seq_base + B.seq_off[slot];
-    L.lw = 0; L.nl = 0; L.wnext = 0; L.wnext2 = 0;
+    L.lw = 0; L.nl = 0;
     L.hist = B.hist ? B.hist[idx] : 0u;
     int ev = EV_NONE;
     if (!wbits_valid(m.window_bits) || (in == nullptr && m.in_len != 0) || (m.out == nullptr && m.out_cap != 0)) {
@@ -798,10 +812,11 @@ ZSB_DEV int lane_block(Lane &L, uint8_t *T, const uint32_t *lut, const Batch &B)
 }
 
 template <int W>
-__device__ __forceinline__ void warp_lanes(const Batch &B, uint8_t *slots, uint8_t *scr, const uint32_t *lut, int lane) {
+__device__ __forceinline__ void warp_lanes(const Batch &B, uint8_t *slots, uint8_t *scr, uint32_t *rings, const uint32_t *lut, int lane) {
     Lane L;
+    L.ring = rings + lane * RING_WORDS;
     L.d.pos = 0; L.d.cap = 0; L.d.b.p = nullptr; L.d.b.len = 0; L.d.b.next = 0; L.d.b.nbits = 0; L.d.b.hold = 0;
-    L.d.d64 = 0; L.d.msg = 0; L.nl = 0; L.lw = 0; L.seq = L.seq0 = nullptr; L.wnext = 0; L.wnext2 = 0; L.nlen = 0; L.ndist = 0;
+    L.d.d64 = 0; L.d.msg = 0; L.nl = 0; L.lw = 0; L.seq = L.seq0 = nullptr; L.nlen = 0; L.ndist = 0;
     L.mm.idx = 0;
     uint8_t *T = slots + (size_t)lane * SLOT;
     int st = LS_FETCH;

@@ -59,6 +59,7 @@ struct Run {               // lane 0's bookkeeping during one call
     uint32_t phase;
     uint64_t unit;         // bit position where the current unit started
     int stop;
+    uint32_t last0;        // BFINAL as it was when the current block header unit started
     bool hdr_stop;
     uint32_t hdr_tin, hdr_bits;
 };
@@ -105,6 +106,7 @@ ZSB_DEV int run_serial(State &S, Lane &L, Run &R, uint8_t *T, const uint32_t *lu
         }
         case PH_BLOCK: {
             R.unit = bitpos(b);
+            R.last0 = d.last;
             if (d.last) {
                 bi_drop(b, b.nbits & 7);
                 R.unit = bitpos(b);
@@ -244,7 +246,7 @@ ZSB_DEV int run_serial(State &S, Lane &L, Run &R, uint8_t *T, const uint32_t *lu
 // One call's decode: all W lanes enter, lane 0 owns the stream.
 template <int W>
 ZSB_DEV void stream_decode(State &S, const uint8_t *in, uint32_t in_len, uint32_t out_cap, seq_t *seq,
-                           const uint8_t *fixed_tab, uint8_t *scr, const uint32_t *lut, int ln) {
+                           const uint8_t *fixed_tab, uint8_t *scr, uint32_t *ring, const uint32_t *lut, int ln) {
     Lane L;
     Run R;
     Dec &d = L.d;
@@ -255,8 +257,8 @@ ZSB_DEV void stream_decode(State &S, const uint8_t *in, uint32_t in_len, uint32_
     d.out = nullptr; d.pos = 0; d.cap = out_cap; d.d64 = S.d64; d.last = S.last; d.at_type = 0; d.msg = 0;
     d.extent = 0; d.mlen = 0; d.mdist = 0; d.mtrunc = 0;
     L.mm.idx = 0; L.mm.kind = S.kind; L.mm.adler0 = S.check; L.mm.hdr_stop = false; L.mm.hdr_tin = 0; L.mm.hdr_bits = 0;
-    L.seq = L.seq0 = seq; L.lw = 0; L.nl = 0; L.wnext = 0; L.wnext2 = 0; L.hist = S.whave; L.nlen = 0; L.ndist = 0;
-    R.phase = S.phase; R.unit = 0; R.stop = EV_NONE; R.hdr_stop = false; R.hdr_tin = 0; R.hdr_bits = 0;
+    L.seq = L.seq0 = seq; L.lw = 0; L.nl = 0; L.ring = ring; L.hist = S.whave; L.nlen = 0; L.ndist = 0;
+    R.phase = S.phase; R.unit = 0; R.stop = EV_NONE; R.last0 = S.last; R.hdr_stop = false; R.hdr_tin = 0; R.hdr_bits = 0;
     if (active && R.phase != PH_HEAD) seek_bit(d.b, S.bit0);
     for (;;) {
         int want = 0;
@@ -306,6 +308,7 @@ ZSB_DEV void stream_decode(State &S, const uint8_t *in, uint32_t in_len, uint32_
     }
     // ---- resume point ----
     S.last = d.last;
+    if (R.stop == EV_STARVE && R.phase == PH_BLOCK) S.last = R.last0;   // the header is read again
     if (R.stop == EV_STARVE || R.stop == EV_OUTFULL) {
         uint64_t rb = R.unit;
         if (R.stop == EV_STARVE && R.phase == PH_STORED) rb = 8ull * in_len;
@@ -322,6 +325,68 @@ ZSB_DEV void stream_decode(State &S, const uint8_t *in, uint32_t in_len, uint32_
         S.bit0 = 0;
         S.phase = R.stop == EV_NEEDDICT ? PH_NEEDDICT : PH_BAD;
     }
+}
+
+
+// What k_zs_finish's first thread does once the check value of this call's output is known: running
+// check and length, the trailer (reference src/inflate.c:1194-1232), the window accounting
+// (src/inflate.c:1255-1260, 375-419).  `check` = S.check continued over the new output.
+ZSB_DEV void finish_call(State &S, const uint8_t *in, uint32_t in_len, uint32_t check, bool finish) {
+    Call c = S.call;
+    const uint32_t produced = c.produced, kind = S.kind;
+    S.total_lo += produced;
+    if (kind != 0) {                  // kind is only set once the wrapper header has been read
+        S.check = check;
+        c.adler = check;
+    }
+    if (c.need_trailer && c.stop == EV_DONE) {
+        uint32_t pos = c.trailer_pos, phase = S.phase;
+        bool done = false;
+        if (phase == PH_CHECK) {
+            if (in_len - pos < 4) {
+                c.stop = EV_STARVE; c.cpos = in_len; c.resume_byte = pos; c.data_type = 8 * (in_len - pos) + 64;
+                done = true;
+            } else {
+                uint32_t v = le32(in + pos);
+                if (kind == 1) v = (v >> 24) | ((v >> 8) & 0xff00u) | ((v & 0xff00u) << 8) | (v << 24);
+                pos += 4;
+                if (v != check) {
+                    c.stop = EV_ERR; c.msg = M_DATACHECK; c.cpos = pos; c.resume_byte = pos; c.data_type = 32 + 64;
+                    S.phase = PH_BAD;
+                    done = true;
+                } else {
+                    phase = PH_LENGTH;
+                }
+            }
+        }
+        if (!done && kind == 2) {
+            if (in_len - pos < 4) {
+                c.stop = EV_STARVE; c.cpos = in_len; c.resume_byte = pos; c.data_type = 8 * (in_len - pos) + 64;
+                S.phase = PH_LENGTH;
+                done = true;
+            } else {
+                const uint32_t isz = le32(in + pos);
+                pos += 4;
+                if (isz != S.total_lo) {
+                    c.stop = EV_ERR; c.msg = M_LENCHECK; c.cpos = pos; c.resume_byte = pos; c.data_type = 32 + 64;
+                    S.phase = PH_BAD;
+                    done = true;
+                }
+            }
+        }
+        if (!done) {
+            c.stop = EV_DONE; c.cpos = pos; c.resume_byte = pos; c.data_type = 64;
+            S.phase = PH_DONE;
+        }
+    }
+    // history the reference would keep (src/inflate.c:1255-1260, 375-419)
+    const uint32_t ph = S.phase;
+    if (S.wsize || (produced && ph < PH_BAD && (ph < PH_CHECK || !finish))) {
+        S.wsize = 1u << S.wbits;
+        const uint64_t h = (uint64_t)S.whave + produced;
+        S.whave = h > S.wsize ? S.wsize : (uint32_t)h;
+    }
+    S.call = c;
 }
 
 }  // namespace zs

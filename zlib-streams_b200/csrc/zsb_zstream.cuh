@@ -17,9 +17,10 @@ __global__ void __launch_bounds__(32) k_zs_decode(zs::State *S, const uint8_t *i
                                                   lane::seq_t *seq, const uint8_t *fixed_tab) {
     __shared__ uint32_t lut[LUT_WORDS];
     __shared__ __align__(16) uint8_t scr[lane::WSCR];
+    __shared__ uint32_t ring[32 * lane::RING_WORDS];
     init_lut(lut, threadIdx.x, 32);
     __syncwarp();
-    zs::stream_decode<32>(*S, in, in_len, out_cap, seq, fixed_tab, scr, lut, threadIdx.x);
+    zs::stream_decode<32>(*S, in, in_len, out_cap, seq, fixed_tab, scr, ring + threadIdx.x * lane::RING_WORDS, lut, threadIdx.x);
 }
 
 __global__ void __launch_bounds__(32) k_zs_lz(const zs::State *S, uint8_t *out, const uint8_t *in, const lane::seq_t *seq) {
@@ -40,60 +41,8 @@ __global__ void __launch_bounds__(CHK_THREADS) k_zs_finish(zs::State *S, uint8_t
     uint32_t check = S->check;
     if (kind != 0 && produced) check = cta_check(sh, kind, w + zs::HIST, produced, check);
     if (tid == 0) {
-        zs::Call c = S->call;
-        S->total_lo += produced;
-        if (kind != 0) {                  // kind is only set once the wrapper header has been read
-            S->check = check;
-            c.adler = check;
-        }
-        if (c.need_trailer && c.stop == EV_DONE) {
-            uint32_t pos = c.trailer_pos, phase = S->phase;
-            bool done = false;
-            if (phase == zs::PH_CHECK) {
-                if (in_len - pos < 4) {
-                    c.stop = EV_STARVE; c.cpos = in_len; c.resume_byte = pos; c.data_type = 8 * (in_len - pos) + 64;
-                    done = true;
-                } else {
-                    uint32_t v = le32(in + pos);
-                    if (kind == 1) v = (v >> 24) | ((v >> 8) & 0xff00u) | ((v & 0xff00u) << 8) | (v << 24);
-                    pos += 4;
-                    if (v != check) {
-                        c.stop = EV_ERR; c.msg = M_DATACHECK; c.cpos = pos; c.resume_byte = pos; c.data_type = 32 + 64;
-                        S->phase = zs::PH_BAD;
-                        done = true;
-                    } else {
-                        phase = zs::PH_LENGTH;
-                    }
-                }
-            }
-            if (!done && kind == 2) {
-                if (in_len - pos < 4) {
-                    c.stop = EV_STARVE; c.cpos = in_len; c.resume_byte = pos; c.data_type = 8 * (in_len - pos) + 64;
-                    S->phase = zs::PH_LENGTH;
-                    done = true;
-                } else {
-                    const uint32_t isz = le32(in + pos);
-                    pos += 4;
-                    if (isz != S->total_lo) {
-                        c.stop = EV_ERR; c.msg = M_LENCHECK; c.cpos = pos; c.resume_byte = pos; c.data_type = 32 + 64;
-                        S->phase = zs::PH_BAD;
-                        done = true;
-                    }
-                }
-            }
-            if (!done) {
-                c.stop = EV_DONE; c.cpos = pos; c.resume_byte = pos; c.data_type = 64;
-                S->phase = zs::PH_DONE;
-            }
-        }
-        // history the reference would keep (src/inflate.c:1255-1260, 375-419)
-        const uint32_t ph = S->phase;
-        if (S->wsize || (produced && ph < zs::PH_BAD && (ph < zs::PH_CHECK || !finish))) {
-            S->wsize = 1u << S->wbits;
-            const uint64_t h = (uint64_t)S->whave + produced;
-            S->whave = h > S->wsize ? S->wsize : (uint32_t)h;
-        }
-        S->call = c;
+        zs::finish_call(*S, in, in_len, check, finish != 0);
+        const zs::Call &c = S->call;
         s_resume = c.resume_byte;
         s_cpos = c.cpos;
     }
@@ -314,3 +263,95 @@ ZSB_API int inflateEnd(z_streamp strm) {
 }
 
 }  // extern "C"
+
+// inflate(): reference src/inflate.c:597-1275.  Z_BLOCK / Z_TREES are accepted and treated as
+// Z_NO_FLUSH (they only add early returns the reference's callers never ask for).
+extern "C" ZSB_API int inflate(z_streamp strm, int flush) {
+    using namespace zsb;
+    ZsHandle *h = zs_handle(strm);
+    if (!h || strm->next_out == Z_NULL || (strm->next_in == Z_NULL && strm->avail_in != 0)) return Z_STREAM_ERROR;
+    ZStream *z = h->zs;
+    if (z->phase == zs::PH_NEEDDICT) return Z_NEED_DICT;        // src/inflate.c:824-827: no bookkeeping
+    if (z->phase == zs::PH_DONE || z->phase == zs::PH_BAD) {    // sticky states, src/inflate.c:1233-1240
+        strm->data_type = (int)z->last_dt;
+        return z->phase == zs::PH_DONE ? Z_STREAM_END : Z_DATA_ERROR;
+    }
+    std::lock_guard<std::mutex> lk(g_zs.mu);
+    int cur = 0;
+    cudaGetDevice(&cur);
+    const int dev = g_zs.ctx->devs[0].device;
+    if (cur != dev) cudaSetDevice(dev);
+    cudaStream_t st = g_zs.st;
+    const uInt in0 = strm->avail_in, out0 = strm->avail_out;
+    int ret = Z_OK;
+    zs::Call c;
+    memset(&c, 0, sizeof c);
+    bool cuda_ok = true;
+    for (;;) {
+        const uint32_t ni = strm->avail_in < ZS_IN_SLICE ? strm->avail_in : ZS_IN_SLICE;
+        const uint32_t no = strm->avail_out < ZS_OUT_SLICE ? strm->avail_out : ZS_OUT_SLICE;
+        if (z->carry_len + ni > ZS_IN_SLICE + ZS_CARRY_CAP) {
+            ret = Z_MEM_ERROR;                                  // a wrapper header longer than the carry buffer
+            break;
+        }
+        const uint32_t in_len = z->carry_len + ni;
+        cuda_ok = cuda_ok && (z->carry_len == 0 ||
+                  cudaMemcpyAsync(g_zs.d_in, z->d_carry, z->carry_len, cudaMemcpyDeviceToDevice, st) == cudaSuccess);
+        cuda_ok = cuda_ok && (ni == 0 ||
+                  cudaMemcpyAsync(g_zs.d_in + z->carry_len, strm->next_in, ni, cudaMemcpyHostToDevice, st) == cudaSuccess);
+        cuda_ok = cuda_ok && cudaMemcpyAsync(g_zs.d_w, z->d_hist, zs::HIST, cudaMemcpyDeviceToDevice, st) == cudaSuccess;
+        if (!cuda_ok) break;
+        k_zs_decode<<<1, 32, 0, st>>>(z->d_state, g_zs.d_in, in_len, no, g_zs.d_seq, g_zs.ctx->devs[0].fixed_lane);
+        k_zs_lz<<<1, 32, 0, st>>>(z->d_state, g_zs.d_w + zs::HIST, g_zs.d_in, g_zs.d_seq);
+        k_zs_finish<<<1, CHK_THREADS, 0, st>>>(z->d_state, g_zs.d_in, in_len, g_zs.d_w, z->d_hist, z->d_carry,
+                                               flush == Z_FINISH);
+        cuda_ok = cudaGetLastError() == cudaSuccess &&
+                  cudaMemcpyAsync(g_zs.h_call, &z->d_state->call, sizeof(zs::Call), cudaMemcpyDeviceToHost, st) == cudaSuccess &&
+                  cudaStreamSynchronize(st) == cudaSuccess;
+        if (!cuda_ok) break;
+        c = *g_zs.h_call;
+        if (c.produced) {
+            cuda_ok = cudaMemcpyAsync(strm->next_out, g_zs.d_w + zs::HIST, c.produced, cudaMemcpyDeviceToHost, st) == cudaSuccess &&
+                      cudaStreamSynchronize(st) == cudaSuccess;
+            if (!cuda_ok) break;
+        }
+        uint32_t cpos = c.cpos;
+        if (c.stop == EV_NEEDDICT) cpos = in_len < 6 ? in_len : 6;   // header + dictionary id were read
+        const uint32_t used = cpos > z->carry_len ? cpos - z->carry_len : 0;
+        strm->next_in += used;
+        strm->avail_in -= used;
+        strm->next_out += c.produced;
+        strm->avail_out -= c.produced;
+        z->carry_len = c.cpos > c.resume_byte ? c.cpos - c.resume_byte : 0;
+        if (c.stop == EV_STARVE && strm->avail_in > 0) continue;
+        if (c.stop == EV_OUTFULL && strm->avail_out > 0) continue;
+        break;
+    }
+    if (cur != dev) cudaSetDevice(cur);
+    if (!cuda_ok) {
+        cudaGetLastError();
+        return Z_MEM_ERROR;
+    }
+    if (ret == Z_MEM_ERROR) return ret;
+    const uInt in_used = in0 - strm->avail_in, out_used = out0 - strm->avail_out;
+    if (c.stop == EV_NEEDDICT) {                                // returns before the exit bookkeeping
+        strm->adler = c.adler;
+        z->phase = zs::PH_NEEDDICT;
+        return Z_NEED_DICT;
+    }
+    strm->total_in += in_used;
+    strm->total_out += out_used;
+    if (z->wrap) strm->adler = c.adler;
+    strm->data_type = (int)c.data_type;
+    if (c.stop == EV_DONE) {
+        ret = Z_STREAM_END;
+        z->phase = zs::PH_DONE;
+    } else if (c.stop == EV_ERR || c.stop == EV_INITERR) {
+        ret = Z_DATA_ERROR;
+        strm->msg = (char *)zsb_message(c.msg);
+        z->phase = zs::PH_BAD;
+    }
+    z->last_dt = c.data_type & 0x7fu;
+    if (((in_used == 0 && out_used == 0) || flush == Z_FINISH) && ret == Z_OK) ret = Z_BUF_ERROR;
+    return ret;
+}
