@@ -1,5 +1,6 @@
 """GPU tier: the CUDA path through the C ABI (libzsb.so) against the oracle, bit for bit: output bytes,
 ret, msg, total_in, total_out, check (strm->adler) and data_type.  Every group width is exercised."""
+import ctypes
 import hashlib
 
 import pytest
@@ -143,3 +144,46 @@ def test_lane_path_slices(eng):
 def zsblib_gen():
     import gen
     return gen
+
+
+# ---- the z_stream surface (inflateInit2_ / inflate / inflateEnd of libzsb.so) ----
+def zs_compare(api, name, data, wb, chunks, ocap):
+    ta, oa = CHK.stream(data, wb, chunks, ocap, True, max_calls=200000)
+    tb, ob = api.stream(data, wb, chunks, ocap, True, max_calls=200000)
+    if ta != tb:
+        k = next((i for i, (x, y) in enumerate(zip(ta, tb)) if x != y), min(len(ta), len(tb)))
+        raise AssertionError((name, wb, chunks, ocap, "call", k, ta[max(k - 1, 0):k + 1], tb[max(k - 1, 0):k + 1]))
+    assert oa == ob, (name, "output differs")
+
+
+def test_zstream_wasm_pattern():
+    """32 KiB in / 64 KiB out, Z_NO_FLUSH then Z_FINISH: what src/wasm/api/zlib-streams.js:73-138 does."""
+    api = zsblib.ZStreamApi()
+    items = [(n, d, -16) for n, d, m in cases.golden_fixtures()]
+    items += [(n, d, w) for n, d, w, p in cases.valid_streams()[::7]]
+    items += [(n, d, w) for n, d, w, c in cases.damaged_streams(60)[:60]]
+    for name, data, wb in items:
+        zs_compare(api, name, data, wb, [32768], 65536)
+
+
+def test_zstream_random_chunkings():
+    import random
+    api = zsblib.ZStreamApi()
+    rnd = random.Random(5)
+    pool = [(n, d, w) for n, d, w, p in cases.valid_streams()[3::11]] + \
+           [(n, d, w) for n, d, w, c in cases.damaged_streams(40)[:40:2]]
+    for name, data, wb in pool:
+        if len(data) > 30000:
+            continue
+        chunks = [rnd.choice([1, 3, 64, 1000, 32768]) for _ in range(4)]
+        zs_compare(api, name, data, wb, chunks, rnd.choice([5, 300, 65536]))
+
+
+def test_zstream_init_codes():
+    api = zsblib.ZStreamApi()
+    for wb in (-17, -16, -15, -8, -7, 0, 7, 8, 15, 16, 23, 24, 31, 47, 48, 63):
+        assert api.init_ret(wb) == CHK.init_ret(wb), wb
+    s = zsblib.ZStreamStruct()
+    assert api.lib.inflateInit2_(ctypes.byref(s), 15, b"2.0", ctypes.sizeof(s)) == -6      # Z_VERSION_ERROR
+    assert api.lib.inflateInit2_(ctypes.byref(s), 15, b"1.3", 100) == -6
+    assert api.lib.inflateEnd(ctypes.byref(s)) == -2                                     # never initialised

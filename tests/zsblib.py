@@ -182,3 +182,69 @@ def emul():
     if _emul is None:
         _emul = Emul()
     return _emul
+
+
+# ---- the z_stream surface of libzsb.so (inflateInit2_ / inflate / inflateEnd), through ctypes ----
+class ZStreamStruct(ctypes.Structure):
+    _fields_ = [("next_in", ctypes.c_void_p), ("avail_in", ctypes.c_uint), ("total_in", ctypes.c_ulong),
+                ("next_out", ctypes.c_void_p), ("avail_out", ctypes.c_uint), ("total_out", ctypes.c_ulong),
+                ("msg", ctypes.c_char_p), ("state", ctypes.c_void_p), ("zalloc", ctypes.c_void_p),
+                ("zfree", ctypes.c_void_p), ("opaque", ctypes.c_void_p), ("data_type", ctypes.c_int),
+                ("adler", ctypes.c_ulong), ("reserved", ctypes.c_ulong)]
+
+
+class ZStreamApi:
+    """Drives libzsb.so's zlib entry points the way the reference's callers do
+    (src/wasm/wasm_stream_common.c:37-63, test/payload_decompress.c:124-192)."""
+
+    def __init__(self):
+        self.lib = load_product()
+        self.lib.inflateInit2_.argtypes = [ctypes.c_void_p, ctypes.c_int, ctypes.c_char_p, ctypes.c_int]
+        self.lib.inflate.argtypes = [ctypes.c_void_p, ctypes.c_int]
+        self.lib.inflateEnd.argtypes = [ctypes.c_void_p]
+        self.lib.inflateReset.argtypes = [ctypes.c_void_p]
+        self.msgs = {self.lib.zsb_message(i): i for i in range(1, 19)}
+
+    def init_ret(self, wbits):
+        s = ZStreamStruct()
+        rc = self.lib.inflateInit2_(ctypes.byref(s), wbits, b"1.3", ctypes.sizeof(s))
+        if rc == 0:
+            self.lib.inflateEnd(ctypes.byref(s))
+        return rc
+
+    def stream(self, data, wbits, in_chunks, out_cap, finish=True, max_calls=1000000):
+        """Same driver and trace format as orclib.Checker.stream()."""
+        s = ZStreamStruct()
+        rc = self.lib.inflateInit2_(ctypes.byref(s), wbits, b"1.3", ctypes.sizeof(s))
+        if rc != 0:
+            return [("init", rc)], b""
+        trace, out = [], bytearray()
+        buf = ctypes.create_string_buffer(max(out_cap, 1))
+        pos, k = 0, 0
+        pending = b""
+        try:
+            for _ in range(max_calls):
+                if not pending and pos < len(data):
+                    n = in_chunks[k % len(in_chunks)]
+                    k += 1
+                    pending = data[pos:pos + n]
+                    pos += len(pending)
+                flush = 4 if (finish and pos >= len(data)) else 0
+                ibuf = ctypes.create_string_buffer(pending, max(len(pending), 1))
+                s.next_in = ctypes.addressof(ibuf)
+                s.avail_in = len(pending)
+                s.next_out = ctypes.addressof(buf)
+                s.avail_out = out_cap
+                ret = self.lib.inflate(ctypes.byref(s), flush)
+                c, p = len(pending) - s.avail_in, out_cap - s.avail_out
+                out += buf.raw[:p]
+                trace.append((ret, self.msgs.get(s.msg, 0) if s.msg else 0, s.total_in, s.total_out,
+                              s.adler & 0xffffffff, s.data_type, c, p))
+                pending = pending[c:]
+                if ret not in (0, -5):
+                    break
+                if ret == -5 and c == 0 and p == 0 and pos >= len(data):
+                    break
+        finally:
+            self.lib.inflateEnd(ctypes.byref(s))
+        return trace, bytes(out)
