@@ -263,6 +263,7 @@ ZSB_DEV void stream_decode(State &S, const uint8_t *in, uint32_t in_len, uint32_
     for (;;) {
         int want = 0;
         if (active) want = run_serial(S, L, R, T, lut, primed);
+        lane::Wp<W>::sync();                  // lane 0's code lengths (in S.tables) visible to the warp
         want = (int)lane::Wp<W>::shfl((uint32_t)want, 0);
         if (want == 0) break;
         const uint32_t info = lane::Wp<W>::shfl(L.nlen | (L.ndist << 12), 0);
