@@ -91,6 +91,9 @@ struct Lane {
     uint32_t lw, nl;     // literals waiting for their sequence
     uint32_t hist;       // valid bytes of history before out[0] (0 for one-shot members)
     uint32_t nlen, ndist;
+    uint32_t mode;       // fast_step: 0 = the next code is a literal/length code, 1 = a distance code
+    uint32_t pl;         // fast_step: length of the match whose distance code comes next (mode 1)
+    uint32_t ring_sa;    // shared-window address of `ring` (device only)
 };
 
 ZSB_DEV void emit(Lane &L, uint32_t lo, uint32_t hi) {
@@ -227,28 +230,32 @@ ZSB_DEV uint32_t lookup_dist(const uint8_t *T, uint32_t h32, uint32_t &nb) {
 // reference would wait for input (src/inflate.c:1046-1142).  Returns EV_LIT (byte in d.mdist),
 // EV_MATCH (d.mlen, d.mdist), EV_EOB, EV_ERR or EV_STARVE.
 // ------------------------------------------------------------------------------------------------
-ZSB_DEV int careful_symbol(Dec &d, const uint8_t *T, const uint32_t *lut) {
+// have_len: the length code and its extra bits have been consumed already (d.mlen is set): resume at
+// the distance code, as the reference resumes in mode DIST (src/inflate.c:1097).
+ZSB_DEV int careful_symbol(Dec &d, const uint8_t *T, const uint32_t *lut, bool have_len = false) {
     BitIn &b = d.b;
-    bi_fill(b);
-    uint32_t nb;
-    uint32_t e = lookup_litlen(T, (uint32_t)b.hold, nb);
-    if (nb > b.nbits) return EV_STARVE;
-    bi_drop(b, nb);
-    uint32_t kind = e & 0x30u, v = e >> 6;
-    if (kind == K_LIT) {
-        d.mdist = v;
-        return EV_LIT;
+    uint32_t nb, xb;
+    if (!have_len) {
+        bi_fill(b);
+        uint32_t e = lookup_litlen(T, (uint32_t)b.hold, nb);
+        if (nb > b.nbits) return EV_STARVE;
+        bi_drop(b, nb);
+        uint32_t kind = e & 0x30u, v = e >> 6;
+        if (kind == K_LIT) {
+            d.mdist = v;
+            return EV_LIT;
+        }
+        if (kind == K_SPECIAL) {
+            if (v == 0) return EV_EOB;
+            d.msg = M_LITCODE;
+            return EV_ERR;
+        }
+        uint32_t lw = lut[LUT_LEN + d.d64 * 32 + v];
+        xb = lw >> 16;
+        if (!bi_need(b, xb)) return EV_STARVE;
+        d.mlen = (lw & 0xffffu) + (xb ? bi_peek(b, xb) : 0u);
+        bi_drop(b, xb);
     }
-    if (kind == K_SPECIAL) {
-        if (v == 0) return EV_EOB;
-        d.msg = M_LITCODE;
-        return EV_ERR;
-    }
-    uint32_t lw = lut[LUT_LEN + d.d64 * 32 + v];
-    uint32_t xb = lw >> 16;
-    if (!bi_need(b, xb)) return EV_STARVE;
-    d.mlen = (lw & 0xffffu) + (xb ? bi_peek(b, xb) : 0u);
-    bi_drop(b, xb);
     bi_fill(b);
     uint32_t s = lookup_dist(T, (uint32_t)b.hold, nb);
     if (nb > b.nbits) return EV_STARVE;
@@ -370,6 +377,137 @@ ZSB_DEV bool fast_symbol(Lane &L, const uint8_t *T, const uint32_t *lut) {
         L.lw |= v << (8 * L.nl);
         L.nl++;
     }
+    return true;
+}
+
+// ------------------------------------------------------------------------------------------------
+// The lock-step loop of k_lane: ONE Huffman code per trip and lane.  A match takes two trips (the
+// length code, then the distance code), so that a trip's dependent chain is one root lookup (+ one
+// side-array lookup) + one base/extra-bits lookup for every lane, whatever it decodes, and literal
+// and match lanes run the same instructions.  Everything is straight-line and predicated; the only
+// branch is the search for codes the roots do not resolve (rare).
+// Returns false without consuming the code when the lane has to leave the loop (end of block, invalid
+// code, distance too far back, capacity reached): the checked path takes over at that code, with
+// L.mode telling it whether the length has been consumed already.
+// ------------------------------------------------------------------------------------------------
+ZSB_DEV uint32_t ring_load(const Lane &L, uint32_t byteoff) {          // byteoff = 0, 4, 8 or 12
+#if defined(__CUDA_ARCH__)
+    uint32_t v;
+    asm volatile("ld.shared.u32 %0, [%1];" : "=r"(v) : "r"(L.ring_sa + byteoff) : "memory");
+    return v;
+#else
+    return L.ring[byteoff >> 2];
+#endif
+}
+// if p: start the copy of the input word at byte offset off (nothing past the end) and close a group
+ZSB_DEV void fetch_word_if(const Lane &L, bool p, uint32_t off) {
+    const BitIn &b = L.d.b;
+#if defined(__CUDA_ARCH__)
+    const uint32_t go = (p && off < b.len) ? 1u : 0u, grp = p ? 1u : 0u;
+    asm volatile(
+        "{\n\t.reg .pred q, r;\n\tsetp.ne.u32 q, %0, 0;\n\tsetp.ne.u32 r, %1, 0;\n\t"
+        "@q cp.async.ca.shared.global [%2], [%3], 4;\n\t@r cp.async.commit_group;\n\t}" ::"r"(go),
+        "r"(grp), "r"(L.ring_sa + (off & 12u)), "l"(b.p + off)
+        : "memory");
+#else
+    if (p && off < b.len) L.ring[(off >> 2) & 3u] = *(const uint32_t *)(b.p + off);
+#endif
+}
+ZSB_DEV void store_seq_if(seq_t *at, bool p, uint32_t lo, uint32_t hi) {
+#if defined(__CUDA_ARCH__)
+    asm volatile("{\n\t.reg .pred q;\n\tsetp.ne.u32 q, %0, 0;\n\t@q st.global.v2.u32 [%1], {%2, %3};\n\t}" ::"r"(
+                     (uint32_t)p),
+                 "l"(at), "r"(lo), "r"(hi)
+                 : "memory");
+#else
+    if (p) {
+        at->lo = lo;
+        at->hi = hi;
+    }
+#endif
+}
+// distance codes longer than DRB bits: search of the per-length limits
+ZSB_DEV uint32_t dist_long(const uint8_t *T, uint32_t h32, uint32_t &nb) {
+    const uint32_t c15 = __brev(h32) >> 17;
+    const uint16_t *lim = (const uint16_t *)(T + S_DLIM);
+    uint32_t k = 0;
+#pragma unroll
+    for (int j = 0; j < 8; j++) k += c15 >= lim[j] ? 1u : 0u;
+    const uint32_t l = 7 + k;
+    const uint32_t idx = (T[S_DBASE + k] + (c15 >> (15 - l))) & 31u;
+    nb = l;
+    return T[S_DS + idx];
+}
+
+// codes the roots do not resolve, both kinds: returns nb | kind | value << 6 (rare; kept out of line
+// so that the compiler does not split the loop body by mode around it)
+#if defined(__CUDACC__)
+__device__ __noinline__
+#else
+static inline
+#endif
+uint32_t slow_lookup(const uint8_t *T, uint32_t w, uint32_t mode) {
+    uint32_t nb;
+    if (mode) {
+        const uint32_t s = dist_long(T, w, nb);
+        return nb | K_LEN | (s << 6);
+    }
+    const uint32_t e2 = litlen_mixed(T, w, nb);
+    return nb | (e2 & ~15u);
+}
+ZSB_DEV uint32_t sel(uint32_t m, uint32_t a, uint32_t b) { return (a & m) | (b & ~m); }   // m ? a : b, m = 0 / ~0
+
+ZSB_DEV bool fast_step(Lane &L, const uint8_t *T, const uint32_t *lut) {
+    Dec &d = L.d;
+    BitIn &b = d.b;
+    // ---- refill: 32 more bits when fewer than 32 are held; the word three ahead is requested ----
+    const bool need = b.nbits < 32;
+    ZSB_CP_WAIT(2);
+    const uint32_t rw = ring_load(L, b.next & 12u);
+    fetch_word_if(L, need, b.next + 12);
+    b.hold |= need ? (uint64_t)rw << b.nbits : 0ull;
+    b.nbits += need ? 32u : 0u;
+    b.next += need ? 4u : 0u;
+    // ---- both roots are read; the lane's mode picks one (mask arithmetic, no branch) ----
+    const uint32_t w = (uint32_t)b.hold;
+    const uint32_t m = 0u - L.mode;                                // ~0 in distance mode
+    const uint32_t eL = ((const uint16_t *)(T + S_LR))[w & 255u];
+    const uint32_t eD = T[S_DR + (w & 63u)];
+    const bool link = (eL & 0x30u) == K_LINK;
+    const uint32_t x = (eL & 7u) + 1u;
+    const uint32_t idx = link ? (eL >> 7) + ((__brev(w >> LRB) >> 1) >> (31 - x)) : 0u;
+    const uint32_t ls = T[S_LS + idx];
+    // entry in the common format: nb | kind | value << 6   (K_LEN = "has a base and extra bits")
+    const uint32_t entL = link ? ((LRB + x) | K_LIT | (ls << 6)) : eL;
+    const uint32_t entD = (eD & 7u) | K_LEN | ((eD >> 3) << 6);
+    uint32_t ent = sel(m, entD, entL);
+    const uint32_t slowL = link ? (eL & (LINK_MIXED | LINK_HI)) : 0u;
+    const uint32_t slowD = eD == 0 ? 1u : 0u;
+    const uint32_t badD = (eD & 7u) == 7u ? 1u : 0u;
+    if (sel(m, slowD, slowL)) ent = slow_lookup(T, w, L.mode);
+    const uint32_t nb = ent & 15u, kind = ent & 0x30u, v = ent >> 6;
+    const bool hasx = kind == K_LEN, islit = kind == K_LIT;
+    const uint32_t lw = lut[sel(m, LUT_DIST, LUT_LEN) + d.d64 * 32 + (v & 31u)];
+    const uint32_t xb = hasx ? (lw >> 16) & 31u : 0u;
+    const uint32_t val = (lw & 0xffffu) + ((w >> nb) & ((1u << xb) - 1u));
+    const uint32_t used = nb + xb;
+    // ---- may this code be committed here? ----
+    const uint32_t okD = (!(badD & m) && !(lw >> 31) && val <= d.pos + L.hist && d.pos + L.pl <= d.cap) ? 1u : 0u;
+    const uint32_t okL = (hasx || (islit && d.pos < d.cap)) ? 1u : 0u;
+    if (!sel(m, okD, okL)) return false;
+    // ---- commit ----
+    b.hold >>= used;
+    b.nbits -= used;
+    const bool put = m != 0 || (islit && L.nl == 3);
+    store_seq_if(L.seq, put, L.lw | (L.nl << Q_NLIT_SHIFT) | (m & Q_MATCH), m & ((val - 1u) | ((L.pl - 3u) << 16)));
+    L.seq += put ? 1 : 0;
+    L.lw = put ? 0u : L.lw;
+    L.nl = put ? 0u : L.nl;
+    L.lw |= islit ? v << (8 * L.nl) : 0u;
+    L.nl += islit ? 1u : 0u;
+    d.pos += sel(m, L.pl, islit ? 1u : 0u);
+    L.pl = val;                   // meaningful after a length code
+    L.mode = (~m & (hasx ? 1u : 0u));
     return true;
 }
 
@@ -715,7 +853,7 @@ ZSB_DEV int start_member(Lane &L, uint32_t slot, const Batch &B) {
     d.d64 = m.window_bits == -16;
     d.last = 0; d.at_type = 0; d.msg = 0; d.extent = 0; d.mlen = 0; d.mdist = 0; d.mtrunc = 0;
     L.seq = L.seq0 = B.seq_base + B.seq_off[slot];
-    L.lw = 0; L.nl = 0;
+    L.lw = 0; L.nl = 0; L.mode = 0; L.pl = 0;
     L.hist = B.hist ? B.hist[idx] : 0u;
     int ev = EV_NONE;
     if (!wbits_valid(m.window_bits) || (in == nullptr && m.in_len != 0) || (m.out == nullptr && m.out_cap != 0)) {
@@ -817,7 +955,12 @@ __device__ __forceinline__ void warp_lanes(const Batch &B, uint8_t *slots, uint8
     L.ring = rings + lane * RING_WORDS;
     L.d.pos = 0; L.d.cap = 0; L.d.b.p = nullptr; L.d.b.len = 0; L.d.b.next = 0; L.d.b.nbits = 0; L.d.b.hold = 0;
     L.d.d64 = 0; L.d.msg = 0; L.nl = 0; L.lw = 0; L.seq = L.seq0 = nullptr; L.nlen = 0; L.ndist = 0;
-    L.mm.idx = 0;
+    L.mm.idx = 0; L.mode = 0; L.pl = 0; L.hist = 0;
+#if defined(__CUDA_ARCH__)
+    L.ring_sa = (uint32_t)__cvta_generic_to_shared(L.ring);
+#else
+    L.ring_sa = 0;
+#endif
     uint8_t *T = slots + (size_t)lane * SLOT;
     int st = LS_FETCH;
     const unsigned lt = (1u << lane) - 1u;
@@ -868,7 +1011,9 @@ __device__ __forceinline__ void warp_lanes(const Batch &B, uint8_t *slots, uint8
             }
             if (st == LS_SYM && L.d.b.next + 8 > L.d.b.len) st = LS_TAIL;
             while (st == LS_TAIL) {             // the last bytes of a member: every step checked
-                int e2 = careful_symbol(L.d, T, lut);
+                if (L.mode) L.d.mlen = L.pl;          // the loop stopped between a length and its distance
+                int e2 = careful_symbol(L.d, T, lut, L.mode != 0);
+                L.mode = 0;
                 if (e2 == EV_LIT) {
                     if (L.d.pos >= L.d.cap) e2 = EV_OUTFULL;
                     else {
@@ -894,7 +1039,7 @@ __device__ __forceinline__ void warp_lanes(const Batch &B, uint8_t *slots, uint8
 #pragma unroll 1
         for (;;) {
             if (st == LS_SYM) {
-                if (L.d.b.next + 8 > L.d.b.len || !fast_symbol(L, T, lut)) st = LS_TAIL;
+                if (L.d.b.next + 8 > L.d.b.len || !fast_step(L, T, lut)) st = LS_TAIL;
             }
             if (Wp<W>::any(st != LS_SYM && st != LS_IDLE)) break;
         }
