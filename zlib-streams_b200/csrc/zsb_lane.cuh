@@ -24,22 +24,29 @@ namespace zsb {
 namespace lane {
 
 // ---- per-member table slot (bytes) ----
-constexpr int LRB = 8;                    // literal/length root bits
-constexpr int DRB = 6;                    // distance root bits
-constexpr int S_LR = 0;                   // u16[256]  litlen root: same entry format as zsb_device.cuh
-constexpr int S_LS = 512;                 // u8[288]   low byte of the symbols with codes longer than LRB, code order
-constexpr int S_DS = 800;                 // u8[32]    distance symbols with codes longer than DRB, code order
-constexpr int S_DR = 832;                 // u8[64]    distance root: sym<<3 | len (1..6), 0 = longer code, 7 = invalid
-constexpr int S_LLIM = 896;               // u16[8]    litlen left-aligned (15 bit) code limits for lengths 9..15
-constexpr int S_LBASE = 912;              // u16[8]    index bias into S_LS for lengths 9..15
-constexpr int S_LT256 = 928;              // u16[8]    first S_LS index holding a symbol >= 256, per length 9..15
-constexpr int S_DLIM = 944;               // u16[9]    distance limits for lengths 7..15
-constexpr int S_DBASE = 962;              // u8[9]     index bias into S_DS for lengths 7..15
-constexpr int SLOT = 972;                 // bytes per member
+// Canonical-code tables, the same three arrays for both codes: for every code length l = 1..15 the
+// left-aligned (15 bit) limit lim[l] = (first code of length l + number of codes of length l) <<
+// (15 - l) — non-decreasing in l, so the length of the code at the head of the bit buffer is the
+// first l whose limit exceeds the next 15 bits — a bias that turns those bits into an index into the
+// symbols in code order, and those symbols (one byte each; for the literal/length code the ninth bit
+// comes from lt256[l], the index of the first symbol >= 256 of that length).
+// 470 bytes per member: 14 warps x 32 members per SM, enough to hold a whole 65,536-member batch in
+// flight on 148 SMs.
+constexpr int S_LLIM = 0;                 // u16[15]  literal/length limits, lengths 1..15
+constexpr int S_LBASE = 30;               // u16[15]  index bias per length
+constexpr int S_LT256 = 60;               // u16[15]  first index holding a symbol >= 256, per length
+constexpr int S_LS = 90;                  // u8[288]  low byte of the symbols in code order (the fixed code has 288)
+constexpr int S_D = 378;                  // distance code: same shape without lt256
+constexpr int S_DLIM = S_D;               // u16[15]
+constexpr int S_DBASE = S_D + 30;         // u16[15]
+constexpr int S_DS = S_D + 60;            // u8[32]
+constexpr int SLOT = 470;                 // bytes per member
 // while a block header is read the slot holds (the tables are built over it afterwards):
 constexpr int H_LENS = 0;                 // u8[320]   code lengths of the litlen + distance codes
-constexpr int H_CL = 512;                 // u8[128]   code-length code root (7 bits): sym<<3 | len
-constexpr int H_CLL = 640;                // u8[19]    code-length code lengths
+constexpr int H_CL = 320;                 // u8[128]   code-length code root (7 bits): sym<<3 | len
+constexpr int H_CLL = 448;                // u8[19]    code-length code lengths
+constexpr int H_CNT = 0;                  // u16[16]   census of the code-length code (before H_LENS is filled)
+constexpr int H_NXT = 32;                 // u16[16]
 
 // ---- per-warp scratch (bytes) for the cooperative table build ----
 constexpr int W_SORT = 0;                 // u16[288]  symbols in code order
@@ -47,9 +54,9 @@ constexpr int W_CNT = 576;                // u32[16]   codes per length
 constexpr int W_LIT = 640;                // u32[16]   codes per length whose symbol is < 256
 constexpr int W_OFF = 704;                // u32[16]   running sort offset per length
 constexpr int W_DL = 768;                 // u8[32]    distance code lengths
-constexpr int WSCR = 1024;
+constexpr int WSCR = 992;
 
-constexpr int WARPS = 7;                  // warps per CTA, one CTA per SM: 224 members in flight per SM
+constexpr int WARPS = 14;                 // warps per CTA, one CTA per SM: 448 members in flight per SM
 constexpr size_t SMEM = LUT_BYTES + (size_t)WARPS * WSCR + (size_t)WARPS * 32 * SLOT + (size_t)WARPS * 32 * 16;
 
 // ---- LZ sequence (8 bytes): lo = lit0 | lit1<<8 | lit2<<16 | flags, hi = payload ----
@@ -159,8 +166,10 @@ ZSB_DEV void prime(Lane &L) {
 }
 
 // ------------------------------------------------------------------------------------------------
-// Code lookups on the compact tables.  `h` holds the next input bits (zero padded past the end of the
-// input); nb receives the code length.  Entries are in the format of zsb_device.cuh.
+// Code lookups on the canonical tables.  `h32` holds the next input bits (zero padded past the end of
+// the input); nb receives the code length.  A bit pattern that is no code (possible only with the
+// incomplete sets the reference accepts: a single one-bit code, or no distance code at all,
+// src/inftrees.c:131-153) reads as the reference's filler entry: invalid, one bit (`:301-317`).
 // ------------------------------------------------------------------------------------------------
 ZSB_DEV uint32_t sym_entry(uint32_t sym) {        // symbol -> entry without the length field
     if (sym < 256) return K_LIT | (sym << 6);
@@ -168,61 +177,38 @@ ZSB_DEV uint32_t sym_entry(uint32_t sym) {        // symbol -> entry without the
     if (sym < 286) return K_LEN | ((sym - 257) << 6);
     return E_INVALID;
 }
-
-// A root entry of kind K_LINK stands for all codes longer than LRB bits that start with that root
-// index.  Canonical codes that share a prefix are neighbours in code order, so when they all have the
-// same length l the symbol is LS[base + next (l - LRB) bits] with no further table: entry bits [2:0] =
-// l - LRB - 1, bits [15:7] = base.  The few prefixes that hold codes of several lengths (LINK_MIXED)
-// or a symbol >= 256 (LINK_HI) go through the search over the per-length limits instead.
-constexpr uint32_t LINK_HI = 1u << 3;
-constexpr uint32_t LINK_MIXED = 1u << 6;
-
-ZSB_DEV uint32_t litlen_mixed(const uint8_t *T, uint32_t h32, uint32_t &nb) {
-    const uint32_t c15 = __brev(h32) >> 17;
-    const uint16_t *lim = (const uint16_t *)(T + S_LLIM);
-    uint32_t k = 0;                                  // limits do not decrease: count those at or below c15
-#pragma unroll
-    for (int j = 0; j < 6; j++) k += c15 >= lim[j] ? 1u : 0u;
-    const uint32_t l = 9 + k;
-    const uint32_t idx = (((const uint16_t *)(T + S_LBASE))[k] + (c15 >> (15 - l))) & 0x1ffu;
-    uint32_t sym = T[S_LS + idx];
-    if (idx >= ((const uint16_t *)(T + S_LT256))[k]) sym += 256;
-    nb = l;
-    return sym_entry(sym);
-}
-ZSB_DEV uint32_t litlen_long(const uint8_t *T, uint32_t e, uint32_t h32, uint32_t &nb) {
-    if (e & (LINK_MIXED | LINK_HI)) return litlen_mixed(T, h32, nb);
-    const uint32_t x = (e & 7u) + 1u;
-    const uint32_t idx = (e >> 7) + (__brev(h32 >> LRB) >> (32 - x));
-    nb = LRB + x;
-    return K_LIT | ((uint32_t)T[S_LS + idx] << 6);
+// number of lengths whose limit is at or below c15 (0..15) = code length - 1; 15 = no code
+ZSB_DEV uint32_t canon_len(const uint16_t *lim, uint32_t c15) {
+    uint32_t k = c15 >= lim[7] ? 8u : 0u;
+    k += c15 >= lim[k + 3] ? 4u : 0u;
+    k += c15 >= lim[k + 1] ? 2u : 0u;
+    k += c15 >= lim[k] ? 1u : 0u;
+    return k;
 }
 ZSB_DEV uint32_t lookup_litlen(const uint8_t *T, uint32_t h32, uint32_t &nb) {
-    uint32_t e = ((const uint16_t *)(T + S_LR))[h32 & 255u];
-    if ((e & 0x30u) == K_LINK) return litlen_long(T, e, h32, nb);
-    nb = e & 15u;
-    return e;
+    const uint32_t c15 = __brev(h32) >> 17;
+    const uint32_t k = canon_len((const uint16_t *)(T + S_LLIM), c15);
+    if (k == 15) {
+        nb = 1;
+        return E_INVALID;
+    }
+    const uint32_t idx = (((const uint16_t *)(T + S_LBASE))[k] + (c15 >> (14 - k))) & 0x1ffu;
+    uint32_t sym = T[S_LS + idx];
+    if (idx >= ((const uint16_t *)(T + S_LT256))[k]) sym += 256;
+    nb = k + 1;
+    return sym_entry(sym);
 }
 // distance code: returns the symbol, 32 for an invalid code
 ZSB_DEV uint32_t lookup_dist(const uint8_t *T, uint32_t h32, uint32_t &nb) {
-    uint32_t e = T[S_DR + (h32 & 63u)];
-    if (e == 0) {
-        const uint32_t c15 = __brev(h32) >> 17;
-        const uint16_t *lim = (const uint16_t *)(T + S_DLIM);
-        uint32_t k = 0;
-#pragma unroll
-        for (int j = 0; j < 8; j++) k += c15 >= lim[j] ? 1u : 0u;
-        const uint32_t l = 7 + k;
-        const uint32_t idx = (T[S_DBASE + k] + (c15 >> (15 - l))) & 31u;
-        nb = l;
-        return T[S_DS + idx];
-    }
-    nb = e & 7u;
-    if (nb == 7) {
+    const uint32_t c15 = __brev(h32) >> 17;
+    const uint32_t k = canon_len((const uint16_t *)(T + S_DLIM), c15);
+    if (k == 15) {
         nb = 1;
         return 32;
     }
-    return e >> 3;
+    const uint32_t idx = (((const uint16_t *)(T + S_DBASE))[k] + (c15 >> (14 - k))) & 31u;
+    nb = k + 1;
+    return T[S_DS + idx];
 }
 
 // ------------------------------------------------------------------------------------------------
@@ -292,95 +278,6 @@ ZSB_DEV int accept_match(Lane &L) {
 }
 
 // ------------------------------------------------------------------------------------------------
-// One symbol on the unchecked path: the caller guarantees that two whole input words are still
-// unread (b.next + 8 <= b.len), so nothing can run dry.  Returns EV_NONE or the stop event.
-// ------------------------------------------------------------------------------------------------
-ZSB_DEV void refill(Lane &L) {
-    BitIn &b = L.d.b;
-    ZSB_CP_WAIT(2);                                            // all but the two youngest words have arrived
-    b.hold |= (uint64_t)L.ring[(b.next >> 2) & 3u] << b.nbits;
-    b.nbits += 32;
-    fetch_word(L, b.next + 12);
-    b.next += 4;
-}
-
-// Returns true when the symbol was a literal or a whole match that fits and has been committed.
-// Anything else (end of block, invalid codes, a distance too far back, the capacity reached) leaves
-// the lane at the start of the symbol (only a refill may have happened) and returns false: the
-// checked path then decodes that symbol again and stops where the reference stops.
-// Written as straight-line code: the match fields are computed for every lane and selected
-// afterwards, because with 32 members per warp every branch of a symbol is taken by some lane on
-// nearly every trip anyway.
-ZSB_DEV bool fast_symbol(Lane &L, const uint8_t *T, const uint32_t *lut) {
-    Dec &d = L.d;
-    BitIn &b = d.b;
-    if (b.nbits < 32) refill(L);
-    // the code and its extra bits (at most 31 bits) are taken from a 32-bit view of the bit buffer
-    const uint32_t w = (uint32_t)b.hold;
-    const uint32_t e = ((const uint16_t *)(T + S_LR))[w & 255u];
-    const bool link = (e & 0x30u) == K_LINK;
-    const uint32_t x = (e & 7u) + 1u;
-    const uint32_t idx = link ? (e >> 7) + ((__brev(w >> LRB) >> 1) >> (31 - x)) : 0u;
-    const uint32_t ls = T[S_LS + idx];
-    uint32_t nb = link ? LRB + x : (e & 15u);
-    uint32_t kind = link ? K_LIT : (e & 0x30u);
-    uint32_t v = link ? ls : (e >> 6);
-    if (link && (e & (LINK_MIXED | LINK_HI))) {
-        const uint32_t e2 = litlen_mixed(T, w, nb);
-        kind = e2 & 0x30u;
-        v = e2 >> 6;
-    }
-    const bool islit = kind == K_LIT, islen = kind == K_LEN;
-    // ---- length extra bits, distance code and extra bits (meaningful when islen) ----
-    const uint32_t lutoff = d.d64 * 32;
-    const uint32_t lw = lut[LUT_LEN + lutoff + (v & 31u)];
-    const uint32_t xb = lw >> 16;
-    const uint32_t mlen = (lw & 0xffffu) + ((w >> nb) & ((1u << xb) - 1u));
-    const uint32_t used1 = nb + (islen ? xb : 0u);
-    uint64_t h2 = b.hold >> used1;
-    uint32_t n2 = b.nbits - used1;
-    const bool again = islen && n2 < 32;          // second refill: its prefetch is only issued on commit
-    if (again) {
-        ZSB_CP_WAIT(2);
-        h2 |= (uint64_t)L.ring[(b.next >> 2) & 3u] << n2;
-        n2 += 32;
-    }
-    const uint32_t w2 = (uint32_t)h2;
-    uint32_t nb2 = 0, s = 0;
-    if (islen) s = lookup_dist(T, w2, nb2);
-    const uint32_t dw = lut[LUT_DIST + lutoff + (s & 31u)];
-    const uint32_t xb2 = (dw >> 16) & 15u;
-    const uint32_t mdist = (dw & 0xffffu) + ((w2 >> nb2) & ((1u << xb2) - 1u));
-    const uint32_t used2 = islen ? nb2 + xb2 : 0u;
-    const uint32_t n = islen ? mlen : 1u;
-    bool clean = (islit || islen) && d.pos + n <= d.cap;
-    if (islen && (s >= 32 || (dw >> 31) || mdist > d.pos + L.hist)) clean = false;
-    if (!clean) return false;
-    // ---- commit ----
-    b.hold = h2 >> used2;
-    b.nbits = n2 - used2;
-    if (again) {
-        fetch_word(L, b.next + 12);
-        b.next += 4;
-    }
-    d.pos += n;
-    const bool put = islen || L.nl == 3;
-    if (put) {
-        seq_t q;
-        q.lo = L.lw | (L.nl << Q_NLIT_SHIFT) | (islen ? Q_MATCH : 0u);
-        q.hi = islen ? ((mdist - 1u) | ((mlen - 3u) << 16)) : 0u;
-        *L.seq++ = q;
-        L.lw = 0;
-        L.nl = 0;
-    }
-    if (islit) {
-        L.lw |= v << (8 * L.nl);
-        L.nl++;
-    }
-    return true;
-}
-
-// ------------------------------------------------------------------------------------------------
 // The lock-step loop of k_lane: ONE Huffman code per trip and lane.  A match takes two trips (the
 // length code, then the distance code), so that a trip's dependent chain is one root lookup (+ one
 // side-array lookup) + one base/extra-bits lookup for every lane, whatever it decodes, and literal
@@ -426,35 +323,6 @@ ZSB_DEV void store_seq_if(seq_t *at, bool p, uint32_t lo, uint32_t hi) {
     }
 #endif
 }
-// distance codes longer than DRB bits: search of the per-length limits
-ZSB_DEV uint32_t dist_long(const uint8_t *T, uint32_t h32, uint32_t &nb) {
-    const uint32_t c15 = __brev(h32) >> 17;
-    const uint16_t *lim = (const uint16_t *)(T + S_DLIM);
-    uint32_t k = 0;
-#pragma unroll
-    for (int j = 0; j < 8; j++) k += c15 >= lim[j] ? 1u : 0u;
-    const uint32_t l = 7 + k;
-    const uint32_t idx = (T[S_DBASE + k] + (c15 >> (15 - l))) & 31u;
-    nb = l;
-    return T[S_DS + idx];
-}
-
-// codes the roots do not resolve, both kinds: returns nb | kind | value << 6 (rare; kept out of line
-// so that the compiler does not split the loop body by mode around it)
-#if defined(__CUDACC__)
-__device__ __noinline__
-#else
-static inline
-#endif
-uint32_t slow_lookup(const uint8_t *T, uint32_t w, uint32_t mode) {
-    uint32_t nb;
-    if (mode) {
-        const uint32_t s = dist_long(T, w, nb);
-        return nb | K_LEN | (s << 6);
-    }
-    const uint32_t e2 = litlen_mixed(T, w, nb);
-    return nb | (e2 & ~15u);
-}
 ZSB_DEV uint32_t sel(uint32_t m, uint32_t a, uint32_t b) { return (a & m) | (b & ~m); }   // m ? a : b, m = 0 / ~0
 
 ZSB_DEV bool fast_step(Lane &L, const uint8_t *T, const uint32_t *lut) {
@@ -468,32 +336,28 @@ ZSB_DEV bool fast_step(Lane &L, const uint8_t *T, const uint32_t *lut) {
     b.hold |= need ? (uint64_t)rw << b.nbits : 0ull;
     b.nbits += need ? 32u : 0u;
     b.next += need ? 4u : 0u;
-    // ---- both roots are read; the lane's mode picks one (mask arithmetic, no branch) ----
+    // ---- the code at the head of the buffer, in the lane's current code (mask arithmetic, no branch) ----
     const uint32_t w = (uint32_t)b.hold;
     const uint32_t m = 0u - L.mode;                                // ~0 in distance mode
-    const uint32_t eL = ((const uint16_t *)(T + S_LR))[w & 255u];
-    const uint32_t eD = T[S_DR + (w & 63u)];
-    const bool link = (eL & 0x30u) == K_LINK;
-    const uint32_t x = (eL & 7u) + 1u;
-    const uint32_t idx = link ? (eL >> 7) + ((__brev(w >> LRB) >> 1) >> (31 - x)) : 0u;
-    const uint32_t ls = T[S_LS + idx];
-    // entry in the common format: nb | kind | value << 6   (K_LEN = "has a base and extra bits")
-    const uint32_t entL = link ? ((LRB + x) | K_LIT | (ls << 6)) : eL;
-    const uint32_t entD = (eD & 7u) | K_LEN | ((eD >> 3) << 6);
-    uint32_t ent = sel(m, entD, entL);
-    const uint32_t slowL = link ? (eL & (LINK_MIXED | LINK_HI)) : 0u;
-    const uint32_t slowD = eD == 0 ? 1u : 0u;
-    const uint32_t badD = (eD & 7u) == 7u ? 1u : 0u;
-    if (sel(m, slowD, slowL)) ent = slow_lookup(T, w, L.mode);
-    const uint32_t nb = ent & 15u, kind = ent & 0x30u, v = ent >> 6;
-    const bool hasx = kind == K_LEN, islit = kind == K_LIT;
+    const uint32_t c16 = __brev(w) >> 16, c15 = c16 >> 1;
+    const uint8_t *tb = T + (m & (uint32_t)S_D);
+    const uint32_t k = canon_len((const uint16_t *)tb, c15);       // code length - 1; 15 = no such code
+    const uint32_t bias = ((const uint16_t *)(tb + S_LBASE))[k];
+    const uint32_t lt = ((const uint16_t *)(T + S_LT256))[k];
+    const uint32_t idx = (bias + (c16 >> (15 - k))) & 0x1ffu;
+    const uint32_t sb = tb[sel(m, (uint32_t)(S_DS - S_D), (uint32_t)S_LS) + idx];
+    const uint32_t sym = sb + ((~m & (idx >= lt ? 256u : 0u)));
+    const uint32_t nb = k + 1;
+    const bool islit = !m && sym < 256;
+    const uint32_t v = sel(m, sym, sym - 257u);                    // index of the base / extra-bits entry
+    const bool hasx = k < 15 && (m || v < 29u);                    // a length or a distance code
     const uint32_t lw = lut[sel(m, LUT_DIST, LUT_LEN) + d.d64 * 32 + (v & 31u)];
     const uint32_t xb = hasx ? (lw >> 16) & 31u : 0u;
     const uint32_t val = (lw & 0xffffu) + ((w >> nb) & ((1u << xb) - 1u));
     const uint32_t used = nb + xb;
     // ---- may this code be committed here? ----
-    const uint32_t okD = (!(badD & m) && !(lw >> 31) && val <= d.pos + L.hist && d.pos + L.pl <= d.cap) ? 1u : 0u;
-    const uint32_t okL = (hasx || (islit && d.pos < d.cap)) ? 1u : 0u;
+    const uint32_t okD = (hasx && !(lw >> 31) && val <= d.pos + L.hist && d.pos + L.pl <= d.cap) ? 1u : 0u;
+    const uint32_t okL = (hasx || (k < 15 && islit && d.pos < d.cap)) ? 1u : 0u;
     if (!sel(m, okD, okL)) return false;
     // ---- commit ----
     b.hold >>= used;
@@ -503,7 +367,7 @@ ZSB_DEV bool fast_step(Lane &L, const uint8_t *T, const uint32_t *lut) {
     L.seq += put ? 1 : 0;
     L.lw = put ? 0u : L.lw;
     L.nl = put ? 0u : L.nl;
-    L.lw |= islit ? v << (8 * L.nl) : 0u;
+    L.lw |= islit ? sym << (8 * L.nl) : 0u;
     L.nl += islit ? 1u : 0u;
     d.pos += sel(m, L.pl, islit ? 1u : 0u);
     L.pl = val;                   // meaningful after a length code
@@ -516,8 +380,6 @@ ZSB_DEV bool fast_step(Lane &L, const uint8_t *T, const uint32_t *lut) {
 // code and the code lengths of both codes, left as bytes at T[H_LENS..].  The two decoding tables
 // are built afterwards by the whole warp (build_tables).  Returns EV_NONE, EV_ERR or EV_STARVE.
 // ------------------------------------------------------------------------------------------------
-constexpr int H_CNT = 672;                // u16[16] scratch of the code-length code census
-constexpr int H_NXT = 704;                // u16[16]
 
 ZSB_DEV bool build_clen8(uint8_t *T, bool d64) {
     const uint8_t *lens = T + H_CLL;
@@ -622,9 +484,9 @@ ZSB_DEV int lane_dynamic_header(Lane &L, uint8_t *T, const uint32_t *lut) {
 #ifndef ZSB_SMEM_ADD
 #define ZSB_SMEM_ADD(p, v) atomicAdd((p), (v))
 #endif
-constexpr int W_FIRST = 832;              // u32[16] first canonical code per length
-constexpr int W_LIM = 896;                // u32[16] (first+count) left-aligned to 15 bits
-constexpr int W_OFF0 = 960;               // u32[16] index of the first symbol of each length in code order
+constexpr int W_FIRST = 800;              // u32[16] first canonical code per length
+constexpr int W_LIM = 864;                // u32[16] (first+count) left-aligned to 15 bits
+constexpr int W_OFF0 = 928;               // u32[16] index of the first symbol of each length in code order
 
 // Table space the reference's two-level builder would use with `root` index bits: the root plus one
 // sub-table per root prefix that carries longer codes, sized by the longest code under the prefix
@@ -716,48 +578,14 @@ ZSB_DEV bool build_litlen_tab(uint8_t *T, uint8_t *scr, const uint8_t *lens, uin
     const uint32_t *off0 = (const uint32_t *)(scr + W_OFF0);
     const uint16_t *sorted = (const uint16_t *)(scr + W_SORT);
     if (maxl > 9 && ref_table_space(cnt, first, 9, maxl) > (d64 ? 851u : 852u)) return false;
-    uint16_t *LR = (uint16_t *)(T + S_LR);
-    const uint32_t nroot0 = off0[LRB + 1];
-    for (uint32_t i = lane; i < 256; i += W) {
-        const uint32_t c15 = __brev(i) >> 17;
-        uint32_t l = 1;
-#pragma unroll
-        for (int j = 1; j <= LRB; j++) l += c15 >= lim[j] ? 1u : 0u;
-        uint32_t e;
-        if (l > LRB) {
-            if (k == 2) {
-                e = E_INVALID | 1u;
-            } else {
-                // lengths of the first and of the last code under this prefix
-                const uint32_t last15 = c15 | ((1u << (15 - LRB)) - 1u);
-                uint32_t lf = LRB + 1, ll = LRB + 1;
-                for (int j = LRB + 1; j < 15; j++) {
-                    lf += c15 >= lim[j] ? 1u : 0u;
-                    ll += last15 >= lim[j] ? 1u : 0u;
-                }
-                if (lf == ll) {
-                    const uint32_t at = off0[lf] + (c15 >> (15 - lf)) - first[lf];     // first code under the prefix
-                    e = K_LINK | (lf - LRB - 1u) | ((at - nroot0) << 7);
-                    if (sorted[at + (1u << (lf - LRB)) - 1u] >= 256) e |= LINK_HI;   // symbols ascend within a length
-                } else {
-                    e = K_LINK | LINK_MIXED;
-                }
-            }
-        } else {
-            const uint32_t s = sorted[off0[l] + (c15 >> (15 - l)) - first[l]];
-            e = sym_entry(s) | l;
-        }
-        LR[i] = (uint16_t)e;
+    for (int j = lane; j < 15; j += W) {
+        const uint32_t l = j + 1;
+        ((uint16_t *)(T + S_LLIM))[j] = (uint16_t)lim[l];
+        ((uint16_t *)(T + S_LBASE))[j] = (uint16_t)(off0[l] - first[l]);
+        ((uint16_t *)(T + S_LT256))[j] = (uint16_t)(off0[l] + lit[l]);
     }
     const uint32_t total = off0[15] + cnt[15];
-    const uint32_t nroot = maxl > LRB ? off0[LRB + 1] : total;
-    for (uint32_t j = lane; j + nroot < total; j += W) T[S_LS + j] = (uint8_t)sorted[nroot + j];
-    for (int j = lane; j < 7; j += W) {
-        const uint32_t l = 9 + j;
-        ((uint16_t *)(T + S_LLIM))[j] = (uint16_t)lim[l];
-        ((uint16_t *)(T + S_LBASE))[j] = (uint16_t)(off0[l] - nroot - first[l]);
-        ((uint16_t *)(T + S_LT256))[j] = (uint16_t)(off0[l] - nroot + lit[l]);
-    }
+    for (uint32_t j = lane; j < total; j += W) T[S_LS + j] = (uint8_t)sorted[j];
     Wp<W>::sync();
     return true;
 }
@@ -768,9 +596,9 @@ ZSB_DEV bool build_dist_tab(uint8_t *T, uint8_t *scr, const uint8_t *lens, uint3
     uint32_t maxl;
     const int k = census_sort<W>(lens, ndist, scr, lane, maxl);
     if (k < 0) return false;
-    if (k == 1) {                                           // src/inftrees.c:131-139
+    if (k == 1) {                                           // no codes at all: src/inftrees.c:131-139
         if (d64) return false;
-        for (int i = lane; i < 64; i += W) T[S_DR + i] = 7;
+        for (int j = lane; j < 15; j += W) ((uint16_t *)(T + S_DLIM))[j] = 0;      // every pattern: invalid, one bit
         Wp<W>::sync();
         return true;
     }
@@ -779,24 +607,13 @@ ZSB_DEV bool build_dist_tab(uint8_t *T, uint8_t *scr, const uint8_t *lens, uint3
     const uint32_t *off0 = (const uint32_t *)(scr + W_OFF0);
     const uint16_t *sorted = (const uint16_t *)(scr + W_SORT);
     if (d64 && maxl > 6 && ref_table_space(cnt, first, 6, maxl) > 593u) return false;
-    for (uint32_t i = lane; i < 64; i += W) {
-        const uint32_t c15 = __brev(i) >> 17;
-        uint32_t l = 1;
-#pragma unroll
-        for (int j = 1; j <= DRB; j++) l += c15 >= lim[j] ? 1u : 0u;
-        uint32_t e;
-        if (l > DRB) e = k == 2 ? 7u : 0u;
-        else e = ((uint32_t)sorted[off0[l] + (c15 >> (15 - l)) - first[l]] << 3) | l;
-        T[S_DR + i] = (uint8_t)e;
+    for (int j = lane; j < 15; j += W) {
+        const uint32_t l = j + 1;
+        ((uint16_t *)(T + S_DLIM))[j] = (uint16_t)lim[l];
+        ((uint16_t *)(T + S_DBASE))[j] = (uint16_t)(off0[l] - first[l]);
     }
     const uint32_t total = off0[15] + cnt[15];
-    const uint32_t nroot = maxl > DRB ? off0[DRB + 1] : total;
-    for (uint32_t j = lane; j + nroot < total; j += W) T[S_DS + j] = (uint8_t)sorted[nroot + j];
-    for (int j = lane; j < 9; j += W) {
-        const uint32_t l = 7 + j;
-        ((uint16_t *)(T + S_DLIM))[j] = (uint16_t)lim[l];
-        T[S_DBASE + j] = (uint8_t)(off0[l] - nroot - first[l]);
-    }
+    for (uint32_t j = lane; j < total; j += W) T[S_DS + j] = (uint8_t)sorted[j];
     Wp<W>::sync();
     return true;
 }
@@ -991,9 +808,9 @@ __device__ __forceinline__ void warp_lanes(const Batch &B, uint8_t *slots, uint8
                 uint8_t *Ts = slots + (size_t)src * SLOT;
                 int msg = 0;
                 if (info & 1u) {
-                    const uint32_t *f = (const uint32_t *)B.fixed_tab;
-                    uint32_t *t32 = (uint32_t *)Ts;
-                    for (int i = lane; i < SLOT / 4; i += W) t32[i] = f[i];
+                    const uint16_t *f = (const uint16_t *)B.fixed_tab;
+                    uint16_t *t16 = (uint16_t *)Ts;
+                    for (int i = lane; i < SLOT / 2; i += W) t16[i] = f[i];
                     Wp<W>::sync();
                 } else {
                     msg = build_tables<W>(Ts, scr, (info >> 2) & 1023u, info >> 12, (info >> 1) & 1u, lane);

@@ -209,15 +209,6 @@ ZSB_DEV int run_serial(State &S, Lane &L, Run &R, uint8_t *T, const uint32_t *lu
         }
         case PH_SYM: {
             R.unit = bitpos(b);
-            if (b.next + 8 <= b.len) {
-                if (!primed) {
-                    lane::prime(L);
-                    primed = true;
-                }
-                if (lane::fast_symbol(L, T, lut)) break;
-            }
-            primed = false;
-            R.unit = bitpos(b);
             const int ev = lane::careful_symbol(d, T, lut);
             if (ev == EV_LIT) {
                 S.plit = d.mdist;
@@ -269,7 +260,7 @@ ZSB_DEV void stream_decode(State &S, const uint8_t *in, uint32_t in_len, uint32_
         const uint32_t info = lane::Wp<W>::shfl(L.nlen | (L.ndist << 12), 0);
         int msg = 0;
         if (want == 2) {
-            for (int i = ln; i < lane::SLOT / 4; i += W) ((uint32_t *)T)[i] = ((const uint32_t *)fixed_tab)[i];
+            for (int i = ln; i < lane::SLOT / 2; i += W) ((uint16_t *)T)[i] = ((const uint16_t *)fixed_tab)[i];
             lane::Wp<W>::sync();
         } else {
             msg = lane::build_tables<W>(T, scr, info & 1023u, info >> 12, S.d64 != 0, ln);
