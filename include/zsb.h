@@ -92,10 +92,15 @@ ZSB_API int zsb_inflate_batch_device(zsb_ctx *ctx, int dev_index, size_t n, cons
 #define ZSB_RAW_ONLY    4u /* every member has window_bits < 0: skip checksum/trailer kernels */
 
 /* Tuning knobs: "path" 0 auto / 1 lane path (one member per lane, k_lane + k_lz) / 2 group path
- * (k_inflate<G>); "lanes_per_member" G of the group path (1,2,4,8,16,32); "seq_arena_bytes" most
+ * (k_inflate<G>); "profile" 1 = time the decode kernels (zsb_profile_read); "lanes_per_member" G of the group path (1,2,4,8,16,32); "seq_arena_bytes" most
  * sequence scratch the lane path may hold at once (larger batches are decoded in slices). */
 ZSB_API int zsb_set_option(zsb_ctx *ctx, const char *name, long value);
 ZSB_API long zsb_get_option(const zsb_ctx *ctx, const char *name);
+
+/* With option "profile" = 1 every k_lane / k_lz launch is bracketed by CUDA events on the launching
+ * stream.  zsb_profile_read() waits for them, returns the number of launch pairs recorded on device
+ * `dev_index` since the last read and their summed durations in milliseconds. */
+ZSB_API long zsb_profile_read(zsb_ctx *ctx, int dev_index, double *lane_ms, double *lz_ms);
 
 /* Number of kernels the last zsb_inflate_batch*() call launched (for accounting). */
 ZSB_API long zsb_last_launches(const zsb_ctx *ctx);

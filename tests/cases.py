@@ -146,3 +146,52 @@ def damaged_streams(count=300):
     for wb in (-17, -7, 7, 16 + 7, 48, 100, -16, -15, 0, 16):
         out.append(("wbits%d" % wb, gen.deflate(b"hello world", 6, -15), wb, 100))
     return out
+
+
+def deflate64_streams(big=False):
+    """(name, data, wbits, plain): Deflate64 streams from the test-only encoder (tests/d64enc.py) that use
+    what the reference's fixtures never do: length code 285 with its 16 extra bits, distance codes 30/31
+    (in dynamic and fixed blocks), matches longer than 258, distances beyond 32 KiB, all block kinds.
+    Callers first check with the reference build that each one decodes back to `plain`."""
+    import d64enc
+    rnd = random.Random(64)
+    blk = bytes(rnd.getrandbits(8) for _ in range(50000))
+    plains = {
+        "soup": gen.word_soup(90000, 3),
+        "far": blk + gen.word_soup(12000, 4) + blk + blk[:40000],
+        "runs": b"ab" * 40000 + bytes(70000) + b"xyz" * 30000 + bytes(range(256)) * 300,
+        "mixed": gen.mixed_plain(150000, 5),
+        "tiny": b"q",
+        "empty": b"",
+    }
+    if big:                       # a C3-like member: 4 MiB, long matches at far distances
+        seg = gen.word_soup(60000, 9)
+        plains["c3_4MiB"] = (seg + blk[:5000]) * 64 + bytes(4 * 1024 * 1024 - 65000 * 64)
+    out = []
+    for name, plain in plains.items():
+        for tag, kinds, bt in (("dyn", ("dynamic",), 4000), ("fix", ("fixed",), 100000),
+                               ("mix", ("dynamic", "stored", "fixed"), 1500)):
+            if name == "c3_4MiB" and tag != "dyn":
+                continue
+            out.append(("d64_%s_%s" % (name, tag), d64enc.compress(plain, True, bt, kinds), -16, plain))
+        out.append(("d64_%s_f285" % name, d64enc.compress(plain, True, 5000, ("dynamic",), force285=True), -16, plain))
+        # the same tokens restricted to deflate's limits, decoded in both modes
+        comp = d64enc.compress(plain, False, 5000, ("dynamic", "fixed"))
+        out.append(("d32_%s" % name, comp, -15, plain))
+    return out
+
+
+def deflate64_damaged(count=200):
+    base = [c for c in deflate64_streams() if len(c[1]) > 8]
+    rnd = random.Random(6464)
+    out = []
+    for k in range(count):
+        name, data, wb, plain = base[rnd.randrange(len(base))]
+        out.append(("dmg%d_%s" % (k, name), gen.corrupt(data, 700 + k), wb, len(plain) + 100))
+    for name, data, wb, plain in base[::3]:
+        for cut in (1, len(data) // 3, len(data) - 3, len(data) - 1):
+            out.append(("trunc%d_%s" % (cut, name), data[:cut], wb, len(plain) + 10))
+        for cap in (0, 1, 258, 259, len(plain) // 2, len(plain) - 1):
+            out.append(("cap%d_%s" % (cap, name), data, wb, max(cap, 0)))
+        out.append(("asdeflate_%s" % name, data, -15 if wb == -16 else -16, len(plain) + 10))
+    return out

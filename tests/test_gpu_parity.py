@@ -187,3 +187,15 @@ def test_zstream_init_codes():
     assert api.lib.inflateInit2_(ctypes.byref(s), 15, b"2.0", ctypes.sizeof(s)) == -6      # Z_VERSION_ERROR
     assert api.lib.inflateInit2_(ctypes.byref(s), 15, b"1.3", 100) == -6
     assert api.lib.inflateEnd(ctypes.byref(s)) == -2                                     # never initialised
+
+
+def test_host_batch_pipelined(eng):
+    """Host-pointer batches cut into chunks whose copies and decodes overlap (option "chunks")."""
+    items = [(n, d, w, len(p) + 8) for n, d, w, p in cases.valid_streams()]
+    items += cases.damaged_streams(100)[:400]
+    try:
+        for k in (3, 8):
+            eng.set_option("chunks", k)
+            run_cases(eng, 0, items)
+    finally:
+        eng.set_option("chunks", 0)

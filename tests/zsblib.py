@@ -15,7 +15,8 @@ EMUL_DIR = os.path.join(ROOT, "tests", "emul")
 
 API_SYMBOLS = ["zsb_create", "zsb_destroy", "zsb_create_error", "zsb_last_error", "zsb_num_devices",
                "zsb_inflate_batch", "zsb_inflate_batch_device", "zsb_set_option", "zsb_get_option",
-               "zsb_last_launches", "zsb_plan_shards", "zsb_host_alloc", "zsb_host_free", "zsb_message"]
+               "zsb_last_launches", "zsb_plan_shards", "zsb_host_alloc", "zsb_host_free", "zsb_message",
+               "zsb_profile_read"]
 ZLIB_SYMBOLS = ["inflateInit_", "inflateInit2_", "inflate", "inflateEnd", "inflateReset", "inflateReset2",
                 "inflateResetKeep"]
 
@@ -69,6 +70,9 @@ def load_product():
     lib.zsb_host_free.argtypes = [ctypes.c_void_p]
     lib.zsb_message.restype = ctypes.c_char_p
     lib.zsb_message.argtypes = [ctypes.c_int]
+    lib.zsb_profile_read.restype = ctypes.c_long
+    lib.zsb_profile_read.argtypes = [ctypes.c_void_p, ctypes.c_int, ctypes.POINTER(ctypes.c_double),
+                                     ctypes.POINTER(ctypes.c_double)]
     return lib
 
 

@@ -200,16 +200,32 @@ static int run_lane(zsb_ctx *ctx, zsb_dev &dv, size_t n, const zsb_member *dm, z
         B.n = (uint32_t)cnt;
         B.counter = dv.counters;
         B.fixed_tab = dv.fixed_lane;
-        const size_t per_cta = (size_t)lane::WARPS * 32;
+        // one CTA per SM, with just the warps the slice needs so that a small slice spreads over all SMs
+        const size_t per_sm = (cnt + dv.sm_count - 1) / dv.sm_count;
+        const size_t warps = std::min<size_t>(lane::WARPS, std::max<size_t>(1, (per_sm + 31) / 32));
+        const size_t per_cta = warps * 32;
         unsigned grid = (unsigned)std::max<size_t>(1, std::min((cnt + per_cta - 1) / per_cta, (size_t)dv.sm_count));
-        k_lane<<<grid, lane::WARPS * 32, lane::SMEM, st>>>(B);
+        cudaEvent_t *pe = nullptr;
+        if (ctx->profile) {
+            if (dv.prof_used + 3 > dv.prof_ev.size()) {
+                const size_t old = dv.prof_ev.size();
+                dv.prof_ev.resize(old + 96);
+                for (size_t i = old; i < dv.prof_ev.size(); i++) CK(ctx, cudaEventCreate(&dv.prof_ev[i]));
+            }
+            pe = &dv.prof_ev[dv.prof_used];
+            dv.prof_used += 3;
+            CK(ctx, cudaEventRecord(pe[0], st));
+        }
+        k_lane<<<grid, (unsigned)per_cta, lane::SMEM, st>>>(B);
         ctx->launches++;
         CK(ctx, cudaGetLastError());
+        if (pe) CK(ctx, cudaEventRecord(pe[1], st));
         const size_t wpc = LZ_THREADS / 32;
         grid = (unsigned)std::max<size_t>(1, std::min((cnt + wpc - 1) / wpc, (size_t)dv.sm_count * dv.lz_occ));
         k_lz<<<grid, LZ_THREADS, 0, st>>>(B, dv.counters + 2);
         ctx->launches++;
         CK(ctx, cudaGetLastError());
+        if (pe) CK(ctx, cudaEventRecord(pe[2], st));
     }
     return 0;
 }
@@ -259,6 +275,7 @@ static int init_device(zsb_ctx *ctx, zsb_dev &dv, int device) {
     dv.sm_count = prop.multiProcessorCount;
     CK(ctx, cudaStreamCreateWithFlags(&dv.stream, cudaStreamNonBlocking));
     CK(ctx, cudaStreamCreateWithFlags(&dv.copy_stream, cudaStreamNonBlocking));
+    CK(ctx, cudaStreamCreateWithFlags(&dv.back_stream, cudaStreamNonBlocking));
     CK(ctx, cudaMalloc(&dv.fixed, STREAM_BYTES));
     CK(ctx, cudaMalloc(&dv.fixed_lane, lane::SLOT));
     CK(ctx, cudaMalloc(&dv.counters, 4 * sizeof(uint32_t)));
@@ -286,6 +303,9 @@ static void free_device(zsb_dev &dv) {
     cudaSetDevice(dv.device);
     if (dv.stream) cudaStreamDestroy(dv.stream);
     if (dv.copy_stream) cudaStreamDestroy(dv.copy_stream);
+    if (dv.back_stream) cudaStreamDestroy(dv.back_stream);
+    for (cudaEvent_t e : dv.pipe_ev) cudaEventDestroy(e);
+    dv.pipe_ev.clear();
     cudaFree(dv.fixed);
     cudaFree(dv.fixed_lane);
     cudaFree(dv.d_seq);
@@ -296,6 +316,8 @@ static void free_device(zsb_dev &dv) {
     cudaFree(dv.d_out);
     cudaFree(dv.d_desc);
     if (dv.h_desc) cudaFreeHost(dv.h_desc);
+    for (cudaEvent_t e : dv.prof_ev) cudaEventDestroy(e);
+    dv.prof_ev.clear();
 }
 
 extern "C" zsb_ctx *zsb_create(const int *devices, int ndev) {
@@ -349,6 +371,15 @@ extern "C" int zsb_set_option(zsb_ctx *ctx, const char *name, long value) {
         ctx->slab_bytes = (size_t)value;
         return 0;
     }
+    if (!strcmp(name, "profile")) {
+        ctx->profile = value != 0;
+        return 0;
+    }
+    if (!strcmp(name, "chunks")) {
+        if (value < 0 || value > 64) return ZSB_E_ARG;
+        ctx->chunks = (int)value;
+        return 0;
+    }
     if (!strcmp(name, "path")) {
         if (value < 0 || value > 2) return ZSB_E_ARG;
         ctx->path = (int)value;
@@ -366,9 +397,33 @@ extern "C" long zsb_get_option(const zsb_ctx *ctx, const char *name) {
     if (!strcmp(name, "lanes_per_member")) return ctx->lanes;
     if (!strcmp(name, "slab_bytes")) return (long)ctx->slab_bytes;
     if (!strcmp(name, "path")) return ctx->path;
+    if (!strcmp(name, "chunks")) return ctx->chunks;
     if (!strcmp(name, "seq_arena_bytes")) return (long)ctx->seq_arena_bytes;
     if (!strcmp(name, "sm_count")) return ctx->devs.empty() ? 0 : ctx->devs[0].sm_count;
     return ZSB_E_ARG;
+}
+
+// Sums the event-timed durations (ms) of the k_lane and k_lz launches recorded on device dev_index since
+// the last read (option "profile" = 1); waits for the last recorded event.  Returns the number of
+// launch pairs, or a negative error.
+extern "C" long zsb_profile_read(zsb_ctx *ctx, int dev_index, double *lane_ms, double *lz_ms) {
+    if (!ctx || dev_index < 0 || dev_index >= (int)ctx->devs.size()) return ZSB_E_ARG;
+    zsb_dev &dv = ctx->devs[dev_index];
+    double a = 0, b = 0;
+    long pairs = 0;
+    for (size_t i = 0; i + 3 <= dv.prof_used; i += 3) {
+        float t0 = 0, t1 = 0;
+        CK(ctx, cudaEventSynchronize(dv.prof_ev[i + 2]));
+        CK(ctx, cudaEventElapsedTime(&t0, dv.prof_ev[i], dv.prof_ev[i + 1]));
+        CK(ctx, cudaEventElapsedTime(&t1, dv.prof_ev[i + 1], dv.prof_ev[i + 2]));
+        a += t0;
+        b += t1;
+        pairs++;
+    }
+    dv.prof_used = 0;
+    if (lane_ms) *lane_ms = a;
+    if (lz_ms) *lz_ms = b;
+    return pairs;
 }
 
 extern "C" int zsb_inflate_batch_device(zsb_ctx *ctx, int dev_index, size_t n, const zsb_member *d_members,
@@ -444,9 +499,25 @@ static size_t layout_runs(const zsb_member *m, const std::vector<uint32_t> &idx,
     return total;
 }
 
-static void plan_layout(const zsb_member *m, Shard &sh) {
-    sh.in_span = layout_runs(m, sh.idx, false, 4095, sh.in_off, sh.in_runs);
-    sh.out_span = layout_runs(m, sh.idx, true, 0, sh.out_off, sh.out_runs);
+// Host-pointer batches are pipelined: a shard is cut into chunks of consecutive members and chunk c's
+// host->device copies (copy_stream), decode (stream) and device->host copies (back_stream) overlap
+// with the other chunks', so that for large batches the call costs about the slower PCIe direction.
+struct Chunk {
+    size_t first = 0, count = 0;       // range of the shard's member list
+    std::vector<uint32_t> idx;         // member indices of the range
+    std::vector<size_t> in_off, out_off;
+    std::vector<Run> in_runs, out_runs;
+    size_t in_base = 0, out_base = 0;  // where the chunk's spans start in the device arenas
+};
+
+static int choose_chunks(const zsb_ctx *ctx, const zsb_dev &dv, const zsb_member *m, const Shard &sh) {
+    if (ctx->chunks > 0) return (int)std::min<size_t>(ctx->chunks, std::max<size_t>(sh.idx.size(), 1));
+    size_t bytes = 0;
+    for (uint32_t i : sh.idx) bytes += m[i].in_len + m[i].out_cap;
+    // a chunk should still give every SM a warp of members and be worth a round of copies
+    const size_t by_members = sh.idx.size() / ((size_t)dv.sm_count * 48);
+    const size_t by_bytes = bytes / (128u << 20);
+    return (int)std::max<size_t>(1, std::min<size_t>(8, std::min(by_members, by_bytes)));
 }
 
 static int batch_host(zsb_ctx *ctx, size_t n, const zsb_member *m, zsb_result *r) {
@@ -471,44 +542,89 @@ static int batch_host(zsb_ctx *ctx, size_t n, const zsb_member *m, zsb_result *r
         const size_t k = sh.idx.size();
         if (!k) continue;
         CK(ctx, cudaSetDevice(dv.device));
-        plan_layout(m, sh);
+        const int K = choose_chunks(ctx, dv, m, sh);
+        std::vector<Chunk> chunks(K);
+        size_t in_total = 0, out_total = 0, seq_most = 0, cnt_most = 0;
+        for (int c = 0; c < K; c++) {
+            Chunk &ch = chunks[c];
+            ch.first = k * c / K;
+            ch.count = k * (c + 1) / K - ch.first;
+            ch.idx.assign(sh.idx.begin() + ch.first, sh.idx.begin() + ch.first + ch.count);
+            ch.in_base = in_total;
+            ch.out_base = out_total;
+            in_total += (layout_runs(m, ch.idx, false, 4095, ch.in_off, ch.in_runs) + 511) & ~(size_t)255;
+            out_total += (layout_runs(m, ch.idx, true, 0, ch.out_off, ch.out_runs) + 511) & ~(size_t)255;
+            uint64_t sq = 0;
+            for (uint32_t i : ch.idx) sq += seq_bound(m[i]);
+            seq_most = std::max<size_t>(seq_most, (size_t)std::min<uint64_t>(sq, ctx->seq_arena_bytes / sizeof(lane::seq_t)));
+            cnt_most = std::max(cnt_most, ch.count);
+        }
         int rc;
-        if ((rc = grow(ctx, dv.d_in, dv.d_in_cap, sh.in_span + 256))) return rc;
-        if ((rc = grow(ctx, dv.d_out, dv.d_out_cap, sh.out_span + 256))) return rc;
+        if ((rc = grow(ctx, dv.d_in, dv.d_in_cap, in_total + 256))) return rc;
+        if ((rc = grow(ctx, dv.d_out, dv.d_out_cap, out_total + 256))) return rc;
         const size_t desc_bytes = k * (sizeof(zsb_member) + sizeof(zsb_result) + sizeof(uint32_t)) + 64;
         if ((rc = grow(ctx, dv.d_desc, dv.d_desc_cap, desc_bytes))) return rc;
+        // scratch of the decode kernels, sized once for the largest chunk: growing it between chunks
+        // would free memory under the running pipeline
+        if ((rc = ensure_aux(ctx, dv, cnt_most))) return rc;
+        if ((rc = grow(ctx, dv.d_plan, dv.d_plan_cap, cnt_most * (sizeof(uint64_t) + sizeof(uint32_t)) + 64))) return rc;
+        if (ctx->path != 2 && (rc = grow(ctx, dv.d_seq, dv.d_seq_cap, seq_most * sizeof(lane::seq_t)))) return rc;
         if (desc_bytes > dv.h_desc_cap) {
             if (dv.h_desc) CK(ctx, cudaFreeHost(dv.h_desc));
             dv.h_desc = nullptr;
             CK(ctx, cudaHostAlloc(&dv.h_desc, desc_bytes + desc_bytes / 8, cudaHostAllocDefault));
             dv.h_desc_cap = desc_bytes + desc_bytes / 8;
         }
+        while (dv.pipe_ev.size() < (size_t)2 * K) {
+            cudaEvent_t e;
+            CK(ctx, cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
+            dv.pipe_ev.push_back(e);
+        }
         zsb_member *hm = (zsb_member *)dv.h_desc;
         zsb_result *hr = (zsb_result *)(hm + k);
         uint32_t *ho = (uint32_t *)(hr + k);
         zsb_member *dm = (zsb_member *)dv.d_desc;
         zsb_result *dr = (zsb_result *)(dm + k);
-        for (size_t j = 0; j < k; j++) {
-            const zsb_member &x = m[sh.idx[j]];
-            hm[j] = x;
-            hm[j].in = x.in ? dv.d_in + sh.in_off[j] : nullptr;
-            hm[j].out = x.out ? dv.d_out + sh.out_off[j] : nullptr;
-            if (x.in_len > 0xfffffff0ull || x.out_cap > 0xfffffff0ull) hm[j].window_bits = 1000;  // -> Z_STREAM_ERROR
-            ho[j] = (uint32_t)j;
+        for (int c = 0; c < K; c++) {
+            Chunk &ch = chunks[c];
+            zsb_member *hmc = hm + ch.first;
+            uint32_t *hoc = ho + ch.first;
+            for (size_t j = 0; j < ch.count; j++) {
+                const zsb_member &x = m[ch.idx[j]];
+                hmc[j] = x;
+                hmc[j].in = x.in ? dv.d_in + ch.in_base + ch.in_off[j] : nullptr;
+                hmc[j].out = x.out ? dv.d_out + ch.out_base + ch.out_off[j] : nullptr;
+                if (x.in_len > 0xfffffff0ull || x.out_cap > 0xfffffff0ull) hmc[j].window_bits = 1000;  // -> Z_STREAM_ERROR
+                hoc[j] = (uint32_t)j;
+            }
+            // largest first: the persistent decoder's lanes then finish together
+            std::stable_sort(hoc, hoc + ch.count, [&](uint32_t a, uint32_t b) {
+                return hmc[a].in_len + hmc[a].out_cap > hmc[b].in_len + hmc[b].out_cap;
+            });
         }
-        // largest first: the persistent decoder groups then finish together
-        std::stable_sort(ho, ho + k, [&](uint32_t a, uint32_t b) {
-            return hm[a].in_len + hm[a].out_cap > hm[b].in_len + hm[b].out_cap;
-        });
-        cudaStream_t st = dv.stream;
-        CK(ctx, cudaMemcpyAsync(dm, hm, k * sizeof(zsb_member), cudaMemcpyHostToDevice, st));
-        for (const Run &rn : sh.in_runs)
-            CK(ctx, cudaMemcpyAsync(dv.d_in + rn.dev_off, (const void *)rn.host, rn.len, cudaMemcpyHostToDevice, st));
-        if ((rc = run_device(ctx, dv, k, dm, dr, hm, ho, flags, st))) return rc;
-        CK(ctx, cudaMemcpyAsync(hr, dr, k * sizeof(zsb_result), cudaMemcpyDeviceToHost, st));
-        // whole buffers come back (bytes past total_out are unspecified by contract): no host sync needed
-        for (const Run &rn : sh.out_runs)
-            CK(ctx, cudaMemcpyAsync((void *)rn.host, dv.d_out + rn.dev_off, rn.len, cudaMemcpyDeviceToHost, st));
+        // the three stages of every chunk, each on its own stream
+        for (int c = 0; c < K; c++) {
+            Chunk &ch = chunks[c];
+            cudaEvent_t ev_in = dv.pipe_ev[2 * c], ev_dec = dv.pipe_ev[2 * c + 1];
+            CK(ctx, cudaMemcpyAsync(dm + ch.first, hm + ch.first, ch.count * sizeof(zsb_member), cudaMemcpyHostToDevice,
+                                    dv.copy_stream));
+            for (const Run &rn : ch.in_runs)
+                CK(ctx, cudaMemcpyAsync(dv.d_in + ch.in_base + rn.dev_off, (const void *)rn.host, rn.len,
+                                        cudaMemcpyHostToDevice, dv.copy_stream));
+            CK(ctx, cudaEventRecord(ev_in, dv.copy_stream));
+            CK(ctx, cudaStreamWaitEvent(dv.stream, ev_in, 0));
+            if ((rc = run_device(ctx, dv, ch.count, dm + ch.first, dr + ch.first, hm + ch.first, ho + ch.first, flags,
+                                 dv.stream)))
+                return rc;
+            CK(ctx, cudaEventRecord(ev_dec, dv.stream));
+            CK(ctx, cudaStreamWaitEvent(dv.back_stream, ev_dec, 0));
+            CK(ctx, cudaMemcpyAsync(hr + ch.first, dr + ch.first, ch.count * sizeof(zsb_result), cudaMemcpyDeviceToHost,
+                                    dv.back_stream));
+            // whole buffers come back (bytes past total_out are unspecified by contract): no host sync needed
+            for (const Run &rn : ch.out_runs)
+                CK(ctx, cudaMemcpyAsync((void *)rn.host, dv.d_out + ch.out_base + rn.dev_off, rn.len,
+                                        cudaMemcpyDeviceToHost, dv.back_stream));
+        }
     }
     for (int s = 0; s < nd; s++) {
         Shard &sh = shards[s];
@@ -516,6 +632,7 @@ static int batch_host(zsb_ctx *ctx, size_t n, const zsb_member *m, zsb_result *r
         const size_t k = sh.idx.size();
         if (!k) continue;
         CK(ctx, cudaSetDevice(dv.device));
+        CK(ctx, cudaStreamSynchronize(dv.back_stream));
         CK(ctx, cudaStreamSynchronize(dv.stream));
         zsb_result *hr = (zsb_result *)((zsb_member *)dv.h_desc + k);
         for (size_t j = 0; j < k; j++) r[sh.idx[j]] = hr[j];

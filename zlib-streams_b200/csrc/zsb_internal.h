@@ -10,7 +10,8 @@ namespace zsb { struct Aux; }
 struct zsb_dev {
     int device = 0;
     int sm_count = 0;
-    cudaStream_t stream = nullptr, copy_stream = nullptr;
+    cudaStream_t stream = nullptr, copy_stream = nullptr, back_stream = nullptr;   // decode, host->device, device->host
+    std::vector<cudaEvent_t> pipe_ev;  // per chunk of a host batch: inputs arrived, decoded
     uint16_t *fixed = nullptr;         // prebuilt fixed-code tables (one member slot, group path)
     uint8_t *fixed_lane = nullptr;     // the same in the lane path's slot format
     uint8_t *d_seq = nullptr;          // LZ sequence arena of the lane path
@@ -29,6 +30,9 @@ struct zsb_dev {
     size_t h_desc_cap = 0;
     bool configured[33] = {};
     int occ[33] = {};
+    // "profile" option: CUDA events around every decode-kernel launch, on the launching stream
+    std::vector<cudaEvent_t> prof_ev;  // 3 per lane-path slice: before k_lane, between, after k_lz
+    size_t prof_used = 0;
 };
 
 struct zsb_ctx {
@@ -37,6 +41,8 @@ struct zsb_ctx {
     int path = 0;                      // 0 auto, 1 lane path (k_lane + k_lz), 2 group path (k_inflate<G>)
     size_t seq_arena_bytes = 32ull << 30;   // most sequence scratch one slice of a batch may use
     size_t slab_bytes = 256u << 20;
+    int chunks = 0;                    // host batches: pipeline depth (0 = choose from the batch)
     long launches = 0;
+    int profile = 0;                   // 1: record per-kernel events (zsb_profile_read)
     char err[256] = "";
 };
