@@ -124,6 +124,7 @@ def main():
     ap.add_argument("--distinct", type=int, default=1024)
     ap.add_argument("--lanes", type=int, default=0, help="0 = lane path (k_lane + k_lz); else group path k_inflate<G>")
     ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--chunk-sweep", default="", help="comma list of pipeline depths to time the e2e leg with (diagnostic)")
     ap.add_argument("--no-cpu", action="store_true")
     args = ap.parse_args()
     if args.warmup < 3:
@@ -310,6 +311,17 @@ def main():
             t = torch.tensor([es], device=dev)
             dist.all_reduce(t, op=dist.ReduceOp.MAX)
             es = float(t.item())
+        if args.chunk_sweep:
+            sweep = {}
+            for kk in [int(x) for x in args.chunk_sweep.split(",")]:
+                eng.set_option("chunks", kk)
+                e2e_step()
+                t0 = time.perf_counter()
+                for _ in range(2):
+                    e2e_step()
+                sweep[kk] = (time.perf_counter() - t0) / 2 * 1e3
+            eng.set_option("chunks", 0)
+            out["e2e_chunk_sweep_ms"] = sweep
         r2 = hres.view(res.dtype)
         got = ctypes.string_at(h_out + (n - 1) * MEMBER_BYTES, MEMBER_BYTES)
         if not ((r2["ret"] == 1).all() and (r2["tout"] == MEMBER_BYTES).all() and

@@ -102,12 +102,16 @@ ZSB_DEV void lane_copy16(uint8_t *dst, const uint8_t *src, uint32_t n) {
 template <int W>
 ZSB_DEV void resolve_member(uint8_t *out, const uint8_t *in, const seq_t *seq, uint32_t nseq, int lane) {
     uint32_t base = 0;
+    seq_t qn;                                 // the next trip's sequence is requested one trip ahead
+    qn.lo = 0;
+    qn.hi = 0;
+    if ((uint32_t)lane < nseq) qn = seq[lane];
     for (uint32_t c = 0; c < nseq; c += W) {
-        const uint32_t t = c + lane;
-        seq_t q;
-        q.lo = 0;
-        q.hi = 0;
-        if (t < nseq) q = seq[t];
+        const seq_t q = qn;
+        const uint32_t tn = c + W + lane;
+        qn.lo = 0;
+        qn.hi = 0;
+        if (tn < nseq) qn = seq[tn];
         const uint32_t nlit = (q.lo >> lane::Q_NLIT_SHIFT) & 3u;
         const bool is_match = (q.lo & lane::Q_MATCH) != 0, is_raw = (q.lo & lane::Q_RAW) != 0;
         uint32_t mlen = 0;
