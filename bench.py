@@ -15,6 +15,10 @@ import argparse
 import ctypes
 import json
 import os
+
+# more hardware work queues than the default 8, so that every chunk of a pipelined host batch (the e2e leg)
+# decodes on a stream of its own; must be in the environment before CUDA starts
+os.environ.setdefault("CUDA_DEVICE_MAX_CONNECTIONS", "32")
 import subprocess
 import sys
 import threading
@@ -124,6 +128,7 @@ def main():
     ap.add_argument("--distinct", type=int, default=1024)
     ap.add_argument("--lanes", type=int, default=0, help="0 = lane path (k_lane + k_lz); else group path k_inflate<G>")
     ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--small-ctas", action="store_true", help="diagnostic: device-resident leg with k_lane in small CTAs")
     ap.add_argument("--chunk-sweep", default="", help="comma list of pipeline depths to time the e2e leg with (diagnostic)")
     ap.add_argument("--no-cpu", action="store_true")
     args = ap.parse_args()
@@ -189,6 +194,8 @@ def main():
         eng.set_option("lanes_per_member", args.lanes)
     else:
         eng.set_option("path", 1)
+        if args.small_ctas:
+            eng.set_option("small_ctas", 1)
     lib = eng.lib
 
     def descriptors(in_base, out_base):

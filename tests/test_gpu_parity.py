@@ -194,8 +194,14 @@ def test_host_batch_pipelined(eng):
     items = [(n, d, w, len(p) + 8) for n, d, w, p in cases.valid_streams()]
     items += cases.damaged_streams(100)[:400]
     try:
-        for k in (3, 8):
+        for k in (3, 8, 40):
             eng.set_option("chunks", k)
             run_cases(eng, 0, items)
+        # a small sequence arena: the chunks share fewer regions / streams and decode in slices
+        arena = eng.get_option("seq_arena_bytes")
+        eng.set_option("seq_arena_bytes", 1 << 20)
+        eng.set_option("chunks", 8)
+        run_cases(eng, 0, items)
+        eng.set_option("seq_arena_bytes", arena)
     finally:
         eng.set_option("chunks", 0)

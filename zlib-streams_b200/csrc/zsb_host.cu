@@ -3,6 +3,7 @@
 // There is no CPU decode path in this library: every member is decoded by k_inflate on the GPU.
 #include <cuda_runtime.h>
 #include <algorithm>
+#include <chrono>
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
@@ -14,6 +15,8 @@
 using namespace zsb;
 
 static thread_local char g_create_err[256] = "";
+constexpr int MAX_CHUNKS_DEV = 64;
+constexpr int BASE_PIPE_STREAMS = 6;    // decode streams that, with the two copy streams, fit the default 8 hardware queues      // sets of work counters per device (option "chunks" <= 64)
 
 #define CK(ctx, call)                                                                              \
     do {                                                                                           \
@@ -83,9 +86,25 @@ extern "C" int zsb_plan_shards(size_t n, const uint64_t *cost, int nshards, int3
     return 0;
 }
 
+// Scratch of one decode (run_device).  NULL = the device's own buffers, grown as needed: only one such
+// decode may be in flight per device.  The chunks of a pipelined host batch run concurrently on several
+// streams, so each gets a preallocated set.
+struct Scratch {
+    Aux *aux;              // n entries
+    uint8_t *plan;         // n * 12 + 64 bytes: sequence offsets (u64) + slot order (u32)
+    uint8_t *seq;          // sequence arena
+    size_t seq_bytes;
+    uint32_t *counters;    // 4 work counters
+    const std::vector<size_t> *cuts;   // lane path: slices planned by the caller (lane_plan), who has also sent
+                           // the slot order and the sequence offsets to `plan`: run_device then issues no copy
+                           // of its own (it would queue behind every input copy already submitted)
+    bool small_ctas;       // k_lane in CTAs of lane::PIPE_WARPS warps, one per 32*PIPE_WARPS members, so that
+                           // launches on different streams share the SMs
+};
+
 template <int G>
 static int launch_inflate(zsb_ctx *ctx, zsb_dev &dv, size_t n, const zsb_member *dm, zsb_result *dr,
-                          const uint32_t *dorder, cudaStream_t st) {
+                          const uint32_t *dorder, cudaStream_t st, const Scratch *sc) {
     using GG = Geo<G>;
     auto kern = k_inflate<G>;
     if (!dv.configured[G]) {
@@ -102,7 +121,7 @@ static int launch_inflate(zsb_ctx *ctx, zsb_dev &dv, size_t n, const zsb_member 
     size_t want = (n + GG::members - 1) / GG::members;
     size_t cap = (size_t)dv.sm_count * dv.occ[G];
     unsigned grid = (unsigned)std::max<size_t>(1, std::min(want, cap));
-    kern<<<grid, GG::threads, GG::smem, st>>>(dm, dr, dv.aux, dorder, (uint32_t)n, dv.counters, dv.fixed);
+    kern<<<grid, GG::threads, GG::smem, st>>>(dm, dr, sc ? sc->aux : dv.aux, dorder, (uint32_t)n, sc ? sc->counters : dv.counters, dv.fixed);
     ctx->launches++;
     CK(ctx, cudaGetLastError());
     return 0;
@@ -138,39 +157,25 @@ static size_t zsb_seq_bound_sizes(size_t in_len, size_t out_cap) {
 }
 
 static int run_group(zsb_ctx *ctx, zsb_dev &dv, size_t n, const zsb_member *dm, zsb_result *dr,
-                     const uint32_t *dorder, cudaStream_t st) {
-    CK(ctx, cudaMemsetAsync(dv.counters, 0, 4 * sizeof(uint32_t), st));
+                     const uint32_t *dorder, cudaStream_t st, const Scratch *sc) {
+    CK(ctx, cudaMemsetAsync(sc ? sc->counters : dv.counters, 0, 4 * sizeof(uint32_t), st));
     switch (ctx->lanes) {
-    case 1: return launch_inflate<1>(ctx, dv, n, dm, dr, dorder, st);
-    case 2: return launch_inflate<2>(ctx, dv, n, dm, dr, dorder, st);
-    case 4: return launch_inflate<4>(ctx, dv, n, dm, dr, dorder, st);
-    case 8: return launch_inflate<8>(ctx, dv, n, dm, dr, dorder, st);
-    case 16: return launch_inflate<16>(ctx, dv, n, dm, dr, dorder, st);
-    default: return launch_inflate<32>(ctx, dv, n, dm, dr, dorder, st);
+    case 1: return launch_inflate<1>(ctx, dv, n, dm, dr, dorder, st, sc);
+    case 2: return launch_inflate<2>(ctx, dv, n, dm, dr, dorder, st, sc);
+    case 4: return launch_inflate<4>(ctx, dv, n, dm, dr, dorder, st, sc);
+    case 8: return launch_inflate<8>(ctx, dv, n, dm, dr, dorder, st, sc);
+    case 16: return launch_inflate<16>(ctx, dv, n, dm, dr, dorder, st, sc);
+    default: return launch_inflate<32>(ctx, dv, n, dm, dr, dorder, st, sc);
     }
 }
 
-// lane path: k_lane + k_lz over slices of the slot order whose sequence scratch fits the arena
-static int run_lane(zsb_ctx *ctx, zsb_dev &dv, size_t n, const zsb_member *dm, zsb_result *dr,
-                    const zsb_member *hm, const uint32_t *horder, const uint32_t *dorder, uint64_t *dseqoff,
-                    cudaStream_t st) {
-    if (!dv.lane_configured) {
-        CK(ctx, cudaFuncSetAttribute(k_lane, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)lane::SMEM));
-        int occ = 0;
-        CK(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, k_lane, lane::WARPS * 32, lane::SMEM));
-        if (occ < 1) {
-            snprintf(ctx->err, sizeof ctx->err, "k_lane does not fit an SM");
-            return ZSB_E_CUDA;
-        }
-        CK(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&dv.lz_occ, k_lz, LZ_THREADS, 0));
-        if (dv.lz_occ < 1) dv.lz_occ = 1;
-        dv.lane_configured = true;
-    }
-    // per-slot sequence offsets, slices cut where the arena would overflow
-    std::vector<uint64_t> off(n);
-    std::vector<size_t> cuts;          // slice = [cuts[k], cuts[k+1])
-    const uint64_t arena_seqs = std::max<uint64_t>(ctx->seq_arena_bytes / sizeof(lane::seq_t), 1);
+// Per-slot sequence offsets (off[n]) and the slices [cuts[k], cuts[k+1]) of the slot order, cut where the
+// arena of arena_seqs sequences would overflow.  Returns the most sequences a slice needs.
+static uint64_t lane_plan(const zsb_member *hm, const uint32_t *horder, size_t n, uint64_t arena_seqs, uint64_t *off,
+                          std::vector<size_t> &cuts) {
+    if (arena_seqs < 1) arena_seqs = 1;
     uint64_t run = 0, most = 0;
+    cuts.clear();
     cuts.push_back(0);
     for (size_t s = 0; s < n; s++) {
         const uint64_t b = seq_bound(hm[horder ? horder[s] : s]);
@@ -183,28 +188,73 @@ static int run_lane(zsb_ctx *ctx, zsb_dev &dv, size_t n, const zsb_member *dm, z
         most = std::max(most, run);
     }
     cuts.push_back(n);
-    int rc;
-    if ((rc = grow(ctx, dv.d_seq, dv.d_seq_cap, (size_t)most * sizeof(lane::seq_t)))) return rc;
-    CK(ctx, cudaMemcpyAsync(dseqoff, off.data(), n * sizeof(uint64_t), cudaMemcpyHostToDevice, st));
+    return most;
+}
+
+// lane path: k_lane + k_lz over slices of the slot order whose sequence scratch fits the arena
+static int run_lane(zsb_ctx *ctx, zsb_dev &dv, size_t n, const zsb_member *dm, zsb_result *dr,
+                    const zsb_member *hm, const uint32_t *horder, const uint32_t *dorder, uint64_t *dseqoff,
+                    cudaStream_t st, const Scratch *sc) {
+    if (!dv.lane_configured) {
+        CK(ctx, cudaFuncSetAttribute(k_lane, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)lane::SMEM));
+        // all of the SM's memory as shared memory also for the small CTAs (the default carve-out fits fewer of them)
+        CK(ctx, cudaFuncSetAttribute(k_lane, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared));
+        int occ = 0;
+        CK(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, k_lane, lane::WARPS * 32, lane::SMEM));
+        if (occ < 1) {
+            snprintf(ctx->err, sizeof ctx->err, "k_lane does not fit an SM");
+            return ZSB_E_CUDA;
+        }
+        CK(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&dv.lane_small_occ, k_lane, lane::PIPE_WARPS * 32,
+                                                              lane::smem_for(lane::PIPE_WARPS)));
+        CK(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&dv.lz_occ, k_lz, LZ_THREADS, 0));
+        if (dv.lz_occ < 1) dv.lz_occ = 1;
+        dv.lane_configured = true;
+    }
+    // per-slot sequence offsets, slices cut where the arena would overflow
+    std::vector<uint64_t> off_own;
+    std::vector<size_t> cuts_own;
+    const std::vector<size_t> *pcuts = sc ? sc->cuts : nullptr;
+    uint32_t *counters = sc ? sc->counters : dv.counters;
+    if (!pcuts) {          // not planned by the caller: plan here and send the offsets on this stream
+        off_own.resize(n);
+        const uint64_t most = lane_plan(hm, horder, n, (sc ? sc->seq_bytes : ctx->seq_arena_bytes) / sizeof(lane::seq_t),
+                                        off_own.data(), cuts_own);
+        int rc;
+        if (!sc && (rc = grow(ctx, dv.d_seq, dv.d_seq_cap, (size_t)most * sizeof(lane::seq_t)))) return rc;
+        // (a pageable source is staged by the runtime before cudaMemcpyAsync returns, so off_own may go)
+        CK(ctx, cudaMemcpyAsync(dseqoff, off_own.data(), n * sizeof(uint64_t), cudaMemcpyHostToDevice, st));
+        pcuts = &cuts_own;
+    }
+    const std::vector<size_t> &cuts = *pcuts;
     for (size_t k = 0; k + 1 < cuts.size(); k++) {
         const size_t first = cuts[k], cnt = cuts[k + 1] - cuts[k];
-        CK(ctx, cudaMemsetAsync(dv.counters, 0, 4 * sizeof(uint32_t), st));
+        // (a planned chunk's counters were zeroed by the caller ahead of its input copies)
+        if (!(sc && sc->cuts) || k > 0) CK(ctx, cudaMemsetAsync(counters, 0, 4 * sizeof(uint32_t), st));
         lane::Batch B;
         B.members = dm;
         B.results = dr;
-        B.aux = dv.aux;
+        B.aux = sc ? sc->aux : dv.aux;
         B.order = dorder + first;
         B.seq_off = dseqoff + first;
-        B.seq_base = (lane::seq_t *)dv.d_seq;
+        B.seq_base = (lane::seq_t *)(sc ? sc->seq : dv.d_seq);
         B.hist = nullptr;
         B.n = (uint32_t)cnt;
-        B.counter = dv.counters;
+        B.counter = counters;
         B.fixed_tab = dv.fixed_lane;
-        // one CTA per SM, with just the warps the slice needs so that a small slice spreads over all SMs
-        const size_t per_sm = (cnt + dv.sm_count - 1) / dv.sm_count;
-        const size_t warps = std::min<size_t>(lane::WARPS, std::max<size_t>(1, (per_sm + 31) / 32));
-        const size_t per_cta = warps * 32;
-        unsigned grid = (unsigned)std::max<size_t>(1, std::min((cnt + per_cta - 1) / per_cta, (size_t)dv.sm_count));
+        size_t warps, per_cta;
+        unsigned grid;
+        if ((sc && sc->small_ctas) || ctx->force_small_ctas) {
+            warps = lane::PIPE_WARPS;
+            per_cta = warps * 32;
+            grid = (unsigned)std::max<size_t>(1, std::min((cnt + per_cta - 1) / per_cta, (size_t)dv.sm_count * dv.lane_small_occ));
+        } else {
+            // one CTA per SM, with just the warps the slice needs so that a small slice spreads over all SMs
+            const size_t per_sm = (cnt + dv.sm_count - 1) / dv.sm_count;
+            warps = std::min<size_t>(lane::WARPS, std::max<size_t>(1, (per_sm + 31) / 32));
+            per_cta = warps * 32;
+            grid = (unsigned)std::max<size_t>(1, std::min((cnt + per_cta - 1) / per_cta, (size_t)dv.sm_count));
+        }
         cudaEvent_t *pe = nullptr;
         if (ctx->profile) {
             if (dv.prof_used + 3 > dv.prof_ev.size()) {
@@ -216,13 +266,13 @@ static int run_lane(zsb_ctx *ctx, zsb_dev &dv, size_t n, const zsb_member *dm, z
             dv.prof_used += 3;
             CK(ctx, cudaEventRecord(pe[0], st));
         }
-        k_lane<<<grid, (unsigned)per_cta, lane::SMEM, st>>>(B);
+        k_lane<<<grid, (unsigned)per_cta, lane::smem_for(warps), st>>>(B);
         ctx->launches++;
         CK(ctx, cudaGetLastError());
         if (pe) CK(ctx, cudaEventRecord(pe[1], st));
         const size_t wpc = LZ_THREADS / 32;
         grid = (unsigned)std::max<size_t>(1, std::min((cnt + wpc - 1) / wpc, (size_t)dv.sm_count * dv.lz_occ));
-        k_lz<<<grid, LZ_THREADS, 0, st>>>(B, dv.counters + 2);
+        k_lz<<<grid, LZ_THREADS, 0, st>>>(B, counters + 2);
         ctx->launches++;
         CK(ctx, cudaGetLastError());
         if (pe) CK(ctx, cudaEventRecord(pe[2], st));
@@ -232,29 +282,31 @@ static int run_lane(zsb_ctx *ctx, zsb_dev &dv, size_t n, const zsb_member *dm, z
 
 // dm/dr: device arrays; hm: host copy of the descriptors; horder: host slot order (NULL = identity)
 static int run_device(zsb_ctx *ctx, zsb_dev &dv, size_t n, const zsb_member *dm, zsb_result *dr,
-                      const zsb_member *hm, const uint32_t *horder, unsigned flags, cudaStream_t st) {
+                      const zsb_member *hm, const uint32_t *horder, unsigned flags, cudaStream_t st,
+                      const Scratch *sc = nullptr) {
     if (n == 0) return 0;
     if (n > 0xffffff00ull) return ZSB_E_ARG;
-    int rc = ensure_aux(ctx, dv, n);
-    if (rc) return rc;
+    int rc = 0;
+    if (!sc && (rc = ensure_aux(ctx, dv, n))) return rc;
     // slot order and sequence offsets travel in one per-call plan buffer
     const size_t plan_bytes = n * (sizeof(uint64_t) + sizeof(uint32_t)) + 64;
-    if ((rc = grow(ctx, dv.d_plan, dv.d_plan_cap, plan_bytes))) return rc;
-    uint64_t *dseqoff = (uint64_t *)dv.d_plan;
+    if (!sc && (rc = grow(ctx, dv.d_plan, dv.d_plan_cap, plan_bytes))) return rc;
+    uint64_t *dseqoff = (uint64_t *)(sc ? sc->plan : dv.d_plan);
     uint32_t *dorder = (uint32_t *)(dseqoff + n);
     std::vector<uint32_t> ident;
     if (!horder) {
         ident.resize(n);
         for (size_t i = 0; i < n; i++) ident[i] = (uint32_t)i;
     }
-    CK(ctx, cudaMemcpyAsync(dorder, horder ? horder : ident.data(), n * sizeof(uint32_t), cudaMemcpyHostToDevice, st));
+    if (!(sc && sc->cuts))
+        CK(ctx, cudaMemcpyAsync(dorder, horder ? horder : ident.data(), n * sizeof(uint32_t), cudaMemcpyHostToDevice, st));
     const bool use_lane = ctx->path == 1 || (ctx->path == 0);
-    if (use_lane) rc = run_lane(ctx, dv, n, dm, dr, hm, horder, dorder, dseqoff, st);
-    else rc = run_group(ctx, dv, n, dm, dr, dorder, st);
+    if (use_lane) rc = run_lane(ctx, dv, n, dm, dr, hm, horder, dorder, dseqoff, st, sc);
+    else rc = run_group(ctx, dv, n, dm, dr, dorder, st, sc);
     if (rc) return rc;
     if (!(flags & ZSB_RAW_ONLY)) {
         unsigned grid = (unsigned)std::min<size_t>(n, (size_t)dv.sm_count * 8);
-        k_check<<<grid, CHK_THREADS, 0, st>>>(dm, dr, dv.aux, (uint32_t)n, dv.counters + 1);
+        k_check<<<grid, CHK_THREADS, 0, st>>>(dm, dr, sc ? sc->aux : dv.aux, (uint32_t)n, (sc ? sc->counters : dv.counters) + 1);
         ctx->launches++;
         CK(ctx, cudaGetLastError());
     }
@@ -276,9 +328,19 @@ static int init_device(zsb_ctx *ctx, zsb_dev &dv, int device) {
     CK(ctx, cudaStreamCreateWithFlags(&dv.stream, cudaStreamNonBlocking));
     CK(ctx, cudaStreamCreateWithFlags(&dv.copy_stream, cudaStreamNonBlocking));
     CK(ctx, cudaStreamCreateWithFlags(&dv.back_stream, cudaStreamNonBlocking));
+    // The decode streams of pipelined host batches.  Streams share the device's hardware work queues
+    // (CUDA_DEVICE_MAX_CONNECTIONS, 8 unless the process raised it before CUDA started), and two streams
+    // on one queue wait for each other.  Created back to back, these eight streams get eight different
+    // queues; with more queues available a batch may use more decode streams (pipe_stream_limit).
+    dv.pipe_streams.push_back(dv.stream);
+    for (int i = 1; i < BASE_PIPE_STREAMS; i++) {
+        cudaStream_t st;
+        CK(ctx, cudaStreamCreateWithFlags(&st, cudaStreamNonBlocking));
+        dv.pipe_streams.push_back(st);
+    }
     CK(ctx, cudaMalloc(&dv.fixed, STREAM_BYTES));
     CK(ctx, cudaMalloc(&dv.fixed_lane, lane::SLOT));
-    CK(ctx, cudaMalloc(&dv.counters, 4 * sizeof(uint32_t)));
+    CK(ctx, cudaMalloc(&dv.counters, 4 * MAX_CHUNKS_DEV * sizeof(uint32_t)));
     CrcConsts cc;
     cc.x2n[0] = 0x40000000u;
     for (int k = 1; k < 40; k++) cc.x2n[k] = gf2_mul(cc.x2n[k - 1], cc.x2n[k - 1]);
@@ -304,6 +366,8 @@ static void free_device(zsb_dev &dv) {
     if (dv.stream) cudaStreamDestroy(dv.stream);
     if (dv.copy_stream) cudaStreamDestroy(dv.copy_stream);
     if (dv.back_stream) cudaStreamDestroy(dv.back_stream);
+    for (size_t i = 1; i < dv.pipe_streams.size(); i++) cudaStreamDestroy(dv.pipe_streams[i]);   // [0] is dv.stream
+    dv.pipe_streams.clear();
     for (cudaEvent_t e : dv.pipe_ev) cudaEventDestroy(e);
     dv.pipe_ev.clear();
     cudaFree(dv.fixed);
@@ -378,6 +442,10 @@ extern "C" int zsb_set_option(zsb_ctx *ctx, const char *name, long value) {
     if (!strcmp(name, "chunks")) {
         if (value < 0 || value > 64) return ZSB_E_ARG;
         ctx->chunks = (int)value;
+        return 0;
+    }
+    if (!strcmp(name, "small_ctas")) {        // diagnostic: k_lane in the small CTAs of the pipelined host path
+        ctx->force_small_ctas = value != 0;
         return 0;
     }
     if (!strcmp(name, "path")) {
@@ -502,6 +570,13 @@ static size_t layout_runs(const zsb_member *m, const std::vector<uint32_t> &idx,
 // Host-pointer batches are pipelined: a shard is cut into chunks of consecutive members and chunk c's
 // host->device copies (copy_stream), decode (stream) and device->host copies (back_stream) overlap
 // with the other chunks', so that for large batches the call costs about the slower PCIe direction.
+constexpr int MAX_CHUNKS = 32;
+// decode streams a pipelined host batch may use: the hardware queues left beside the two copy streams
+static int pipe_stream_limit() {
+    const char *e = getenv("CUDA_DEVICE_MAX_CONNECTIONS");
+    const int conn = e ? atoi(e) : 8;
+    return std::max(BASE_PIPE_STREAMS, std::min(conn, 32) - 2);
+}
 struct Chunk {
     size_t first = 0, count = 0;       // range of the shard's member list
     std::vector<uint32_t> idx;         // member indices of the range
@@ -514,15 +589,20 @@ static int choose_chunks(const zsb_ctx *ctx, const zsb_dev &dv, const zsb_member
     if (ctx->chunks > 0) return (int)std::min<size_t>(ctx->chunks, std::max<size_t>(sh.idx.size(), 1));
     size_t bytes = 0;
     for (uint32_t i : sh.idx) bytes += m[i].in_len + m[i].out_cap;
-    // a chunk should still give every SM a warp of members and be worth a round of copies
-    // (a member decodes at a fixed pace however few are in flight, so many small chunks only add decode time:
-    // measured on C2, 65,536 x 64 KiB: 1 chunk 149 ms, 2: 138, 4: 124, 8: 147, 16: 232)
-    const size_t by_members = sh.idx.size() / ((size_t)dv.sm_count * 96);
-    const size_t by_bytes = bytes / (256u << 20);
-    return (int)std::max<size_t>(1, std::min<size_t>(4, std::min(by_members, by_bytes)));
+    // A member decodes at a fixed pace however few are in flight (one lane each), so the chunks' decodes
+    // must overlap each other: every chunk has its own stream and k_lane runs in small CTAs that share the
+    // SMs (Scratch::small_ctas).  A chunk is then only bounded below by the cost of its ~12 API calls.
+    // Every stream decodes its chunks one after the other, so at least two rounds of chunks keep the copy
+    // engines busy while a round decodes.
+    (void)dv;
+    const size_t by_members = sh.idx.size() / 2048;
+    const size_t by_bytes = bytes / (128u << 20);
+    const size_t by_streams = (size_t)std::min(MAX_CHUNKS, 2 * pipe_stream_limit());
+    return (int)std::max<size_t>(1, std::min(by_streams, std::min(by_members, by_bytes)));
 }
 
 static int batch_host(zsb_ctx *ctx, size_t n, const zsb_member *m, zsb_result *r) {
+    const auto t_call = std::chrono::steady_clock::now();
     const int nd = (int)ctx->devs.size();
     std::vector<int32_t> shard_of(n, 0);
     if (nd > 1) {
@@ -546,7 +626,9 @@ static int batch_host(zsb_ctx *ctx, size_t n, const zsb_member *m, zsb_result *r
         CK(ctx, cudaSetDevice(dv.device));
         const int K = choose_chunks(ctx, dv, m, sh);
         std::vector<Chunk> chunks(K);
-        size_t in_total = 0, out_total = 0, seq_most = 0, cnt_most = 0;
+        std::vector<uint64_t> seq_need(K);
+        size_t in_total = 0, out_total = 0;
+        const uint64_t arena_seqs = ctx->seq_arena_bytes / sizeof(lane::seq_t);
         for (int c = 0; c < K; c++) {
             Chunk &ch = chunks[c];
             ch.first = k * c / K;
@@ -558,35 +640,71 @@ static int batch_host(zsb_ctx *ctx, size_t n, const zsb_member *m, zsb_result *r
             out_total += (layout_runs(m, ch.idx, true, 0, ch.out_off, ch.out_runs) + 511) & ~(size_t)255;
             uint64_t sq = 0;
             for (uint32_t i : ch.idx) sq += seq_bound(m[i]);
-            seq_most = std::max<size_t>(seq_most, (size_t)std::min<uint64_t>(sq, ctx->seq_arena_bytes / sizeof(lane::seq_t)));
-            cnt_most = std::max(cnt_most, ch.count);
+            seq_need[c] = std::min<uint64_t>(sq, arena_seqs);
+        }
+        // Chunk c decodes on stream c % NS with sequence region c % NS; the regions together stay inside
+        // the arena (fewer streams if they would not).
+        int NS = std::min(K, pipe_stream_limit());
+        std::vector<uint64_t> region;
+        for (;; NS = (NS + 1) / 2) {
+            region.assign(NS, 0);
+            for (int c = 0; c < K; c++) region[c % NS] = std::max(region[c % NS], seq_need[c]);
+            uint64_t sum = 0;
+            for (uint64_t v : region) sum += v;
+            if (sum <= arena_seqs || NS == 1) break;
+        }
+        std::vector<uint64_t> region_off(NS, 0);
+        uint64_t seq_total = 0;
+        for (int q = 0; q < NS; q++) {
+            region_off[q] = seq_total;
+            seq_total += (region[q] + 31) & ~(uint64_t)31;
         }
         int rc;
         if ((rc = grow(ctx, dv.d_in, dv.d_in_cap, in_total + 256))) return rc;
         if ((rc = grow(ctx, dv.d_out, dv.d_out_cap, out_total + 256))) return rc;
-        const size_t desc_bytes = k * (sizeof(zsb_member) + sizeof(zsb_result) + sizeof(uint32_t)) + 64;
+        const size_t desc_bytes = k * (sizeof(zsb_member) + sizeof(zsb_result)) + 64;
         if ((rc = grow(ctx, dv.d_desc, dv.d_desc_cap, desc_bytes))) return rc;
-        // scratch of the decode kernels, sized once for the largest chunk: growing it between chunks
+        // scratch of the decode kernels, allocated before anything is enqueued: growing it between chunks
         // would free memory under the running pipeline
-        if ((rc = ensure_aux(ctx, dv, cnt_most))) return rc;
-        if ((rc = grow(ctx, dv.d_plan, dv.d_plan_cap, cnt_most * (sizeof(uint64_t) + sizeof(uint32_t)) + 64))) return rc;
-        if (ctx->path != 2 && (rc = grow(ctx, dv.d_seq, dv.d_seq_cap, seq_most * sizeof(lane::seq_t)))) return rc;
-        if (desc_bytes > dv.h_desc_cap) {
+        if ((rc = ensure_aux(ctx, dv, k))) return rc;
+        if ((rc = grow(ctx, dv.d_plan, dv.d_plan_cap, k * (sizeof(uint64_t) + sizeof(uint32_t)) + (size_t)K * 64))) return rc;
+        if (ctx->path != 2 && (rc = grow(ctx, dv.d_seq, dv.d_seq_cap, (size_t)seq_total * sizeof(lane::seq_t)))) return rc;
+        const size_t hdesc_bytes = k * (sizeof(zsb_member) + sizeof(zsb_result) + sizeof(uint64_t) + sizeof(uint32_t)) + 64;
+        if (hdesc_bytes > dv.h_desc_cap) {
             if (dv.h_desc) CK(ctx, cudaFreeHost(dv.h_desc));
             dv.h_desc = nullptr;
-            CK(ctx, cudaHostAlloc(&dv.h_desc, desc_bytes + desc_bytes / 8, cudaHostAllocDefault));
-            dv.h_desc_cap = desc_bytes + desc_bytes / 8;
+            CK(ctx, cudaHostAlloc(&dv.h_desc, hdesc_bytes + hdesc_bytes / 8, cudaHostAllocDefault));
+            dv.h_desc_cap = hdesc_bytes + hdesc_bytes / 8;
         }
         while (dv.pipe_ev.size() < (size_t)2 * K) {
             cudaEvent_t e;
             CK(ctx, cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
             dv.pipe_ev.push_back(e);
         }
+        while (dv.pipe_streams.size() < (size_t)NS) {
+            cudaStream_t st;
+            CK(ctx, cudaStreamCreateWithFlags(&st, cudaStreamNonBlocking));
+            dv.pipe_streams.push_back(st);
+        }
+        // ZSB_TRACE=1: per-chunk timeline (inputs arrived, decoded, outputs back; ms since the first copy) on stderr
+        static const bool trace = getenv("ZSB_TRACE") != nullptr;
+        std::vector<cudaEvent_t> tev;
+        if (trace) {
+            tev.resize(3 * K + 1);
+            for (auto &e : tev) CK(ctx, cudaEventCreate(&e));
+            CK(ctx, cudaEventRecord(tev[3 * K], dv.copy_stream));
+        }
         zsb_member *hm = (zsb_member *)dv.h_desc;
         zsb_result *hr = (zsb_result *)(hm + k);
-        uint32_t *ho = (uint32_t *)(hr + k);
+        uint64_t *hs = (uint64_t *)(hr + k);
+        uint32_t *ho = (uint32_t *)(hs + k);
         zsb_member *dm = (zsb_member *)dv.d_desc;
         zsb_result *dr = (zsb_result *)(dm + k);
+        // the three stages of every chunk: inputs on copy_stream, decode on the chunk's stream, results and
+        // outputs on back_stream
+        size_t plan_off = 0;
+        std::vector<std::vector<size_t>> cuts_of(K);
+        CK(ctx, cudaMemsetAsync(dv.counters, 0, 4 * (size_t)K * sizeof(uint32_t), dv.copy_stream));
         for (int c = 0; c < K; c++) {
             Chunk &ch = chunks[c];
             zsb_member *hmc = hm + ch.first;
@@ -599,26 +717,39 @@ static int batch_host(zsb_ctx *ctx, size_t n, const zsb_member *m, zsb_result *r
                 if (x.in_len > 0xfffffff0ull || x.out_cap > 0xfffffff0ull) hmc[j].window_bits = 1000;  // -> Z_STREAM_ERROR
                 hoc[j] = (uint32_t)j;
             }
-            // largest first: the persistent decoder's lanes then finish together
+            // largest first: the decoder's lanes then finish together
             std::stable_sort(hoc, hoc + ch.count, [&](uint32_t a, uint32_t b) {
                 return hmc[a].in_len + hmc[a].out_cap > hmc[b].in_len + hmc[b].out_cap;
             });
-        }
-        // the three stages of every chunk, each on its own stream
-        for (int c = 0; c < K; c++) {
-            Chunk &ch = chunks[c];
             cudaEvent_t ev_in = dv.pipe_ev[2 * c], ev_dec = dv.pipe_ev[2 * c + 1];
+            cudaStream_t dst = dv.pipe_streams[c % NS];
             CK(ctx, cudaMemcpyAsync(dm + ch.first, hm + ch.first, ch.count * sizeof(zsb_member), cudaMemcpyHostToDevice,
                                     dv.copy_stream));
             for (const Run &rn : ch.in_runs)
                 CK(ctx, cudaMemcpyAsync(dv.d_in + ch.in_base + rn.dev_off, (const void *)rn.host, rn.len,
                                         cudaMemcpyHostToDevice, dv.copy_stream));
+            Scratch sc;
+            sc.aux = dv.aux + ch.first;
+            sc.plan = dv.d_plan + plan_off;
+            plan_off += (ch.count * (sizeof(uint64_t) + sizeof(uint32_t)) + 63) & ~(size_t)63;
+            sc.seq = dv.d_seq + region_off[c % NS] * sizeof(lane::seq_t);
+            sc.seq_bytes = (size_t)region[c % NS] * sizeof(lane::seq_t);
+            sc.counters = dv.counters + 4 * c;
+            sc.small_ctas = K > 1;
+            // the chunk's plan travels with its inputs: slot order, and for the lane path the sequence offsets
+            lane_plan(hmc, hoc, ch.count, region[c % NS], hs + ch.first, cuts_of[c]);
+            sc.cuts = &cuts_of[c];
+            CK(ctx, cudaMemcpyAsync(sc.plan, hs + ch.first, ch.count * sizeof(uint64_t), cudaMemcpyHostToDevice, dv.copy_stream));
+            CK(ctx, cudaMemcpyAsync(sc.plan + ch.count * sizeof(uint64_t), hoc, ch.count * sizeof(uint32_t),
+                                    cudaMemcpyHostToDevice, dv.copy_stream));
             CK(ctx, cudaEventRecord(ev_in, dv.copy_stream));
-            CK(ctx, cudaStreamWaitEvent(dv.stream, ev_in, 0));
+            if (trace) CK(ctx, cudaEventRecord(tev[3 * c], dv.copy_stream));
+            CK(ctx, cudaStreamWaitEvent(dst, ev_in, 0));
             if ((rc = run_device(ctx, dv, ch.count, dm + ch.first, dr + ch.first, hm + ch.first, ho + ch.first, flags,
-                                 dv.stream)))
+                                 dst, &sc)))
                 return rc;
-            CK(ctx, cudaEventRecord(ev_dec, dv.stream));
+            CK(ctx, cudaEventRecord(ev_dec, dst));
+            if (trace) CK(ctx, cudaEventRecord(tev[3 * c + 1], dst));
             CK(ctx, cudaStreamWaitEvent(dv.back_stream, ev_dec, 0));
             CK(ctx, cudaMemcpyAsync(hr + ch.first, dr + ch.first, ch.count * sizeof(zsb_result), cudaMemcpyDeviceToHost,
                                     dv.back_stream));
@@ -626,6 +757,21 @@ static int batch_host(zsb_ctx *ctx, size_t n, const zsb_member *m, zsb_result *r
             for (const Run &rn : ch.out_runs)
                 CK(ctx, cudaMemcpyAsync((void *)rn.host, dv.d_out + ch.out_base + rn.dev_off, rn.len,
                                         cudaMemcpyDeviceToHost, dv.back_stream));
+            if (trace) CK(ctx, cudaEventRecord(tev[3 * c + 2], dv.back_stream));
+        }
+        if (trace) {
+            fprintf(stderr, "zsb trace host: all %d chunks enqueued %.2f ms after the call started\n", K,
+                    std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t_call).count());
+            CK(ctx, cudaStreamSynchronize(dv.back_stream));
+            for (int c = 0; c < K; c++) {
+                float a = 0, b = 0, d = 0;
+                cudaEventElapsedTime(&a, tev[3 * K], tev[3 * c]);
+                cudaEventElapsedTime(&b, tev[3 * K], tev[3 * c + 1]);
+                cudaEventElapsedTime(&d, tev[3 * K], tev[3 * c + 2]);
+                fprintf(stderr, "zsb trace dev %d chunk %2d/%d members %zu: in %.2f dec %.2f out %.2f ms\n", s, c, K,
+                        chunks[c].count, a, b, d);
+            }
+            for (auto &e : tev) cudaEventDestroy(e);
         }
     }
     for (int s = 0; s < nd; s++) {
@@ -635,7 +781,6 @@ static int batch_host(zsb_ctx *ctx, size_t n, const zsb_member *m, zsb_result *r
         if (!k) continue;
         CK(ctx, cudaSetDevice(dv.device));
         CK(ctx, cudaStreamSynchronize(dv.back_stream));
-        CK(ctx, cudaStreamSynchronize(dv.stream));
         zsb_result *hr = (zsb_result *)((zsb_member *)dv.h_desc + k);
         for (size_t j = 0; j < k; j++) r[sh.idx[j]] = hr[j];
     }

@@ -11,6 +11,7 @@ struct zsb_dev {
     int device = 0;
     int sm_count = 0;
     cudaStream_t stream = nullptr, copy_stream = nullptr, back_stream = nullptr;   // decode, host->device, device->host
+    std::vector<cudaStream_t> pipe_streams;   // decode streams of the chunks of a pipelined host batch
     std::vector<cudaEvent_t> pipe_ev;  // per chunk of a host batch: inputs arrived, decoded
     uint16_t *fixed = nullptr;         // prebuilt fixed-code tables (one member slot, group path)
     uint8_t *fixed_lane = nullptr;     // the same in the lane path's slot format
@@ -19,7 +20,7 @@ struct zsb_dev {
     uint8_t *d_plan = nullptr;         // per call: slot order (u32) + per-slot sequence offsets (u64)
     size_t d_plan_cap = 0;
     bool lane_configured = false;
-    int lz_occ = 0;
+    int lz_occ = 0, lane_small_occ = 0;
     uint32_t *counters = nullptr;      // [0] decode work counter, [1] check work counter
     zsb::Aux *aux = nullptr;
     size_t aux_cap = 0;
@@ -43,6 +44,7 @@ struct zsb_ctx {
     size_t slab_bytes = 256u << 20;
     int chunks = 0;                    // host batches: pipeline depth (0 = choose from the batch)
     long launches = 0;
+    bool force_small_ctas = false;
     int profile = 0;                   // 1: record per-kernel events (zsb_profile_read)
     char err[256] = "";
 };

@@ -231,15 +231,18 @@ k_check(const zsb_member *__restrict__ members, zsb_result *__restrict__ results
 
 namespace zsb {
 
+// The CTA's warps come from the launch (1..lane::WARPS); shared memory is laid out for that many, so that
+// small CTAs of different launches (the chunks of a pipelined host batch) share an SM.
 __global__ void __launch_bounds__(lane::WARPS * 32, 1) k_lane(lane::Batch B) {
     extern __shared__ __align__(16) uint8_t smem[];
     uint32_t *lut = (uint32_t *)smem;
     init_lut(lut, threadIdx.x, blockDim.x);
     __syncthreads();
     const int ln = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const size_t warps = blockDim.x >> 5;
     uint8_t *scr = smem + LUT_BYTES + (size_t)warp * lane::WSCR;
-    uint8_t *slots = smem + LUT_BYTES + (size_t)lane::WARPS * lane::WSCR + (size_t)warp * 32 * lane::SLOT;
-    uint32_t *rings = (uint32_t *)(smem + LUT_BYTES + (size_t)lane::WARPS * lane::WSCR + (size_t)lane::WARPS * 32 * lane::SLOT) + warp * 32 * lane::RING_WORDS;
+    uint8_t *slots = smem + LUT_BYTES + warps * lane::WSCR + (size_t)warp * 32 * lane::SLOT;
+    uint32_t *rings = (uint32_t *)(smem + LUT_BYTES + warps * lane::WSCR + warps * 32 * lane::SLOT) + warp * 32 * lane::RING_WORDS;
     lane::warp_lanes<32>(B, slots, scr, rings, lut, ln);
 }
 

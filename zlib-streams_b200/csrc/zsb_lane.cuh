@@ -57,7 +57,9 @@ constexpr int W_DL = 768;                 // u8[32]    distance code lengths
 constexpr int WSCR = 992;
 
 constexpr int WARPS = 14;                 // warps per CTA, one CTA per SM: 448 members in flight per SM
-constexpr size_t SMEM = LUT_BYTES + (size_t)WARPS * WSCR + (size_t)WARPS * 32 * SLOT + (size_t)WARPS * 32 * 16;
+constexpr size_t smem_for(size_t warps) { return LUT_BYTES + warps * WSCR + warps * 32 * SLOT + warps * 32 * 16; }
+constexpr size_t SMEM = smem_for(WARPS);
+constexpr int PIPE_WARPS = 2;             // CTA size of the chunks of a pipelined host batch: 6 CTAs share an SM
 
 // ---- LZ sequence (8 bytes): lo = lit0 | lit1<<8 | lit2<<16 | flags, hi = payload ----
 constexpr uint32_t Q_NLIT_SHIFT = 24;     // bits 24,25: number of literals (0..3)
