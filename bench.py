@@ -291,8 +291,29 @@ def main():
     # ---------------- end-to-end leg: host buffers through the public batch call ----------------
     if not args.no_e2e:
         in_bytes = tiles * blob_len
+        # pinned buffers on the GPU's own NUMA node: pages are placed where the allocating thread runs
+        saved_aff, numa = None, "n/a"
+        try:
+            props = torch.cuda.get_device_properties(local_rank)
+            bdf = "%04x:%02x:%02x.0" % (props.pci_domain_id, props.pci_bus_id, props.pci_device_id)
+            with open("/sys/bus/pci/devices/%s/local_cpulist" % bdf) as f:
+                cpus = set()
+                for part in f.read().strip().split(","):
+                    a, _, b = part.partition("-")
+                    cpus.update(range(int(a), int(b or a) + 1))
+            cpus &= os.sched_getaffinity(0)
+            if cpus:
+                saved_aff = os.sched_getaffinity(0)
+                os.sched_setaffinity(0, cpus)
+                numa = "gpu-local cpus %d" % len(cpus)
+        except Exception as e:          # no sysfs / no such attribute: allocate wherever we run
+            numa = "unpinned (%s)" % type(e).__name__
         h_in = lib.zsb_host_alloc(in_bytes)
         h_out = lib.zsb_host_alloc(n * MEMBER_BYTES)
+        if h_out:
+            ctypes.memset(h_out, 0, n * MEMBER_BYTES)
+        if saved_aff is not None:
+            os.sched_setaffinity(0, saved_aff)
         if not h_in or not h_out:
             raise SystemExit("bench.py: pinned host allocation failed")
         src = (ctypes.c_char * blob_len).from_buffer(blob)
@@ -336,6 +357,7 @@ def main():
             raise SystemExit("bench.py: e2e results differ from expectation")
         out["e2e"] = {"value": world * sum_out / es / 1e9, "unit": "GB/s", "h2d_bytes_per_step": int(sum_in + n * 40),
                       "d2h_bytes_per_step": int(sum_out + n * 32), "ms_per_step": es * 1e3, "steps": e2e_steps,
+                      "host_buffers": "pinned (zsb_host_alloc), " + numa,
                       "timer": "host clock around the synchronous zsb_inflate_batch() call, max over ranks",
                       "gpu_launches": int(lib.zsb_last_launches(eng.ctx))}
         lib.zsb_host_free(h_in)

@@ -98,6 +98,7 @@ struct Scratch {
     const std::vector<size_t> *cuts;   // lane path: slices planned by the caller (lane_plan), who has also sent
                            // the slot order and the sequence offsets to `plan`: run_device then issues no copy
                            // of its own (it would queue behind every input copy already submitted)
+    size_t nbig;           // with cuts: the first nbig slots go to the group path (split_big), the plan covers the rest
     bool small_ctas;       // k_lane in CTAs of lane::PIPE_WARPS warps, one per 32*PIPE_WARPS members, so that
                            // launches on different streams share the SMs
 };
@@ -121,7 +122,7 @@ static int launch_inflate(zsb_ctx *ctx, zsb_dev &dv, size_t n, const zsb_member 
     size_t want = (n + GG::members - 1) / GG::members;
     size_t cap = (size_t)dv.sm_count * dv.occ[G];
     unsigned grid = (unsigned)std::max<size_t>(1, std::min(want, cap));
-    kern<<<grid, GG::threads, GG::smem, st>>>(dm, dr, sc ? sc->aux : dv.aux, dorder, (uint32_t)n, sc ? sc->counters : dv.counters, dv.fixed);
+    kern<<<grid, GG::threads, GG::smem, st>>>(dm, dr, sc ? sc->aux : dv.aux, dorder, (uint32_t)n, (sc ? sc->counters : dv.counters) + 3, dv.fixed);
     ctx->launches++;
     CK(ctx, cudaGetLastError());
     return 0;
@@ -157,9 +158,9 @@ static size_t zsb_seq_bound_sizes(size_t in_len, size_t out_cap) {
 }
 
 static int run_group(zsb_ctx *ctx, zsb_dev &dv, size_t n, const zsb_member *dm, zsb_result *dr,
-                     const uint32_t *dorder, cudaStream_t st, const Scratch *sc) {
-    CK(ctx, cudaMemsetAsync(sc ? sc->counters : dv.counters, 0, 4 * sizeof(uint32_t), st));
-    switch (ctx->lanes) {
+                     const uint32_t *dorder, cudaStream_t st, const Scratch *sc, int lanes) {
+    // (the counters were zeroed by run_device, or for a planned chunk by the caller ahead of its input copies)
+    switch (lanes) {
     case 1: return launch_inflate<1>(ctx, dv, n, dm, dr, dorder, st, sc);
     case 2: return launch_inflate<2>(ctx, dv, n, dm, dr, dorder, st, sc);
     case 4: return launch_inflate<4>(ctx, dv, n, dm, dr, dorder, st, sc);
@@ -168,6 +169,32 @@ static int run_group(zsb_ctx *ctx, zsb_dev &dv, size_t n, const zsb_member *dm, 
     default: return launch_inflate<32>(ctx, dv, n, dm, dr, dorder, st, sc);
     }
 }
+
+// The length-aware split of a batch whose slot order is largest first.  In the lane path a member is
+// decoded by ONE lane at about LANE_NS_PER_BYTE of (in + out), however empty the GPU is, so a member much
+// larger than the rest would keep the batch waiting: the first `nbig` slots, whose own lane time exceeds
+// what the remaining members need together, are decoded by the group path instead (a warp or half-warp
+// per member).  Returns nbig (0 when the batch is uniform).
+static size_t split_big(const zsb_member *hm, const uint32_t *order, size_t n) {
+    const double LANE_NS_PER_BYTE = 100;        // measured: 97 KB of in + out in ~20 ms at full occupancy (C2), about
+                                                // twice as fast when the SM is nearly empty (the tail of C4)
+    const double LANE_BATCH_BYTES_PER_NS = 190.0;   // in + out bytes per ns of the whole lane path (C2)
+    const double FLOOR_NS = 4e6;                // a lane batch is not worth less than a few ms
+    double rem = 0;
+    for (size_t i = 0; i < n; i++) rem += (double)hm[i].in_len + (double)hm[i].out_cap;
+    size_t nbig = 0;
+    while (nbig < n) {
+        const zsb_member &x = hm[order ? order[nbig] : nbig];
+        const double c = (double)x.in_len + (double)x.out_cap;
+        if (c * LANE_NS_PER_BYTE <= 1.5 * std::max(rem / LANE_BATCH_BYTES_PER_NS, FLOOR_NS)) break;
+        rem -= c;
+        nbig++;
+    }
+    return nbig;
+}
+// lanes per member for the large members: the leader lane's symbol decode sets the pace, and 16 lanes measured
+// faster per member than 32 (C4: 2.05 s against 2.68 s for the same 16 MiB members)
+static int group_lanes_for(const zsb_dev &, size_t) { return 16; }
 
 // Per-slot sequence offsets (off[n]) and the slices [cuts[k], cuts[k+1]) of the slot order, cut where the
 // arena of arena_seqs sequences would overflow.  Returns the most sequences a slice needs.
@@ -194,7 +221,7 @@ static uint64_t lane_plan(const zsb_member *hm, const uint32_t *horder, size_t n
 // lane path: k_lane + k_lz over slices of the slot order whose sequence scratch fits the arena
 static int run_lane(zsb_ctx *ctx, zsb_dev &dv, size_t n, const zsb_member *dm, zsb_result *dr,
                     const zsb_member *hm, const uint32_t *horder, const uint32_t *dorder, uint64_t *dseqoff,
-                    cudaStream_t st, const Scratch *sc) {
+                    cudaStream_t st, const Scratch *sc, bool zero_counters) {
     if (!dv.lane_configured) {
         CK(ctx, cudaFuncSetAttribute(k_lane, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)lane::SMEM));
         // all of the SM's memory as shared memory also for the small CTAs (the default carve-out fits fewer of them)
@@ -230,7 +257,8 @@ static int run_lane(zsb_ctx *ctx, zsb_dev &dv, size_t n, const zsb_member *dm, z
     for (size_t k = 0; k + 1 < cuts.size(); k++) {
         const size_t first = cuts[k], cnt = cuts[k + 1] - cuts[k];
         // (a planned chunk's counters were zeroed by the caller ahead of its input copies)
-        if (!(sc && sc->cuts) || k > 0) CK(ctx, cudaMemsetAsync(counters, 0, 4 * sizeof(uint32_t), st));
+        // (and when the group path ran first it zeroed them; it only uses counters[3], so does not dirty these)
+        if ((!(sc && sc->cuts) && zero_counters) || k > 0) CK(ctx, cudaMemsetAsync(counters, 0, 3 * sizeof(uint32_t), st));
         lane::Batch B;
         B.members = dm;
         B.results = dr;
@@ -293,17 +321,38 @@ static int run_device(zsb_ctx *ctx, zsb_dev &dv, size_t n, const zsb_member *dm,
     if (!sc && (rc = grow(ctx, dv.d_plan, dv.d_plan_cap, plan_bytes))) return rc;
     uint64_t *dseqoff = (uint64_t *)(sc ? sc->plan : dv.d_plan);
     uint32_t *dorder = (uint32_t *)(dseqoff + n);
-    std::vector<uint32_t> ident;
-    if (!horder) {
-        ident.resize(n);
-        for (size_t i = 0; i < n; i++) ident[i] = (uint32_t)i;
+    const bool planned = sc && sc->cuts;
+    std::vector<uint32_t> own;
+    size_t nbig = planned ? sc->nbig : 0;
+    if (!planned) {
+        if (!horder) {
+            own.resize(n);
+            for (size_t i = 0; i < n; i++) own[i] = (uint32_t)i;
+            if (ctx->path == 0)          // the split needs the largest members first
+                std::stable_sort(own.begin(), own.end(), [&](uint32_t a, uint32_t b) {
+                    return hm[a].in_len + hm[a].out_cap > hm[b].in_len + hm[b].out_cap;
+                });
+            horder = own.data();
+        }
+        if (ctx->path == 0 && ctx->split_big) nbig = split_big(hm, horder, n);
+        else if (ctx->path == 2) nbig = n;
+        CK(ctx, cudaMemcpyAsync(dorder, horder, n * sizeof(uint32_t), cudaMemcpyHostToDevice, st));
     }
-    if (!(sc && sc->cuts))
-        CK(ctx, cudaMemcpyAsync(dorder, horder ? horder : ident.data(), n * sizeof(uint32_t), cudaMemcpyHostToDevice, st));
-    const bool use_lane = ctx->path == 1 || (ctx->path == 0);
-    if (use_lane) rc = run_lane(ctx, dv, n, dm, dr, hm, horder, dorder, dseqoff, st, sc);
-    else rc = run_group(ctx, dv, n, dm, dr, dorder, st, sc);
-    if (rc) return rc;
+    // large members on the group stream, beside the lane path on the caller's stream (fork / join by events)
+    const bool fork = nbig && nbig < n;
+    if (nbig) {
+        const int lanes = ctx->path == 2 ? ctx->lanes : group_lanes_for(dv, nbig);
+        if (!planned) CK(ctx, cudaMemsetAsync(sc ? sc->counters : dv.counters, 0, 4 * sizeof(uint32_t), st));
+        if (fork) {
+            CK(ctx, cudaEventRecord(dv.ev_fork, st));
+            CK(ctx, cudaStreamWaitEvent(dv.group_stream, dv.ev_fork, 0));
+        }
+        if ((rc = run_group(ctx, dv, nbig, dm, dr, dorder, fork ? dv.group_stream : st, sc, lanes))) return rc;
+        if (fork) CK(ctx, cudaEventRecord(dv.ev_join, dv.group_stream));
+    }
+    if (nbig < n && (rc = run_lane(ctx, dv, n - nbig, dm, dr, hm, horder + nbig, dorder + nbig, dseqoff + nbig, st, sc, nbig == 0)))
+        return rc;
+    if (fork) CK(ctx, cudaStreamWaitEvent(st, dv.ev_join, 0));
     if (!(flags & ZSB_RAW_ONLY)) {
         unsigned grid = (unsigned)std::min<size_t>(n, (size_t)dv.sm_count * 8);
         k_check<<<grid, CHK_THREADS, 0, st>>>(dm, dr, sc ? sc->aux : dv.aux, (uint32_t)n, (sc ? sc->counters : dv.counters) + 1);
@@ -338,6 +387,9 @@ static int init_device(zsb_ctx *ctx, zsb_dev &dv, int device) {
         CK(ctx, cudaStreamCreateWithFlags(&st, cudaStreamNonBlocking));
         dv.pipe_streams.push_back(st);
     }
+    CK(ctx, cudaStreamCreateWithFlags(&dv.group_stream, cudaStreamNonBlocking));
+    CK(ctx, cudaEventCreateWithFlags(&dv.ev_fork, cudaEventDisableTiming));
+    CK(ctx, cudaEventCreateWithFlags(&dv.ev_join, cudaEventDisableTiming));
     CK(ctx, cudaMalloc(&dv.fixed, STREAM_BYTES));
     CK(ctx, cudaMalloc(&dv.fixed_lane, lane::SLOT));
     CK(ctx, cudaMalloc(&dv.counters, 4 * MAX_CHUNKS_DEV * sizeof(uint32_t)));
@@ -366,6 +418,9 @@ static void free_device(zsb_dev &dv) {
     if (dv.stream) cudaStreamDestroy(dv.stream);
     if (dv.copy_stream) cudaStreamDestroy(dv.copy_stream);
     if (dv.back_stream) cudaStreamDestroy(dv.back_stream);
+    if (dv.group_stream) cudaStreamDestroy(dv.group_stream);
+    if (dv.ev_fork) cudaEventDestroy(dv.ev_fork);
+    if (dv.ev_join) cudaEventDestroy(dv.ev_join);
     for (size_t i = 1; i < dv.pipe_streams.size(); i++) cudaStreamDestroy(dv.pipe_streams[i]);   // [0] is dv.stream
     dv.pipe_streams.clear();
     for (cudaEvent_t e : dv.pipe_ev) cudaEventDestroy(e);
@@ -442,6 +497,10 @@ extern "C" int zsb_set_option(zsb_ctx *ctx, const char *name, long value) {
     if (!strcmp(name, "chunks")) {
         if (value < 0 || value > 64) return ZSB_E_ARG;
         ctx->chunks = (int)value;
+        return 0;
+    }
+    if (!strcmp(name, "split_big")) {         // large members to the group path beside the lane path (off: measured no gain)
+        ctx->split_big = value != 0;
         return 0;
     }
     if (!strcmp(name, "small_ctas")) {        // diagnostic: k_lane in the small CTAs of the pipelined host path
@@ -737,7 +796,8 @@ static int batch_host(zsb_ctx *ctx, size_t n, const zsb_member *m, zsb_result *r
             sc.counters = dv.counters + 4 * c;
             sc.small_ctas = K > 1;
             // the chunk's plan travels with its inputs: slot order, and for the lane path the sequence offsets
-            lane_plan(hmc, hoc, ch.count, region[c % NS], hs + ch.first, cuts_of[c]);
+            sc.nbig = (ctx->path == 0 && ctx->split_big) ? split_big(hmc, hoc, ch.count) : ctx->path == 2 ? ch.count : 0;
+            lane_plan(hmc, hoc + sc.nbig, ch.count - sc.nbig, region[c % NS], hs + ch.first + sc.nbig, cuts_of[c]);
             sc.cuts = &cuts_of[c];
             CK(ctx, cudaMemcpyAsync(sc.plan, hs + ch.first, ch.count * sizeof(uint64_t), cudaMemcpyHostToDevice, dv.copy_stream));
             CK(ctx, cudaMemcpyAsync(sc.plan + ch.count * sizeof(uint64_t), hoc, ch.count * sizeof(uint32_t),

@@ -11,6 +11,8 @@ struct zsb_dev {
     int device = 0;
     int sm_count = 0;
     cudaStream_t stream = nullptr, copy_stream = nullptr, back_stream = nullptr;   // decode, host->device, device->host
+    cudaStream_t group_stream = nullptr;      // large members (group path) beside the lane path
+    cudaEvent_t ev_fork = nullptr, ev_join = nullptr;
     std::vector<cudaStream_t> pipe_streams;   // decode streams of the chunks of a pipelined host batch
     std::vector<cudaEvent_t> pipe_ev;  // per chunk of a host batch: inputs arrived, decoded
     uint16_t *fixed = nullptr;         // prebuilt fixed-code tables (one member slot, group path)
@@ -45,6 +47,7 @@ struct zsb_ctx {
     int chunks = 0;                    // host batches: pipeline depth (0 = choose from the batch)
     long launches = 0;
     bool force_small_ctas = false;
+    bool split_big = false;            // path 0: members far larger than the rest go to the group path (split_big())
     int profile = 0;                   // 1: record per-kernel events (zsb_profile_read)
     char err[256] = "";
 };
