@@ -299,6 +299,8 @@ static int run_lane(zsb_ctx *ctx, zsb_dev &dv, size_t n, const zsb_member *dm, z
         CK(ctx, cudaGetLastError());
         if (pe) CK(ctx, cudaEventRecord(pe[1], st));
         const size_t wpc = LZ_THREADS / 32;
+        // (fewer resident CTAs to keep the members' windows in L2 were measured slower: 1/2/3/4/5 CTAs per SM
+        // = 26.4/15.2/11.8/10.3/9.8 ms on C2 against 9.5 ms at the full 6; 8 CTAs of 32 registers: 11.2 ms)
         grid = (unsigned)std::max<size_t>(1, std::min((cnt + wpc - 1) / wpc, (size_t)dv.sm_count * dv.lz_occ));
         k_lz<<<grid, LZ_THREADS, 0, st>>>(B, counters + 2);
         ctx->launches++;

@@ -93,7 +93,7 @@ template <> struct Wp<1> {
 struct Lane {
     Dec d;               // bit input, output accounting, stop bookkeeping (zsb_device.cuh)
     Mem mm;
-    uint32_t *ring;      // 4 words of shared memory: the input words at d.b.next, +4, +8 arrive here
+    uint32_t *ring;      // 4 words of shared memory (RING_STRIDE apart): the input words at d.b.next, +4, +8 arrive here
                          // through cp.async, so a refill never waits on a load scoreboard
     seq_t *seq;          // where this member's next sequence goes
     seq_t *seq0;         // start of its sequence array
@@ -151,11 +151,18 @@ ZSB_DEV void push_raw(Lane &L, uint32_t in_off, uint32_t n) {
 #define ZSB_CP_WAIT(n) asm volatile("cp.async.wait_group %0;" ::"n"(n) : "memory")
 #endif
 constexpr int RING_WORDS = 4;
+// word w of a lane's ring is ring[w * RING_STRIDE]: on the device the 32 rings of a warp are interleaved, so the
+// lanes hit 32 different banks whatever word each one is at (4 consecutive words per lane were a 4-way conflict)
+#if defined(__CUDA_ARCH__)
+constexpr int RING_STRIDE = 32;
+#else
+constexpr int RING_STRIDE = 1;
+#endif
 
 // start the copy of the input word at byte offset `off` (one group per word, empty past the end)
 ZSB_DEV void fetch_word(const Lane &L, uint32_t off) {
     const BitIn &b = L.d.b;
-    if (off < b.len) ZSB_CP4(&L.ring[(off >> 2) & 3u], b.p + off);
+    if (off < b.len) ZSB_CP4(&L.ring[((off >> 2) & 3u) * RING_STRIDE], b.p + off);
     ZSB_CP_COMMIT();
 }
 ZSB_DEV void prime(Lane &L) {
@@ -292,7 +299,7 @@ ZSB_DEV int accept_match(Lane &L) {
 ZSB_DEV uint32_t ring_load(const Lane &L, uint32_t byteoff) {          // byteoff = 0, 4, 8 or 12
 #if defined(__CUDA_ARCH__)
     uint32_t v;
-    asm volatile("ld.shared.u32 %0, [%1];" : "=r"(v) : "r"(L.ring_sa + byteoff) : "memory");
+    asm volatile("ld.shared.u32 %0, [%1];" : "=r"(v) : "r"(L.ring_sa + byteoff * RING_STRIDE) : "memory");
     return v;
 #else
     return L.ring[byteoff >> 2];
@@ -306,7 +313,7 @@ ZSB_DEV void fetch_word_if(const Lane &L, bool p, uint32_t off) {
     asm volatile(
         "{\n\t.reg .pred q, r;\n\tsetp.ne.u32 q, %0, 0;\n\tsetp.ne.u32 r, %1, 0;\n\t"
         "@q cp.async.ca.shared.global [%2], [%3], 4;\n\t@r cp.async.commit_group;\n\t}" ::"r"(go),
-        "r"(grp), "r"(L.ring_sa + (off & 12u)), "l"(b.p + off)
+        "r"(grp), "r"(L.ring_sa + (off & 12u) * RING_STRIDE), "l"(b.p + off)
         : "memory");
 #else
     if (p && off < b.len) L.ring[(off >> 2) & 3u] = *(const uint32_t *)(b.p + off);
@@ -771,7 +778,7 @@ ZSB_DEV int lane_block(Lane &L, uint8_t *T, const uint32_t *lut, const Batch &B)
 template <int W>
 __device__ __forceinline__ void warp_lanes(const Batch &B, uint8_t *slots, uint8_t *scr, uint32_t *rings, const uint32_t *lut, int lane) {
     Lane L;
-    L.ring = rings + lane * RING_WORDS;
+    L.ring = rings + lane * (RING_STRIDE == 1 ? RING_WORDS : 1);
     L.d.pos = 0; L.d.cap = 0; L.d.b.p = nullptr; L.d.b.len = 0; L.d.b.next = 0; L.d.b.nbits = 0; L.d.b.hold = 0;
     L.d.d64 = 0; L.d.msg = 0; L.nl = 0; L.lw = 0; L.seq = L.seq0 = nullptr; L.nlen = 0; L.ndist = 0;
     L.mm.idx = 0; L.mode = 0; L.pl = 0; L.hist = 0;
@@ -856,7 +863,10 @@ __device__ __forceinline__ void warp_lanes(const Batch &B, uint8_t *slots, uint8
         if (!Wp<W>::any(st == LS_SYM)) break;
         // ---------------- the lock-step symbol loop ----------------
 #pragma unroll 1
-        for (;;) {
+        for (;;) {               // two codes per vote: a lane that has to leave waits one step at most
+            if (st == LS_SYM) {
+                if (L.d.b.next + 8 > L.d.b.len || !fast_step(L, T, lut)) st = LS_TAIL;
+            }
             if (st == LS_SYM) {
                 if (L.d.b.next + 8 > L.d.b.len || !fast_step(L, T, lut)) st = LS_TAIL;
             }

@@ -20,7 +20,7 @@ __global__ void __launch_bounds__(32) k_zs_decode(zs::State *S, const uint8_t *i
     __shared__ uint32_t ring[32 * lane::RING_WORDS];
     init_lut(lut, threadIdx.x, 32);
     __syncwarp();
-    zs::stream_decode<32>(*S, in, in_len, out_cap, seq, fixed_tab, scr, ring + threadIdx.x * lane::RING_WORDS, lut, threadIdx.x);
+    zs::stream_decode<32>(*S, in, in_len, out_cap, seq, fixed_tab, scr, ring + threadIdx.x, lut, threadIdx.x);
 }
 
 __global__ void __launch_bounds__(32) k_zs_lz(const zs::State *S, uint8_t *out, const uint8_t *in, const lane::seq_t *seq) {
