@@ -193,7 +193,7 @@ def main():
         eng.set_option("path", 2)
         eng.set_option("lanes_per_member", args.lanes)
     else:
-        eng.set_option("path", 1)
+        eng.set_option("path", 0)           # the default: lane path (k_lane + k_lz)
         if args.small_ctas:
             eng.set_option("small_ctas", 1)
     lib = eng.lib
