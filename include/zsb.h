@@ -45,8 +45,13 @@ typedef struct zsb_member {
     void *out;           /* output buffer; bytes [total_out, out_cap) are unspecified after the call */
     size_t out_cap;      /* < 2^32 */
     int32_t window_bits; /* as inflateInit2: -8..-15 raw, -16 raw Deflate64, 8..15 zlib, +16 gzip, +32 auto */
-    int32_t reserved;
+    int32_t flags;       /* 0, or ZSB_M_* (extensions for container formats; the reference has no equivalent) */
 } zsb_member;
+
+/* zsb_member.flags */
+#define ZSB_M_CRC32  1   /* raw member: report the CRC-32 of the output bytes in zsb_result.check (ZIP entries) */
+#define ZSB_M_STORED 2   /* the member is not deflate data: copy in -> out (ZIP method 0); ret = Z_STREAM_END, or
+                            Z_BUF_ERROR with out_cap bytes copied when out_cap < in_len; window_bits is ignored */
 
 /* What the reference leaves on the z_stream after the one-shot sequence above (src/inflate.c:1253-1274). */
 typedef struct zsb_result {
@@ -118,6 +123,44 @@ ZSB_API void zsb_host_free(void *p);
 #define ZSB_NUM_MESSAGES 19
 ZSB_API const char *zsb_message(int msg_id);
 
+/* ---- ZIP container walker: archive bytes -> batch descriptors -> verified entries ----
+ * The reference decodes the Deflate64 (method 9) and deflate (method 8) entries zip.js hands it one at a
+ * time; its generator reads the same header fields (src/generator/create_deflate64.cpp:51-93: local header
+ * signature PK\3\4, method @+8, sizes @+18/+22, name/extra lengths @+26/+28).  Here a whole archive becomes
+ * one batch.  The walker is host code over the archive's directory only; entry data is touched by the GPU. */
+typedef struct zsb_zip_entry {
+    uint64_t header_off;   /* local file header */
+    uint64_t data_off;     /* first compressed byte (header_off + 30 + name + extra of the LOCAL header) */
+    uint64_t comp_size;
+    uint64_t uncomp_size;
+    uint32_t crc32;        /* from the central directory */
+    uint16_t method;       /* 0 stored, 8 deflate, 9 Deflate64; anything else is reported, not decoded */
+    uint16_t gp_flags;     /* general purpose bits (bit 0 encrypted, bit 3 sizes also in a data descriptor) */
+    uint32_t name_off;     /* file name bytes inside the archive (central directory copy) */
+    uint16_t name_len;
+    uint16_t pad;
+} zsb_zip_entry;
+
+/* Parses the end-of-central-directory record (ZIP64 included) and the central directory of the archive at
+ * host address `zip`.  Writes at most max_entries entries, *count receives the number of entries in the
+ * archive.  Returns 0, or ZSB_E_ZIP when the directory is malformed or points outside the archive. */
+ZSB_API int zsb_zip_scan(const void *zip, size_t len, zsb_zip_entry *entries, size_t max_entries, size_t *count);
+
+/* Batch descriptors for n entries: in = in_base + data_off, out = out_base + out_off[i], out_cap =
+ * uncomp_size, window_bits -15 / -16 by method, flags ZSB_M_CRC32 (| ZSB_M_STORED for method 0).
+ * in_base / out_base may be host or device addresses of the archive and of the output area.  Entries that
+ * cannot be decoded (encrypted, unknown method, sizes >= 4 GiB) get window_bits 1000, i.e. Z_STREAM_ERROR. */
+ZSB_API int zsb_zip_members(const void *in_base, const zsb_zip_entry *entries, size_t n, void *out_base,
+                            const uint64_t *out_off, zsb_member *members);
+
+/* zsb_zip_members + zsb_inflate_batch + the directory checks, per entry: ret = Z_STREAM_END when the entry
+ * decoded to exactly uncomp_size bytes whose CRC-32 (computed on the GPU) equals the directory's; Z_DATA_ERROR
+ * with msg "incorrect data check" / "incorrect length check" (the reference's gzip trailer messages,
+ * src/inflate.c:1209,1223) when CRC or size differ; otherwise the decoder's own ret / msg. */
+ZSB_API int zsb_zip_inflate(zsb_ctx *ctx, const void *zip, const zsb_zip_entry *entries, size_t n, void *out_base,
+                            const uint64_t *out_off, zsb_result *results);
+
+#define ZSB_E_ZIP   (-103)
 #define ZSB_E_ARG   (-100)
 #define ZSB_E_CUDA  (-101)
 #define ZSB_E_NOMEM (-102)

@@ -50,7 +50,7 @@ extern "C" int emul_decode(const uint8_t *in, size_t in_len, uint8_t *out, size_
     alignas(16) uint16_t T[zsb::STREAM_U16];
     memset(T, 0xA5, sizeof T);
     zsb_member m;
-    m.in = in; m.in_len = in_len; m.out = out; m.out_cap = out_cap; m.window_bits = wbits; m.reserved = 0;
+    m.in = in; m.in_len = in_len; m.out = out; m.out_cap = out_cap; m.window_bits = wbits; m.flags = 0;
     zsb::Aux a;
     uint32_t counter = 0;
     zsb::warp_inflate<1>(&m, res, &a, nullptr, 1, &counter, T, lut, fixed, 0, 1u);
@@ -78,7 +78,7 @@ extern "C" int emul_decode_lane(const uint8_t *in, size_t in_len, uint8_t *out, 
     alignas(16) uint8_t T[lane::SLOT];
     memset(T, 0xA5, sizeof T);
     zsb_member m;
-    m.in = in; m.in_len = in_len; m.out = out; m.out_cap = out_cap; m.window_bits = wbits; m.reserved = 0;
+    m.in = in; m.in_len = in_len; m.out = out; m.out_cap = out_cap; m.window_bits = wbits; m.flags = 0;
     Aux a;
     uint32_t counter = 0, order = 0;
     uint64_t seq_off = 0;

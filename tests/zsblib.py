@@ -26,7 +26,7 @@ ZSB_HAS_WRAPPED = 1
 
 class Member(ctypes.Structure):
     _fields_ = [("inp", ctypes.c_void_p), ("in_len", ctypes.c_size_t), ("out", ctypes.c_void_p),
-                ("out_cap", ctypes.c_size_t), ("window_bits", ctypes.c_int32), ("reserved", ctypes.c_int32)]
+                ("out_cap", ctypes.c_size_t), ("window_bits", ctypes.c_int32), ("flags", ctypes.c_int32)]
 
 
 class Result(ctypes.Structure):

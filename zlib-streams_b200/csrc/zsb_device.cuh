@@ -953,7 +953,13 @@ __device__ __forceinline__ void warp_inflate(const zsb_member *members, zsb_resu
                     d.cap = (uint32_t)m.out_cap;
                     d.d64 = m.window_bits == -16;
                     d.last = 0; d.at_type = 0; d.msg = 0; d.extent = 0; d.mlen = 0; d.mdist = 0; d.mtrunc = 0;
-                    if (!wbits_valid(m.window_bits) || (in == nullptr && m.in_len != 0) ||
+                    if (m.flags & ZSB_M_STORED) {      // copied (and checked) by k_check; nothing to decode
+                        Aux a;
+                        a.kind = 0; a.trailer_pos = 0; a.need_trailer = 0; a.init_check = 0; a.nseq = 0;
+                        a.pad[0] = a.pad[1] = a.pad[2] = 0;
+                        aux[idx] = a;
+                        ev = EV_INITERR;               // any event: the group fetches its next member
+                    } else if (!wbits_valid(m.window_bits) || (in == nullptr && m.in_len != 0) ||
                         (out == nullptr && m.out_cap != 0)) {
                         ev = EV_INITERR;
                     } else {
@@ -971,7 +977,7 @@ __device__ __forceinline__ void warp_inflate(const zsb_member *members, zsb_resu
                             mm.hdr_bits = h.bits;
                         }
                     }
-                    if (ev != EV_NONE) write_result(d, mm, ev, results + idx, aux + idx);
+                    if (ev != EV_NONE && !(m.flags & ZSB_M_STORED)) write_result(d, mm, ev, results + idx, aux + idx);
                 }
                 ev = (int)grp_bcast<G>((uint32_t)ev, gmask);
                 st = ev == EV_NONE ? ST_BLOCK : ST_FETCH;

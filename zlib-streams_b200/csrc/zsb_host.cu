@@ -674,7 +674,7 @@ static int batch_host(zsb_ctx *ctx, size_t n, const zsb_member *m, zsb_result *r
     std::vector<Shard> shards(nd);
     for (size_t i = 0; i < n; i++) shards[shard_of[i]].idx.push_back((uint32_t)i);
     bool raw_only = true;
-    for (size_t i = 0; i < n; i++) raw_only &= m[i].window_bits < 0;
+    for (size_t i = 0; i < n; i++) raw_only &= m[i].window_bits < 0 && m[i].flags == 0;
     const unsigned flags = raw_only ? ZSB_RAW_ONLY : ZSB_HAS_WRAPPED;
     ctx->launches = 0;
 
@@ -861,7 +861,7 @@ static int batch_device_ptrs(zsb_ctx *ctx, size_t n, const zsb_member *m, zsb_re
     bool raw_only = true;
     for (size_t i = 0; i < n; i++) {
         ord[i] = (uint32_t)i;
-        raw_only &= m[i].window_bits < 0;
+        raw_only &= m[i].window_bits < 0 && m[i].flags == 0;
     }
     std::stable_sort(ord.begin(), ord.end(), [&](uint32_t a, uint32_t b) {
         return m[a].in_len + m[a].out_cap > m[b].in_len + m[b].out_cap;

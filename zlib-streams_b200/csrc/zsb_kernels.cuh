@@ -209,7 +209,49 @@ k_check(const zsb_member *__restrict__ members, zsb_result *__restrict__ results
         __syncthreads();
         if (idx >= n) break;
         const Aux a = aux[idx];
-        if (a.kind == 0) continue;
+        const int32_t mflags = members[idx].flags;
+        if (mflags & ZSB_M_STORED) {                 // ZIP method 0: the CTA copies the bytes (the decoders skipped it)
+            const zsb_member m = members[idx];
+            const uint8_t *src = (const uint8_t *)m.in;
+            uint8_t *dst = (uint8_t *)m.out;
+            const bool bad = (src == nullptr && m.in_len != 0) || (dst == nullptr && m.out_cap != 0) ||
+                             m.in_len > 0xfffffff0ull || m.out_cap > 0xfffffff0ull;
+            const uint32_t nb = bad ? 0u : (uint32_t)(m.in_len < m.out_cap ? m.in_len : m.out_cap);
+            if (((uintptr_t)src & 15) == ((uintptr_t)dst & 15)) {
+                uint32_t head = (uint32_t)((16 - ((uintptr_t)dst & 15)) & 15);
+                if (head > nb) head = nb;
+                for (uint32_t i = tid; i < head; i += CHK_THREADS) dst[i] = src[i];
+                const uint32_t nv = (nb - head) >> 4;
+                const uint4 *s4 = (const uint4 *)(src + head);
+                uint4 *d4 = (uint4 *)(dst + head);
+                for (uint32_t i = tid; i < nv; i += CHK_THREADS) d4[i] = s4[i];
+                for (uint32_t i = head + 16 * nv + tid; i < nb; i += CHK_THREADS) dst[i] = src[i];
+            } else {
+                for (uint32_t i = tid; i < nb; i += CHK_THREADS) dst[i] = src[i];
+            }
+            __syncthreads();
+            uint32_t crc = 0;
+            if (mflags & ZSB_M_CRC32) crc = cta_check(sh, 2u, dst, nb, 0u);
+            if (tid == 0) {
+                zsb_result r;
+                r.ret = bad ? -2 : (m.in_len <= m.out_cap ? 1 : -5);
+                r.msg_id = 0;
+                r.total_in = nb;
+                r.total_out = nb;
+                r.check = crc;
+                r.data_type = 0;
+                results[idx] = r;
+            }
+            continue;
+        }
+        if (a.kind == 0) {
+            if (mflags & ZSB_M_CRC32) {              // raw member of a container that carries a CRC-32 (ZIP)
+                const uint32_t E0 = (uint32_t)results[idx].total_out;
+                const uint32_t crc = cta_check(sh, 2u, (const uint8_t *)members[idx].out, E0, 0u);
+                if (tid == 0) results[idx].check = crc;
+            }
+            continue;
+        }
         const uint8_t *out = (const uint8_t *)members[idx].out;
         const uint32_t E = (uint32_t)results[idx].total_out;
         const uint32_t check = cta_check(sh, a.kind, out, E, a.init_check);

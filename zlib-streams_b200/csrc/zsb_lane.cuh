@@ -682,6 +682,13 @@ ZSB_DEV int start_member(Lane &L, uint32_t slot, const Batch &B) {
     L.lw = 0; L.nl = 0; L.mode = 0; L.pl = 0;
     L.hist = B.hist ? B.hist[idx] : 0u;
     int ev = EV_NONE;
+    if (m.flags & ZSB_M_STORED) {          // copied (and checked) by k_check; nothing to decode
+        Aux a;
+        a.kind = 0; a.trailer_pos = 0; a.need_trailer = 0; a.init_check = 0; a.nseq = 0;
+        a.pad[0] = a.pad[1] = a.pad[2] = 0;
+        B.aux[idx] = a;
+        return LS_FETCH;
+    }
     if (!wbits_valid(m.window_bits) || (in == nullptr && m.in_len != 0) || (m.out == nullptr && m.out_cap != 0)) {
         ev = EV_INITERR;
     } else {
