@@ -16,7 +16,7 @@ EMUL_DIR = os.path.join(ROOT, "tests", "emul")
 API_SYMBOLS = ["zsb_create", "zsb_destroy", "zsb_create_error", "zsb_last_error", "zsb_num_devices",
                "zsb_inflate_batch", "zsb_inflate_batch_device", "zsb_set_option", "zsb_get_option",
                "zsb_last_launches", "zsb_plan_shards", "zsb_host_alloc", "zsb_host_free", "zsb_message",
-               "zsb_profile_read"]
+               "zsb_profile_read", "zsb_zip_scan", "zsb_zip_members", "zsb_zip_inflate"]
 ZLIB_SYMBOLS = ["inflateInit_", "inflateInit2_", "inflate", "inflateEnd", "inflateReset", "inflateReset2",
                 "inflateResetKeep"]
 
@@ -38,6 +38,25 @@ class Result(ctypes.Structure):
 
     def __repr__(self):
         return "Result(ret=%d msg=%d in=%d out=%d check=%08x dt=%d)" % self.astuple()
+
+
+class ZipEntry(ctypes.Structure):
+    _fields_ = [("header_off", ctypes.c_uint64), ("data_off", ctypes.c_uint64), ("comp_size", ctypes.c_uint64),
+                ("uncomp_size", ctypes.c_uint64), ("crc32", ctypes.c_uint32), ("method", ctypes.c_uint16),
+                ("gp_flags", ctypes.c_uint16), ("name_off", ctypes.c_uint32), ("name_len", ctypes.c_uint16),
+                ("pad", ctypes.c_uint16)]
+
+
+def zip_scan(lib, data):
+    """-> (rc, [ZipEntry]) for archive bytes `data` (host walker, no GPU)."""
+    buf = ctypes.create_string_buffer(data, max(len(data), 1))
+    cnt = ctypes.c_size_t(0)
+    rc = lib.zsb_zip_scan(buf, len(data), None, 0, ctypes.byref(cnt))
+    if rc:
+        return rc, []
+    arr = (ZipEntry * max(cnt.value, 1))()
+    rc = lib.zsb_zip_scan(buf, len(data), arr, cnt.value, ctypes.byref(cnt))
+    return rc, [arr[i] for i in range(cnt.value)]
 
 
 def build_product():
@@ -70,6 +89,12 @@ def load_product():
     lib.zsb_host_free.argtypes = [ctypes.c_void_p]
     lib.zsb_message.restype = ctypes.c_char_p
     lib.zsb_message.argtypes = [ctypes.c_int]
+    lib.zsb_zip_scan.argtypes = [ctypes.c_void_p, ctypes.c_size_t, ctypes.c_void_p, ctypes.c_size_t,
+                                 ctypes.POINTER(ctypes.c_size_t)]
+    lib.zsb_zip_members.argtypes = [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_size_t, ctypes.c_void_p, ctypes.c_void_p,
+                                    ctypes.c_void_p]
+    lib.zsb_zip_inflate.argtypes = [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_void_p, ctypes.c_size_t, ctypes.c_void_p,
+                                    ctypes.c_void_p, ctypes.c_void_p]
     lib.zsb_profile_read.restype = ctypes.c_long
     lib.zsb_profile_read.argtypes = [ctypes.c_void_p, ctypes.c_int, ctypes.POINTER(ctypes.c_double),
                                      ctypes.POINTER(ctypes.c_double)]

@@ -900,5 +900,8 @@ extern "C" int zsb_inflate_batch(zsb_ctx *ctx, size_t n, const zsb_member *m, zs
     return rc;
 }
 
+// the ZIP container walker (zsb_zip_scan / zsb_zip_members / zsb_zip_inflate)
+#include "zsb_zip.cuh"
+
 // the z_stream surface (inflateInit2_ / inflate / inflateEnd): same translation unit, it shares the kernels above
 #include "zsb_zstream.cuh"
