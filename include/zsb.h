@@ -160,6 +160,18 @@ ZSB_API int zsb_zip_members(const void *in_base, const zsb_zip_entry *entries, s
 ZSB_API int zsb_zip_inflate(zsb_ctx *ctx, const void *zip, const zsb_zip_entry *entries, size_t n, void *out_base,
                             const uint64_t *out_off, zsb_result *results);
 
+/* ---- gzip files of several members ----
+ * The reference's inflate() stops after one member (src/inflate.c:1231-1235: mode DONE, trailing bytes stay
+ * unread, total_in = member length); real .gz files are often concatenations.  Every file i is a buffer of
+ * in_len[i] bytes holding one or more gzip members (window_bits 31; 47 also accepts zlib members) back to
+ * back; its members are decoded one after the other into out[i] (capacity out_cap[i]).  Each round decodes
+ * the next member of every unfinished file as one batch.  Per file, r[i] reports the LAST member decoded:
+ * ret = Z_STREAM_END when the whole buffer was consumed by complete members, else that member's ret / msg;
+ * total_in / total_out are summed over the file's members; check is the last member's.  members[i]
+ * (optional) receives the number of complete members.  Host or device pointers, as zsb_inflate_batch. */
+ZSB_API int zsb_gunzip_files(zsb_ctx *ctx, size_t n, const void *const *in, const size_t *in_len, void *const *out,
+                             const size_t *out_cap, int window_bits, zsb_result *r, uint32_t *members);
+
 #define ZSB_E_ZIP   (-103)
 #define ZSB_E_ARG   (-100)
 #define ZSB_E_CUDA  (-101)

@@ -11,6 +11,67 @@ ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 sys.path.insert(0, os.path.join(ROOT, "tests"))
 
 
+def zip_bench(args):
+    """One archive of C5's members as ZIP entries (method 8 / 9), archive and outputs resident in HBM:
+    zsb_zip_scan on the host copy, zsb_zip_inflate (decode + CRC-32 of every entry on the GPU)."""
+    import ctypes
+    import time
+    import zlib
+    import numpy as np
+    import torch
+    import workloads
+    import zipgen
+    import zsblib
+    w = workloads.c5(distinct=2048, tiles=4 if args.small else 32)
+    ents = []
+    for t in range(w["tiles"]):
+        for i, (comp, wb, plain) in enumerate(w["distinct"]):
+            ents.append(dict(name="t%03d/f%05d" % (t, i), method=9 if wb == -16 else 8, data=comp, plain=plain,
+                             crc=zlib.crc32(plain) & 0xffffffff))
+    data = zipgen.build(ents, zip64=len(ents) >= 65535)
+    lib = zsblib.load_product()
+    harr = np.frombuffer(data, dtype=np.uint8)
+    cnt = ctypes.c_size_t(0)
+    zarr = (zsblib.ZipEntry * len(ents))()
+    t0 = time.perf_counter()
+    rc = lib.zsb_zip_scan(ctypes.c_void_p(harr.ctypes.data), len(data), zarr, len(ents), ctypes.byref(cnt))
+    scan_ms = (time.perf_counter() - t0) * 1e3
+    assert rc == 0 and cnt.value == len(ents)
+    zents = list(zarr)
+    n = len(zents)
+    sizes = np.array([e.uncomp_size for e in zents], dtype=np.uint64)
+    offs = np.concatenate(([0], np.cumsum(sizes)[:-1])).astype(np.uint64)
+    total = int(sizes.sum())
+    t_zip = torch.frombuffer(bytearray(data), dtype=torch.uint8).cuda()
+    t_out = torch.zeros(total, dtype=torch.uint8, device="cuda")
+    earr = zarr
+    res = (zsblib.Result * n)()
+    eng = zsblib.Zsb(devices=[0])
+    eng.set_option("path", args.path)
+
+    def step():
+        rc = lib.zsb_zip_inflate(eng.ctx, ctypes.c_void_p(t_zip.data_ptr()), earr, n, ctypes.c_void_p(t_out.data_ptr()),
+                                 offs.ctypes.data, res)
+        assert rc == 0, eng.error()
+    step()
+    torch.cuda.synchronize()
+    t0 = time.perf_counter()
+    for _ in range(args.steps):
+        step()
+    ms = (time.perf_counter() - t0) / args.steps * 1e3
+    bad = [i for i in range(n) if res[i].ret != 1]
+    exp = torch.frombuffer(bytearray(b"".join(m[2] for m in w["distinct"])), dtype=torch.uint8).cuda()
+    B = exp.numel()
+    same = all(bool(torch.equal(t_out[t * B:(t + 1) * B], exp)) for t in range(w["tiles"]))
+    launches = int(lib.zsb_last_launches(eng.ctx))
+    eng.close()
+    return {"config": "ZIP", "workload": "one ZIP archive, %d entries (80%% method 8, 20%% method 9), 1-256 KiB, archive and "
+            "outputs in HBM; decode + CRC-32 of every entry on the GPU" % n, "members": n, "archive_bytes": len(data),
+            "out_bytes": total, "scan_ms_host": scan_ms, "ms_per_step": ms, "decompressed_gbs": total / ms / 1e6,
+            "gpu_launches_per_step": launches, "timer": "host clock around the synchronous zsb_zip_inflate() call",
+            "parity": "ok" if (not bad and same) else "MISMATCH", "mismatches": bad[:5], "path": args.path}
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("configs", nargs="*", default=["C3", "C4", "C5"])
@@ -26,6 +87,9 @@ def main():
     full = {"C3": dict(distinct=8, tiles=512), "C4": dict(distinct=512, tiles=32), "C5": dict(distinct=2048, tiles=512)}
     small = {"C3": dict(distinct=8, tiles=32), "C4": dict(distinct=512, tiles=2), "C5": dict(distinct=2048, tiles=32)}
     for c in args.configs:
+        if c == "ZIP":
+            print(json.dumps(zip_bench(args)), flush=True)
+            continue
         w = workloads.BUILDERS[c](**(small if args.small else full)[c])
         eng = zsblib.Zsb(devices=[0])
         eng.set_option("path", args.path)

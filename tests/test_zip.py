@@ -141,3 +141,65 @@ def test_gpu_zip_inflate_all_methods(z64):
                     assert res[i].check == zlib.crc32(src["plain"]) & 0xffffffff
     finally:
         eng.close()
+
+
+@pytest.mark.gpu
+def test_gpu_gunzip_files_of_several_members():
+    """concatenated gzip members; the checker decodes member by member with the oracle
+    (one inflateInit2/inflate/inflateEnd per member, advancing by total_in, as the reference would be driven)."""
+    import orclib
+    chk = orclib.ref() or orclib.orc()
+    rnd = random.Random(21)
+    files = []
+    for f in range(24):
+        parts = []
+        for k in range(rnd.randrange(1, 6)):
+            plain = gen.word_soup(rnd.randrange(0, 90000), 300 + 10 * f + k)
+            parts.append(gen.deflate(plain, rnd.choice((1, 6, 9)), 31))
+        data = b"".join(parts)
+        if f % 6 == 4:
+            data = data[:-5]                         # the last member's trailer is cut
+        if f % 6 == 5:
+            data += b"\x00\x00\x00\x00"              # something that is not a member follows
+        files.append(data)
+    files.append(b"")
+    n = len(files)
+    caps = []
+    want = []
+    for data in files:                               # member by member with the oracle
+        pos, out, last, members = 0, b"", None, 0
+        cap = 600000
+        while True:
+            r, o = chk.oneshot(data[pos:], cap - len(out), 31)
+            last = r
+            out += o
+            pos += r.total_in
+            if r.ret != 1:
+                break
+            members += 1
+            if pos >= len(data):
+                break
+        want.append((last.ret, last.msg_id, pos, out, members))
+        caps.append(cap)
+    ibufs = [ctypes.create_string_buffer(d, max(len(d), 1)) for d in files]
+    obufs = [ctypes.create_string_buffer(c) for c in caps]
+    iarr = (ctypes.c_void_p * n)(*[ctypes.addressof(b) for b in ibufs])
+    oarr = (ctypes.c_void_p * n)(*[ctypes.addressof(b) for b in obufs])
+    ilen = (ctypes.c_size_t * n)(*[len(d) for d in files])
+    ocap = (ctypes.c_size_t * n)(*caps)
+    res = (zsblib.Result * n)()
+    cnt = (ctypes.c_uint32 * n)()
+    LIB.zsb_gunzip_files.argtypes = [ctypes.c_void_p, ctypes.c_size_t, ctypes.c_void_p, ctypes.c_void_p, ctypes.c_void_p,
+                                     ctypes.c_void_p, ctypes.c_int, ctypes.c_void_p, ctypes.c_void_p]
+    eng = zsblib.Zsb(devices=[0])
+    try:
+        rc = LIB.zsb_gunzip_files(eng.ctx, n, iarr, ilen, oarr, ocap, 31, res, cnt)
+        assert rc == 0, eng.error()
+    finally:
+        eng.close()
+    for i, (ret, msg, tin, out, members) in enumerate(want):
+        got = obufs[i].raw[:res[i].total_out]
+        assert (res[i].ret, res[i].msg_id, res[i].total_in, cnt[i]) == (ret, msg, tin, members), (i, res[i], want[i][:3])
+        assert got == out, i
+    import gzip
+    assert obufs[0].raw[:res[0].total_out] == gzip.decompress(files[0])

@@ -131,3 +131,52 @@ extern "C" int zsb_zip_inflate(zsb_ctx *ctx, const void *zip, const zsb_zip_entr
     }
     return 0;
 }
+
+// gzip files of several members: rounds of one member per unfinished file (include/zsb.h)
+extern "C" int zsb_gunzip_files(zsb_ctx *ctx, size_t n, const void *const *in, const size_t *in_len, void *const *out,
+                                const size_t *out_cap, int window_bits, zsb_result *r, uint32_t *members) {
+    if (!ctx || (n && (!in || !in_len || !out || !out_cap || !r))) return ZSB_E_ARG;
+    std::vector<size_t> live(n), ipos(n, 0), opos(n, 0);
+    for (size_t i = 0; i < n; i++) {
+        live[i] = i;
+        memset(&r[i], 0, sizeof r[i]);
+        r[i].ret = -5;                                    // an empty buffer: Z_BUF_ERROR, as inflate() on no input
+        if (members) members[i] = 0;
+    }
+    std::vector<zsb_member> m;
+    std::vector<zsb_result> rr;
+    while (!live.empty()) {
+        m.resize(live.size());
+        rr.resize(live.size());
+        for (size_t k = 0; k < live.size(); k++) {
+            const size_t i = live[k];
+            m[k].in = (const uint8_t *)in[i] + ipos[i];
+            m[k].in_len = in_len[i] - ipos[i];
+            m[k].out = (uint8_t *)out[i] + opos[i];
+            m[k].out_cap = out_cap[i] - opos[i];
+            m[k].window_bits = window_bits;
+            m[k].flags = 0;
+        }
+        const int rc = zsb_inflate_batch(ctx, live.size(), m.data(), rr.data());
+        if (rc) return rc;
+        std::vector<size_t> next;
+        for (size_t k = 0; k < live.size(); k++) {
+            const size_t i = live[k];
+            const zsb_result &x = rr[k];
+            r[i].ret = x.ret;
+            r[i].msg_id = x.msg_id;
+            r[i].check = x.check;
+            r[i].data_type = x.data_type;
+            r[i].total_in += x.total_in;
+            r[i].total_out += x.total_out;
+            ipos[i] += (size_t)x.total_in;
+            opos[i] += (size_t)x.total_out;
+            if (x.ret == 1) {
+                if (members) members[i]++;
+                if (ipos[i] < in_len[i]) next.push_back(i);       // another member follows
+            }
+        }
+        live.swap(next);
+    }
+    return 0;
+}
