@@ -78,7 +78,7 @@ def main():
     ap.add_argument("--path", type=int, default=0, help="0 length-aware split (default), 1 lane path only, 2 group path only")
     ap.add_argument("--lanes", type=int, default=0)
     ap.add_argument("--small", action="store_true")
-    ap.add_argument("--split", action="store_true", help="option split_big: large members to the group path")
+    ap.add_argument("--no-split", action="store_true", help="option split_big = 0: no k_big for large members")
     ap.add_argument("--steps", type=int, default=3)
     args = ap.parse_args()
     import config_runner
@@ -93,8 +93,8 @@ def main():
         w = workloads.BUILDERS[c](**(small if args.small else full)[c])
         eng = zsblib.Zsb(devices=[0])
         eng.set_option("path", args.path)
-        if args.split:
-            eng.set_option("split_big", 1)
+        if args.no_split:
+            eng.set_option("split_big", 0)
         if args.lanes:
             eng.set_option("lanes_per_member", args.lanes)
         r = config_runner.run(w, eng, steps=args.steps, warmup=2)

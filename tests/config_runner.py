@@ -78,12 +78,16 @@ def run(w, eng, dev=0, steps=2, warmup=1, flags=None):
         step()
     torch.cuda.synchronize(device)
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    eng.set_option("profile", 1)
     e0.record(stream)
     for _ in range(steps):
         step()
     e1.record(stream)
     torch.cuda.synchronize(device)
     ms = e0.elapsed_time(e1) / steps
+    pa, pb = ctypes.c_double(0), ctypes.c_double(0)
+    pairs = eng.lib.zsb_profile_read(eng.ctx, 0, ctypes.byref(pa), ctypes.byref(pb))
+    eng.set_option("profile", 0)
     launches = eng.lib.zsb_last_launches(eng.ctx)
 
     # every member's record
@@ -106,5 +110,6 @@ def run(w, eng, dev=0, steps=2, warmup=1, flags=None):
     sum_in, sum_out = int(lens.sum()) * tiles, int(rec["tout"].sum()) * tiles
     return {"workload": w["desc"], "members": n, "distinct": K, "ms_per_step": ms, "in_bytes": sum_in, "out_bytes": sum_out,
             "decompressed_gbs": sum_out / ms / 1e6, "in_plus_out_gbs": (sum_in + sum_out) / ms / 1e6,
-            "gpu_launches_per_step": int(launches), "non_ok_members": int((rec["ret"] != 1).sum()) * tiles,
+            "gpu_launches_per_step": int(launches), "decode_kernels_ms_per_step": pa.value / steps,
+            "k_lz_ms_per_step": pb.value / steps, "decode_lz_pairs_per_step": pairs / steps, "non_ok_members": int((rec["ret"] != 1).sum()) * tiles,
             "mismatches": bad}

@@ -58,6 +58,9 @@ extern "C" int emul_decode(const uint8_t *in, size_t in_len, uint8_t *out, size_
     return res->ret;
 }
 
+static int g_big = 0;
+extern "C" void emul_set_big(int on) { g_big = on; }
+
 // the lane path with a warp of one lane: k_lane's decoder, then k_lz's resolver
 extern "C" int emul_decode_lane(const uint8_t *in, size_t in_len, uint8_t *out, size_t out_cap, int wbits,
                                 zsb_result *res, uint32_t *aux4, uint64_t seq_cap, uint32_t *nseq_out) {
@@ -87,7 +90,13 @@ extern "C" int emul_decode_lane(const uint8_t *in, size_t in_len, uint8_t *out, 
     B.members = &m; B.results = res; B.aux = &a; B.order = &order; B.seq_off = &seq_off; B.seq_base = seq;
     B.hist = nullptr; B.n = 1; B.counter = &counter; B.fixed_tab = fixed;
     uint32_t ring[lane::RING_WORDS] = {0, 0, 0, 0};
-    lane::warp_lanes<1>(B, T, scr, ring, lut, 0);
+    if (g_big) {                                     // k_big's decoder: lane 0 with the direct tables
+        alignas(16) static uint32_t big_lut[lane::BIG_LUT_BYTES / 4];
+        memset(big_lut, 0xA5, sizeof big_lut);
+        lane::warp_lanes<1, true>(B, T, scr, ring, lut, 0, big_lut);
+    } else {
+        lane::warp_lanes<1>(B, T, scr, ring, lut, 0);
+    }
     if (nseq_out) *nseq_out = a.nseq;
     int rc = res->ret;
     if (a.nseq > seq_cap) rc = -1000;               // the host's scratch bound was too small

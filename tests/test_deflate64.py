@@ -30,7 +30,7 @@ def test_restatement_matches_reference():
         assert a.astuple() == b.astuple() and ao == bo, (name, a, b)
 
 
-@pytest.mark.parametrize("lane", [True, False], ids=["lane", "group"])
+@pytest.mark.parametrize("lane", [True, False, "big"], ids=["lane", "group", "big"])
 def test_emulated_device_source(lane):
     em = zsblib.emul()
     items = [(n, d, w, len(p) + 8) for n, d, w, p in cases.deflate64_streams()] + cases.deflate64_damaged(120)
@@ -42,14 +42,18 @@ def test_emulated_device_source(lane):
 
 
 @pytest.mark.gpu
-@pytest.mark.parametrize("lanes", [0, 16])
+@pytest.mark.parametrize("lanes", [0, "big", 16])
 def test_gpu_deflate64(lanes):
     eng = zsblib.Zsb()
     try:
-        eng.set_option("path", 1 if lanes == 0 else 2)
-        if lanes:
-            eng.set_option("lanes_per_member", lanes)
-        items = [(n, d, w, len(p) + 8) for n, d, w, p in cases.deflate64_streams(big=(lanes == 0))]
+        if lanes == "big":                       # every member through k_big
+            eng.set_option("path", 0)
+            eng.set_option("split_big", 2)
+        else:
+            eng.set_option("path", 1 if lanes == 0 else 2)
+            if lanes:
+                eng.set_option("lanes_per_member", lanes)
+        items = [(n, d, w, len(p) + 8) for n, d, w, p in cases.deflate64_streams(big=(lanes != 16))]
         items += cases.deflate64_damaged(200)
         got = eng.inflate_batch([d for _, d, _, _ in items], [w for _, _, w, _ in items], [c for _, _, _, c in items])
         for (name, data, wb, cap), (r, out) in zip(items, got):

@@ -14,7 +14,7 @@ CHK = orclib.ref() or orclib.orc()
 EM = zsblib.emul()
 
 
-PATHS = pytest.mark.parametrize("lane", [True, False], ids=["lane", "group"])
+PATHS = pytest.mark.parametrize("lane", [True, False, "big"], ids=["lane", "group", "big"])
 
 
 def same(name, data, wb, cap, lane):

@@ -11,13 +11,17 @@ import zsblib
 
 pytestmark = pytest.mark.gpu
 CHK = orclib.ref() or orclib.orc()
-# decoder configurations: 0 = the lane path (k_lane + k_lz), else the group path with that many lanes
-LANES = [0, 32, 1, 4, 8, 2, 16]
+# decoder configurations: 0 = the lane path (k_lane + k_lz), "big" = every member through k_big (a warp each,
+# direct tables) + k_lz, else the group path with that many lanes
+LANES = [0, "big", 32, 1, 4, 8, 2, 16]
 
 
 def select(eng, lanes):
     if lanes == 0:
         eng.set_option("path", 1)
+    elif lanes == "big":
+        eng.set_option("path", 0)
+        eng.set_option("split_big", 2)
     else:
         eng.set_option("path", 2)
         eng.set_option("lanes_per_member", lanes)

@@ -189,7 +189,8 @@ class Emul:
         buf = ctypes.create_string_buffer(max(out_cap, 1))
         r = Result()
         aux = (ctypes.c_uint32 * 4)()
-        if lane:
+        if lane:                                    # True = k_lane's decoder, "big" = k_big's (lane 0 + direct tables)
+            self.lib.emul_set_big(1 if lane == "big" else 0)
             nseq = ctypes.c_uint32(0)
             rc = self.lib.emul_decode_lane(buf_in, len(data), buf if out_cap else None, out_cap, wbits,
                                            ctypes.byref(r), aux, self.seq_bound(len(data), out_cap), ctypes.byref(nseq))

@@ -94,11 +94,13 @@ struct Scratch {
     uint8_t *plan;         // n * 12 + 64 bytes: sequence offsets (u64) + slot order (u32)
     uint8_t *seq;          // sequence arena
     size_t seq_bytes;
-    uint32_t *counters;    // 4 work counters
-    const std::vector<size_t> *cuts;   // lane path: slices planned by the caller (lane_plan), who has also sent
-                           // the slot order and the sequence offsets to `plan`: run_device then issues no copy
-                           // of its own (it would queue behind every input copy already submitted)
-    size_t nbig;           // with cuts: the first nbig slots go to the group path (split_big), the plan covers the rest
+    uint32_t *counters;    // 8 work counters (4 for the large members' part)
+    // Planned by the caller (plan_parts), who has also sent the slot order and the sequence offsets to `plan`
+    // and zeroed the counters: run_device then issues no copy of its own (it would queue behind every input
+    // copy already submitted).  NULL cuts = not planned.
+    const std::vector<size_t> *cuts, *cuts_big;
+    size_t nbig;           // the first nbig slots are the large members (split_big)
+    uint64_t big_seqs;     // sequences at the start of `seq` that belong to the large members' part
     bool small_ctas;       // k_lane in CTAs of lane::PIPE_WARPS warps, one per 32*PIPE_WARPS members, so that
                            // launches on different streams share the SMs
 };
@@ -171,30 +173,46 @@ static int run_group(zsb_ctx *ctx, zsb_dev &dv, size_t n, const zsb_member *dm, 
 }
 
 // The length-aware split of a batch whose slot order is largest first.  In the lane path a member is
-// decoded by ONE lane at about LANE_NS_PER_BYTE of (in + out), however empty the GPU is, so a member much
-// larger than the rest would keep the batch waiting: the first `nbig` slots, whose own lane time exceeds
-// what the remaining members need together, are decoded by the group path instead (a warp or half-warp
-// per member).  Returns nbig (0 when the batch is uniform).
-static size_t split_big(const zsb_member *hm, const uint32_t *order, size_t n) {
-    const double LANE_NS_PER_BYTE = 100;        // measured: 97 KB of in + out in ~20 ms at full occupancy (C2), about
-                                                // twice as fast when the SM is nearly empty (the tail of C4)
-    const double LANE_BATCH_BYTES_PER_NS = 190.0;   // in + out bytes per ns of the whole lane path (C2)
-    const double FLOOR_NS = 4e6;                // a lane batch is not worth less than a few ms
-    double rem = 0;
-    for (size_t i = 0; i < n; i++) rem += (double)hm[i].in_len + (double)hm[i].out_cap;
-    size_t nbig = 0;
-    while (nbig < n) {
-        const zsb_member &x = hm[order ? order[nbig] : nbig];
-        const double c = (double)x.in_len + (double)x.out_cap;
-        if (c * LANE_NS_PER_BYTE <= 1.5 * std::max(rem / LANE_BATCH_BYTES_PER_NS, FLOOR_NS)) break;
-        rem -= c;
-        nbig++;
+// decoded by ONE lane at a fixed pace, so a member much larger than the rest keeps the batch waiting; k_big
+// gives a member a warp of its own and decodes it 2-4 times faster, but the whole GPU then decodes only
+// ~26 bytes/ns of in + out against the lane path's ~190.  Both parts run side by side, so the first nbig slots
+// go to k_big where that minimises max(time of the big part, time of the rest) under this model (measured,
+// scripts/big_pace.py and bench.py; bytes are in_len + out_cap):
+//   lane path:  whole part 190 B/ns; its largest member alone 150 ns/B
+//   k_big:      whole part 26 B/ns; its largest member alone 40 ns/B with <= 4 members per SM, rising to
+//               90 ns/B at 16 per SM (the ALU pipe of an SM sub-partition is shared by its warps)
+// Returns nbig (0 for a uniform batch).
+static size_t split_big(const zsb_member *hm, const uint32_t *order, size_t n, int sm_count) {
+    auto cost = [&](size_t s) {
+        const zsb_member &x = hm[order ? order[s] : s];
+        return (double)x.in_len + (double)x.out_cap;
+    };
+    double total = 0;
+    for (size_t s = 0; s < n; s++) total += cost(s);
+    if (n == 0) return 0;
+    const double c0 = cost(0);
+    const double lo = 4.0 * sm_count, hi = 16.0 * sm_count;
+    double best = std::max(total / 190.0, c0 * 150.0), big_bytes = 0;
+    size_t best_n = 0;
+    const size_t most = std::min<size_t>(n, (size_t)(2 * hi));          // at most two rounds of warps
+    for (size_t k = 1; k <= most; k++) {
+        big_bytes += cost(k - 1);
+        const double dens = k <= lo ? 0.0 : std::min(1.0, (k - lo) / (hi - lo));
+        const double rounds = std::max(1.0, k / hi);
+        const double tb = std::max(big_bytes / 26.0, c0 * (40.0 + 50.0 * dens) * rounds);
+        const double tl = k < n ? std::max((total - big_bytes) / 190.0, cost(k) * 150.0) : 0.0;
+        const double t = std::max(tb, tl);
+        if (t < 0.9 * best) {            // worth a second pair of launches only for a clear gain
+            best = t;
+            best_n = k;
+        } else if (best_n && t < best) {
+            best = t;
+            best_n = k;
+        }
+        if (tb > best) break;
     }
-    return nbig;
+    return best_n;
 }
-// lanes per member for the large members: the leader lane's symbol decode sets the pace, and 16 lanes measured
-// faster per member than 32 (C4: 2.05 s against 2.68 s for the same 16 MiB members)
-static int group_lanes_for(const zsb_dev &, size_t) { return 16; }
 
 // Per-slot sequence offsets (off[n]) and the slices [cuts[k], cuts[k+1]) of the slot order, cut where the
 // arena of arena_seqs sequences would overflow.  Returns the most sequences a slice needs.
@@ -218,61 +236,118 @@ static uint64_t lane_plan(const zsb_member *hm, const uint32_t *horder, size_t n
     return most;
 }
 
-// lane path: k_lane + k_lz over slices of the slot order whose sequence scratch fits the arena
-static int run_lane(zsb_ctx *ctx, zsb_dev &dv, size_t n, const zsb_member *dm, zsb_result *dr,
-                    const zsb_member *hm, const uint32_t *horder, const uint32_t *dorder, uint64_t *dseqoff,
-                    cudaStream_t st, const Scratch *sc, bool zero_counters) {
-    if (!dv.lane_configured) {
-        CK(ctx, cudaFuncSetAttribute(k_lane, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)lane::SMEM));
-        // all of the SM's memory as shared memory also for the small CTAs (the default carve-out fits fewer of them)
-        CK(ctx, cudaFuncSetAttribute(k_lane, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared));
-        int occ = 0;
-        CK(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, k_lane, lane::WARPS * 32, lane::SMEM));
-        if (occ < 1) {
-            snprintf(ctx->err, sizeof ctx->err, "k_lane does not fit an SM");
-            return ZSB_E_CUDA;
-        }
-        CK(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&dv.lane_small_occ, k_lane, lane::PIPE_WARPS * 32,
-                                                              lane::smem_for(lane::PIPE_WARPS)));
-        CK(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&dv.lz_occ, k_lz, LZ_THREADS, 0));
-        if (dv.lz_occ < 1) dv.lz_occ = 1;
-        dv.lane_configured = true;
+// The plan of a batch whose first nbig slots are its large members: both parts' sequence offsets (off[n]; the
+// small part's start after the big part's big_seqs sequences) and slices.  Returns the sequences needed.
+static uint64_t plan_parts(const zsb_member *hm, const uint32_t *order, size_t n, size_t nbig, uint64_t arena_seqs,
+                           uint64_t *off, std::vector<size_t> &cuts_big, std::vector<size_t> &cuts, uint64_t &big_seqs) {
+    // each part may use the arena in proportion to what it could need
+    double need_big = 0, need_all = 0;
+    for (size_t s = 0; s < n; s++) {
+        const double b = (double)seq_bound(hm[order ? order[s] : s]);
+        need_all += b;
+        if (s < nbig) need_big += b;
     }
-    // per-slot sequence offsets, slices cut where the arena would overflow
-    std::vector<uint64_t> off_own;
-    std::vector<size_t> cuts_own;
-    const std::vector<size_t> *pcuts = sc ? sc->cuts : nullptr;
-    uint32_t *counters = sc ? sc->counters : dv.counters;
-    if (!pcuts) {          // not planned by the caller: plan here and send the offsets on this stream
-        off_own.resize(n);
-        const uint64_t most = lane_plan(hm, horder, n, (sc ? sc->seq_bytes : ctx->seq_arena_bytes) / sizeof(lane::seq_t),
-                                        off_own.data(), cuts_own);
-        int rc;
-        if (!sc && (rc = grow(ctx, dv.d_seq, dv.d_seq_cap, (size_t)most * sizeof(lane::seq_t)))) return rc;
-        // (a pageable source is staged by the runtime before cudaMemcpyAsync returns, so off_own may go)
-        CK(ctx, cudaMemcpyAsync(dseqoff, off_own.data(), n * sizeof(uint64_t), cudaMemcpyHostToDevice, st));
-        pcuts = &cuts_own;
+    uint64_t arena_big = arena_seqs;
+    if (nbig && nbig < n && need_all > (double)arena_seqs)
+        arena_big = (uint64_t)std::max(1.0, (double)arena_seqs * need_big / need_all);
+    big_seqs = nbig ? lane_plan(hm, order, nbig, arena_big, off, cuts_big) : 0;
+    const uint64_t left = arena_seqs > big_seqs ? arena_seqs - big_seqs : 1;
+    const uint64_t most = n > nbig ? lane_plan(hm, order ? order + nbig : nullptr, n - nbig, left, off + nbig, cuts) : 0;
+    for (size_t s = nbig; s < n; s++) off[s] += big_seqs;
+    return big_seqs + most;
+}
+
+// One part of a batch on the lane path: k_lane (or k_big: a warp per member, for the large members) + k_lz
+// over the slices `cuts` of the part's slot order.  dorder / dseqoff point at the part's first slot.
+struct LanePart {
+    const uint32_t *dorder;
+    const uint64_t *dseqoff;
+    const std::vector<size_t> *cuts;
+    Aux *aux;
+    lane::seq_t *seq_base;
+    uint32_t *counters;        // 4 of them, zero for the first slice
+    cudaStream_t st;
+    bool small_ctas, big, timed;
+};
+
+static int lane_configure(zsb_ctx *ctx, zsb_dev &dv) {
+    if (dv.lane_configured) return 0;
+    CK(ctx, cudaFuncSetAttribute(k_lane, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)lane::SMEM));
+    // all of the SM's memory as shared memory also for the small CTAs (the default carve-out fits fewer of them)
+    CK(ctx, cudaFuncSetAttribute(k_lane, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared));
+    int occ = 0;
+    CK(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, k_lane, lane::WARPS * 32, lane::SMEM));
+    if (occ < 1) {
+        snprintf(ctx->err, sizeof ctx->err, "k_lane does not fit an SM");
+        return ZSB_E_CUDA;
     }
-    const std::vector<size_t> &cuts = *pcuts;
+    CK(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&dv.lane_small_occ, k_lane, lane::PIPE_WARPS * 32,
+                                                          lane::smem_for(lane::PIPE_WARPS)));
+    CK(ctx, cudaFuncSetAttribute(k_big, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)BIG_SMEM));
+    CK(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&dv.big_occ, k_big, BIG_WARPS * 32, BIG_SMEM));
+    if (dv.big_occ < 1) dv.big_occ = 1;
+    CK(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&dv.lz_occ, k_lz, LZ_THREADS, 0));
+    if (dv.lz_occ < 1) dv.lz_occ = 1;
+    dv.lane_configured = true;
+    return 0;
+}
+
+static int launch_lane(zsb_ctx *ctx, zsb_dev &dv, const zsb_member *dm, zsb_result *dr, const LanePart &P) {
+    int rc0 = lane_configure(ctx, dv);
+    if (rc0) return rc0;
+    cudaStream_t st = P.st;
+    uint32_t *counters = P.counters;
+    const std::vector<size_t> &cuts = *P.cuts;
     for (size_t k = 0; k + 1 < cuts.size(); k++) {
         const size_t first = cuts[k], cnt = cuts[k + 1] - cuts[k];
-        // (a planned chunk's counters were zeroed by the caller ahead of its input copies)
-        // (and when the group path ran first it zeroed them; it only uses counters[3], so does not dirty these)
-        if ((!(sc && sc->cuts) && zero_counters) || k > 0) CK(ctx, cudaMemsetAsync(counters, 0, 3 * sizeof(uint32_t), st));
+        // (the caller zeroed the counters for the first slice; [1] is k_check's and stays)
+        if (k > 0) {
+            CK(ctx, cudaMemsetAsync(counters, 0, sizeof(uint32_t), st));
+            CK(ctx, cudaMemsetAsync(counters + 2, 0, sizeof(uint32_t), st));
+        }
         lane::Batch B;
         B.members = dm;
         B.results = dr;
-        B.aux = sc ? sc->aux : dv.aux;
-        B.order = dorder + first;
-        B.seq_off = dseqoff + first;
-        B.seq_base = (lane::seq_t *)(sc ? sc->seq : dv.d_seq);
+        B.aux = P.aux;
+        B.order = P.dorder + first;
+        B.seq_off = P.dseqoff + first;
+        B.seq_base = P.seq_base;
         B.hist = nullptr;
         B.n = (uint32_t)cnt;
         B.counter = counters;
         B.fixed_tab = dv.fixed_lane;
         size_t warps, per_cta;
         unsigned grid;
-        if ((sc && sc->small_ctas) || ctx->force_small_ctas) {
+        if (P.big) {
+            // a warp per member; with few members, CTAs of just the warps needed so that they spread over the SMs
+            const size_t per_sm = (cnt + dv.sm_count - 1) / dv.sm_count;
+            warps = std::min<size_t>(BIG_WARPS, std::max<size_t>(1, per_sm));
+            per_cta = warps;
+            grid = (unsigned)std::max<size_t>(1, std::min((cnt + warps - 1) / warps, (size_t)dv.sm_count * dv.big_occ));
+            cudaEvent_t *pb = nullptr;
+            if (ctx->profile) {
+                if (dv.prof_used + 3 > dv.prof_ev.size()) {
+                    const size_t old = dv.prof_ev.size();
+                    dv.prof_ev.resize(old + 96);
+                    for (size_t i = old; i < dv.prof_ev.size(); i++) CK(ctx, cudaEventCreate(&dv.prof_ev[i]));
+                }
+                pb = &dv.prof_ev[dv.prof_used];
+                dv.prof_used += 3;
+                CK(ctx, cudaEventRecord(pb[0], st));
+            }
+            k_big<<<grid, (unsigned)(warps * 32), LUT_BYTES + warps * BIG_PER_WARP, st>>>(B);
+            ctx->launches++;
+            CK(ctx, cudaGetLastError());
+            if (pb) CK(ctx, cudaEventRecord(pb[1], st));
+            const size_t wpc0 = LZ_THREADS / 32;
+            grid = (unsigned)std::max<size_t>(1, std::min((cnt + wpc0 - 1) / wpc0, (size_t)dv.sm_count * dv.lz_occ));
+            k_lz<<<grid, LZ_THREADS, 0, st>>>(B, counters + 2);
+            ctx->launches++;
+            CK(ctx, cudaGetLastError());
+            if (pb) CK(ctx, cudaEventRecord(pb[2], st));
+            continue;
+        }
+        if (P.small_ctas || ctx->force_small_ctas) {
             warps = lane::PIPE_WARPS;
             per_cta = warps * 32;
             grid = (unsigned)std::max<size_t>(1, std::min((cnt + per_cta - 1) / per_cta, (size_t)dv.sm_count * dv.lane_small_occ));
@@ -284,7 +359,7 @@ static int run_lane(zsb_ctx *ctx, zsb_dev &dv, size_t n, const zsb_member *dm, z
             grid = (unsigned)std::max<size_t>(1, std::min((cnt + per_cta - 1) / per_cta, (size_t)dv.sm_count));
         }
         cudaEvent_t *pe = nullptr;
-        if (ctx->profile) {
+        if (ctx->profile && P.timed) {
             if (dv.prof_used + 3 > dv.prof_ev.size()) {
                 const size_t old = dv.prof_ev.size();
                 dv.prof_ev.resize(old + 96);
@@ -325,36 +400,68 @@ static int run_device(zsb_ctx *ctx, zsb_dev &dv, size_t n, const zsb_member *dm,
     uint32_t *dorder = (uint32_t *)(dseqoff + n);
     const bool planned = sc && sc->cuts;
     std::vector<uint32_t> own;
+    std::vector<uint64_t> off_own;
+    std::vector<size_t> cuts_own, cuts_big_own;
+    const std::vector<size_t> *cuts = planned ? sc->cuts : &cuts_own, *cuts_big = planned ? sc->cuts_big : &cuts_big_own;
     size_t nbig = planned ? sc->nbig : 0;
+    uint64_t big_seqs = planned ? sc->big_seqs : 0;
+    uint32_t *counters = sc ? sc->counters : dv.counters;
     if (!planned) {
         if (!horder) {
             own.resize(n);
             for (size_t i = 0; i < n; i++) own[i] = (uint32_t)i;
-            if (ctx->path == 0)          // the split needs the largest members first
+            if (ctx->path == 0)          // largest first: lanes finish together, and the split needs it
                 std::stable_sort(own.begin(), own.end(), [&](uint32_t a, uint32_t b) {
                     return hm[a].in_len + hm[a].out_cap > hm[b].in_len + hm[b].out_cap;
                 });
             horder = own.data();
         }
-        if (ctx->path == 0 && ctx->split_big) nbig = split_big(hm, horder, n);
-        else if (ctx->path == 2) nbig = n;
         CK(ctx, cudaMemcpyAsync(dorder, horder, n * sizeof(uint32_t), cudaMemcpyHostToDevice, st));
-    }
-    // large members on the group stream, beside the lane path on the caller's stream (fork / join by events)
-    const bool fork = nbig && nbig < n;
-    if (nbig) {
-        const int lanes = ctx->path == 2 ? ctx->lanes : group_lanes_for(dv, nbig);
-        if (!planned) CK(ctx, cudaMemsetAsync(sc ? sc->counters : dv.counters, 0, 4 * sizeof(uint32_t), st));
-        if (fork) {
-            CK(ctx, cudaEventRecord(dv.ev_fork, st));
-            CK(ctx, cudaStreamWaitEvent(dv.group_stream, dv.ev_fork, 0));
+        CK(ctx, cudaMemsetAsync(counters, 0, 8 * sizeof(uint32_t), st));
+        if (ctx->path != 2) {
+            if (ctx->path == 0 && ctx->split_big) nbig = ctx->split_big == 2 ? n : split_big(hm, horder, n, dv.sm_count);
+            off_own.resize(n);
+            const uint64_t need = plan_parts(hm, horder, n, nbig, (sc ? sc->seq_bytes : ctx->seq_arena_bytes) / sizeof(lane::seq_t),
+                                             off_own.data(), cuts_big_own, cuts_own, big_seqs);
+            if (!sc && (rc = grow(ctx, dv.d_seq, dv.d_seq_cap, (size_t)need * sizeof(lane::seq_t)))) return rc;
+            // (a pageable source is staged by the runtime before cudaMemcpyAsync returns, so off_own may go)
+            CK(ctx, cudaMemcpyAsync(dseqoff, off_own.data(), n * sizeof(uint64_t), cudaMemcpyHostToDevice, st));
         }
-        if ((rc = run_group(ctx, dv, nbig, dm, dr, dorder, fork ? dv.group_stream : st, sc, lanes))) return rc;
-        if (fork) CK(ctx, cudaEventRecord(dv.ev_join, dv.group_stream));
     }
-    if (nbig < n && (rc = run_lane(ctx, dv, n - nbig, dm, dr, hm, horder + nbig, dorder + nbig, dseqoff + nbig, st, sc, nbig == 0)))
-        return rc;
-    if (fork) CK(ctx, cudaStreamWaitEvent(st, dv.ev_join, 0));
+    {
+        static const bool trace = getenv("ZSB_TRACE") != nullptr;
+        if (trace && !planned)
+            fprintf(stderr, "zsb trace decode: %zu members, %zu to k_big (%zu slices, %llu sequences), rest %zu slices\n", n,
+                    nbig, cuts_big->size() ? cuts_big->size() - 1 : 0, (unsigned long long)big_seqs,
+                    cuts->size() ? cuts->size() - 1 : 0);
+    }
+    if (ctx->path == 2) {
+        if ((rc = run_group(ctx, dv, n, dm, dr, dorder, st, sc, ctx->lanes))) return rc;
+    } else {
+        LanePart P;
+        P.aux = sc ? sc->aux : dv.aux;
+        P.small_ctas = sc && sc->small_ctas;
+        lane::seq_t *seq0 = (lane::seq_t *)(sc ? sc->seq : dv.d_seq);
+        // the large members, a warp each, on the group stream beside the rest on the caller's (fork / join by events)
+        const bool fork = nbig && nbig < n;
+        if (nbig) {
+            P.dorder = dorder; P.dseqoff = dseqoff; P.cuts = cuts_big; P.seq_base = seq0;
+            P.counters = counters + 4; P.big = true; P.timed = false;
+            P.st = fork ? dv.group_stream : st;
+            if (fork) {
+                CK(ctx, cudaEventRecord(dv.ev_fork, st));
+                CK(ctx, cudaStreamWaitEvent(dv.group_stream, dv.ev_fork, 0));
+            }
+            if ((rc = launch_lane(ctx, dv, dm, dr, P))) return rc;
+            if (fork) CK(ctx, cudaEventRecord(dv.ev_join, dv.group_stream));
+        }
+        if (nbig < n) {
+            P.dorder = dorder + nbig; P.dseqoff = dseqoff + nbig; P.cuts = cuts; P.seq_base = seq0;
+            P.counters = counters; P.big = false; P.timed = true; P.st = st;
+            if ((rc = launch_lane(ctx, dv, dm, dr, P))) return rc;
+        }
+        if (fork) CK(ctx, cudaStreamWaitEvent(st, dv.ev_join, 0));
+    }
     if (!(flags & ZSB_RAW_ONLY)) {
         unsigned grid = (unsigned)std::min<size_t>(n, (size_t)dv.sm_count * 8);
         k_check<<<grid, CHK_THREADS, 0, st>>>(dm, dr, sc ? sc->aux : dv.aux, (uint32_t)n, (sc ? sc->counters : dv.counters) + 1);
@@ -394,7 +501,7 @@ static int init_device(zsb_ctx *ctx, zsb_dev &dv, int device) {
     CK(ctx, cudaEventCreateWithFlags(&dv.ev_join, cudaEventDisableTiming));
     CK(ctx, cudaMalloc(&dv.fixed, STREAM_BYTES));
     CK(ctx, cudaMalloc(&dv.fixed_lane, lane::SLOT));
-    CK(ctx, cudaMalloc(&dv.counters, 4 * MAX_CHUNKS_DEV * sizeof(uint32_t)));
+    CK(ctx, cudaMalloc(&dv.counters, 8 * MAX_CHUNKS_DEV * sizeof(uint32_t)));
     CrcConsts cc;
     cc.x2n[0] = 0x40000000u;
     for (int k = 1; k < 40; k++) cc.x2n[k] = gf2_mul(cc.x2n[k - 1], cc.x2n[k - 1]);
@@ -501,8 +608,9 @@ extern "C" int zsb_set_option(zsb_ctx *ctx, const char *name, long value) {
         ctx->chunks = (int)value;
         return 0;
     }
-    if (!strcmp(name, "split_big")) {         // large members to the group path beside the lane path (off: measured no gain)
-        ctx->split_big = value != 0;
+    if (!strcmp(name, "split_big")) {         // 1 (default): members far larger than the rest of their batch go to k_big
+        if (value < 0 || value > 2) return ZSB_E_ARG;
+        ctx->split_big = (int)value;          // 2: every member (tests of k_big)
         return 0;
     }
     if (!strcmp(name, "small_ctas")) {        // diagnostic: k_lane in the small CTAs of the pipelined host path
@@ -764,8 +872,8 @@ static int batch_host(zsb_ctx *ctx, size_t n, const zsb_member *m, zsb_result *r
         // the three stages of every chunk: inputs on copy_stream, decode on the chunk's stream, results and
         // outputs on back_stream
         size_t plan_off = 0;
-        std::vector<std::vector<size_t>> cuts_of(K);
-        CK(ctx, cudaMemsetAsync(dv.counters, 0, 4 * (size_t)K * sizeof(uint32_t), dv.copy_stream));
+        std::vector<std::vector<size_t>> cuts_of(K), cuts_big_of(K);
+        CK(ctx, cudaMemsetAsync(dv.counters, 0, 8 * (size_t)K * sizeof(uint32_t), dv.copy_stream));
         for (int c = 0; c < K; c++) {
             Chunk &ch = chunks[c];
             zsb_member *hmc = hm + ch.first;
@@ -795,12 +903,13 @@ static int batch_host(zsb_ctx *ctx, size_t n, const zsb_member *m, zsb_result *r
             plan_off += (ch.count * (sizeof(uint64_t) + sizeof(uint32_t)) + 63) & ~(size_t)63;
             sc.seq = dv.d_seq + region_off[c % NS] * sizeof(lane::seq_t);
             sc.seq_bytes = (size_t)region[c % NS] * sizeof(lane::seq_t);
-            sc.counters = dv.counters + 4 * c;
+            sc.counters = dv.counters + 8 * c;
             sc.small_ctas = K > 1;
             // the chunk's plan travels with its inputs: slot order, and for the lane path the sequence offsets
-            sc.nbig = (ctx->path == 0 && ctx->split_big) ? split_big(hmc, hoc, ch.count) : ctx->path == 2 ? ch.count : 0;
-            lane_plan(hmc, hoc + sc.nbig, ch.count - sc.nbig, region[c % NS], hs + ch.first + sc.nbig, cuts_of[c]);
+            sc.nbig = (ctx->path == 0 && ctx->split_big) ? (ctx->split_big == 2 ? ch.count : split_big(hmc, hoc, ch.count, dv.sm_count)) : 0;
+            plan_parts(hmc, hoc, ch.count, sc.nbig, region[c % NS], hs + ch.first, cuts_big_of[c], cuts_of[c], sc.big_seqs);
             sc.cuts = &cuts_of[c];
+            sc.cuts_big = &cuts_big_of[c];
             CK(ctx, cudaMemcpyAsync(sc.plan, hs + ch.first, ch.count * sizeof(uint64_t), cudaMemcpyHostToDevice, dv.copy_stream));
             CK(ctx, cudaMemcpyAsync(sc.plan + ch.count * sizeof(uint64_t), hoc, ch.count * sizeof(uint32_t),
                                     cudaMemcpyHostToDevice, dv.copy_stream));

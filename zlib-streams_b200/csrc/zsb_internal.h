@@ -22,7 +22,7 @@ struct zsb_dev {
     uint8_t *d_plan = nullptr;         // per call: slot order (u32) + per-slot sequence offsets (u64)
     size_t d_plan_cap = 0;
     bool lane_configured = false;
-    int lz_occ = 0, lane_small_occ = 0;
+    int lz_occ = 0, lane_small_occ = 0, big_occ = 0;
     uint32_t *counters = nullptr;      // [0] decode work counter, [1] check work counter
     zsb::Aux *aux = nullptr;
     size_t aux_cap = 0;
@@ -47,7 +47,8 @@ struct zsb_ctx {
     int chunks = 0;                    // host batches: pipeline depth (0 = choose from the batch)
     long launches = 0;
     bool force_small_ctas = false;
-    bool split_big = false;            // path 0: members far larger than the rest go to the group path (split_big())
+    int split_big = 1;                 // path 0: 1 = members far larger than the rest get a warp each (k_big,
+                                       // split_big()), 0 = never, 2 = every member (tests)
     int profile = 0;                   // 1: record per-kernel events (zsb_profile_read)
     char err[256] = "";
 };

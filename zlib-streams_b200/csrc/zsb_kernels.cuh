@@ -288,6 +288,26 @@ __global__ void __launch_bounds__(lane::WARPS * 32, 1) k_lane(lane::Batch B) {
     lane::warp_lanes<32>(B, slots, scr, rings, lut, ln);
 }
 
+// Large members: one member per WARP, lane 0 decodes with direct-indexed tables (lane::big_run); same
+// sequences, same results, consumed by the same k_lz.  Per warp: build scratch, one table slot, 3 KB of
+// direct tables.
+constexpr int BIG_WARPS = 16;
+constexpr int BIG_SLOT = 480;                                  // lane::SLOT rounded up to 16
+constexpr size_t BIG_PER_WARP = lane::WSCR + BIG_SLOT + lane::BIG_LUT_BYTES;
+constexpr size_t BIG_SMEM = LUT_BYTES + (size_t)BIG_WARPS * BIG_PER_WARP;
+__global__ void __launch_bounds__(BIG_WARPS * 32, 1) k_big(lane::Batch B) {
+    extern __shared__ __align__(16) uint8_t smem[];
+    uint32_t *lut = (uint32_t *)smem;
+    init_lut(lut, threadIdx.x, blockDim.x);
+    __syncthreads();
+    const int ln = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    uint8_t *base = smem + LUT_BYTES + (size_t)warp * BIG_PER_WARP;
+    uint8_t *scr = base, *slot = base + lane::WSCR;
+    uint32_t *big_lut = (uint32_t *)(base + lane::WSCR + BIG_SLOT);
+    // (the input ring of k_lane is not used here; lane 0's ring pointer only has to be a shared address)
+    lane::warp_lanes<32, true>(B, slot, scr, (uint32_t *)scr, lut, ln, big_lut);
+}
+
 constexpr int LZ_THREADS = 256;
 __global__ void __launch_bounds__(LZ_THREADS) k_lz(lane::Batch B, uint32_t *counter) {
     const int ln = threadIdx.x & 31;

@@ -385,6 +385,109 @@ ZSB_DEV bool fast_step(Lane &L, const uint8_t *T, const uint32_t *lut) {
 }
 
 // ------------------------------------------------------------------------------------------------
+// The large-member decoder (k_big): ONE member per warp, decoded by lane 0 with direct-indexed tables.
+// A lane of k_lane decodes its member at a fixed pace (about 200 ns per byte of input + output at full
+// occupancy), so a member far larger than the rest of its batch would hold the batch up.  Such members
+// get a warp of their own and 3 KB of lookup tables beside the canonical ones: 9 index bits for the
+// literal/length code, 8 for the distance code, one 32-bit entry = code length | extra-bit count << 4 |
+// kind << 9 | literal or base << 16.  Codes longer than the index and everything that ends a run of
+// plain symbols (end of block, invalid code, distance too far, capacity, the last bytes of the input) are
+// left to the same checked path as in k_lane, so results are identical by construction.
+// ------------------------------------------------------------------------------------------------
+constexpr int BIG_LBITS = 9, BIG_DBITS = 8;
+constexpr int BIG_LUT_BYTES = ((1 << BIG_LBITS) + (1 << BIG_DBITS)) * 4;
+constexpr uint32_t BK_LIT = 0, BK_BASE = 1, BK_EOB = 2, BK_INVALID = 3;
+
+// entry of the literal/length code at the head of h32 (nb = 1..15 in bits 0-3)
+ZSB_DEV uint32_t big_ll_entry(const uint8_t *T, const uint32_t *lut, uint32_t d64, uint32_t h32) {
+    uint32_t nb;
+    const uint32_t e = lookup_litlen(T, h32, nb);
+    const uint32_t kind = e & 0x30u, v = e >> 6;
+    if (kind == K_LIT) return nb | (BK_LIT << 9) | (v << 16);
+    if (kind == K_SPECIAL) return nb | ((v == 0 ? BK_EOB : BK_INVALID) << 9);
+    const uint32_t lw = lut[LUT_LEN + d64 * 32 + v];
+    return nb | ((lw >> 16) << 4) | (BK_BASE << 9) | (lw << 16);
+}
+ZSB_DEV uint32_t big_dd_entry(const uint8_t *T, const uint32_t *lut, uint32_t d64, uint32_t h32) {
+    uint32_t nb;
+    const uint32_t sym = lookup_dist(T, h32, nb);
+    if (sym >= 32) return nb | (BK_INVALID << 9);
+    const uint32_t dw = lut[LUT_DIST + d64 * 32 + sym];
+    if (dw >> 31) return nb | (BK_INVALID << 9);
+    return nb | (((dw >> 16) & 15u) << 4) | (BK_BASE << 9) | (dw << 16);
+}
+// the direct tables of the member whose canonical tables are at T, by the whole warp; codes longer than
+// the index leave 0 (the loop then asks big_*_entry)
+template <int W>
+ZSB_DEV void big_build(uint32_t *LL, const uint8_t *T, const uint32_t *lut, uint32_t d64, int lane) {
+    uint32_t *DD = LL + (1 << BIG_LBITS);
+    for (uint32_t i = lane; i < (1u << BIG_LBITS); i += W) {
+        const uint32_t e = big_ll_entry(T, lut, d64, i);
+        LL[i] = (e & 15u) <= (uint32_t)BIG_LBITS ? e : 0u;
+    }
+    for (uint32_t i = lane; i < (1u << BIG_DBITS); i += W) {
+        const uint32_t e = big_dd_entry(T, lut, d64, i);
+        DD[i] = (e & 15u) <= (uint32_t)BIG_DBITS ? e : 0u;
+    }
+    Wp<W>::sync();
+}
+
+// plain literals and whole matches until something else comes up; leaves the bit input at the start of the
+// first code it did not take
+ZSB_DEV void big_run(Lane &L, const uint8_t *T, const uint32_t *lut, const uint32_t *LL) {
+    Dec &d = L.d;
+    BitIn &b = d.b;
+    const uint32_t *DD = LL + (1 << BIG_LBITS);
+    if (b.next + 16 > b.len) return;
+    uint32_t pre = __ldg((const uint32_t *)(b.p + b.next));                 // the next input word, requested one refill ahead
+    for (;;) {
+        if (b.next + 16 > b.len) break;
+        if (b.nbits < 32) {
+            b.hold |= (uint64_t)pre << b.nbits;
+            b.nbits += 32;
+            b.next += 4;
+            pre = __ldg((const uint32_t *)(b.p + b.next));
+        }
+        uint32_t e = LL[(uint32_t)b.hold & ((1u << BIG_LBITS) - 1u)];
+        if (!(e & 15u)) e = big_ll_entry(T, lut, d.d64, (uint32_t)b.hold);
+        const uint32_t nb = e & 15u, kind = (e >> 9) & 3u;
+        if (kind == BK_LIT) {
+            if (d.pos >= d.cap) break;
+            b.hold >>= nb;
+            b.nbits -= nb;
+            push_literal(L, e >> 16);
+            continue;
+        }
+        if (kind != BK_BASE) break;                      // end of block / invalid code: the checked path's
+        const uint64_t h0 = b.hold;                      // a match is taken whole or not at all
+        const uint32_t n0 = b.nbits, x0 = b.next;
+        const uint32_t xb = (e >> 4) & 31u;
+        const uint32_t mlen = (e >> 16) + ((uint32_t)(b.hold >> nb) & ((1u << xb) - 1u));
+        b.hold >>= nb + xb;
+        b.nbits -= nb + xb;
+        if (b.nbits < 32) {
+            b.hold |= (uint64_t)pre << b.nbits;
+            b.nbits += 32;
+            b.next += 4;
+            pre = __ldg((const uint32_t *)(b.p + b.next));
+        }
+        uint32_t f = DD[(uint32_t)b.hold & ((1u << BIG_DBITS) - 1u)];
+        if (!(f & 15u)) f = big_dd_entry(T, lut, d.d64, (uint32_t)b.hold);
+        const uint32_t nb2 = f & 15u, xb2 = (f >> 4) & 31u;
+        const uint32_t dist = (f >> 16) + ((uint32_t)(b.hold >> nb2) & ((1u << xb2) - 1u));
+        if (((f >> 9) & 3u) != BK_BASE || dist > d.pos + L.hist || d.pos >= d.cap || mlen > d.cap - d.pos) {
+            b.hold = h0;
+            b.nbits = n0;
+            b.next = x0;
+            break;
+        }
+        b.hold >>= nb2 + xb2;
+        b.nbits -= nb2 + xb2;
+        push_match(L, mlen, dist);
+    }
+}
+
+// ------------------------------------------------------------------------------------------------
 // Dynamic block header, per lane (reference src/inflate.c:905-1004): the counts, the code-length
 // code and the code lengths of both codes, left as bytes at T[H_LENS..].  The two decoding tables
 // are built afterwards by the whole warp (build_tables).  Returns EV_NONE, EV_ERR or EV_STARVE.
@@ -782,8 +885,11 @@ ZSB_DEV int lane_block(Lane &L, uint8_t *T, const uint32_t *lut, const Batch &B)
     }
 }
 
-template <int W>
-__device__ __forceinline__ void warp_lanes(const Batch &B, uint8_t *slots, uint8_t *scr, uint32_t *rings, const uint32_t *lut, int lane) {
+// BIG: one member per warp (lane 0 decodes with the direct tables at `big_lut`, big_run); the other lanes
+// only help to build tables.
+template <int W, bool BIG = false>
+__device__ __forceinline__ void warp_lanes(const Batch &B, uint8_t *slots, uint8_t *scr, uint32_t *rings, const uint32_t *lut, int lane,
+                                           uint32_t *big_lut = nullptr) {
     Lane L;
     L.ring = rings + lane * (RING_STRIDE == 1 ? RING_WORDS : 1);
     L.d.pos = 0; L.d.cap = 0; L.d.b.p = nullptr; L.d.b.len = 0; L.d.b.next = 0; L.d.b.nbits = 0; L.d.b.hold = 0;
@@ -795,7 +901,7 @@ __device__ __forceinline__ void warp_lanes(const Batch &B, uint8_t *slots, uint8
     L.ring_sa = 0;
 #endif
     uint8_t *T = slots + (size_t)lane * SLOT;
-    int st = LS_FETCH;
+    int st = (BIG && lane != 0) ? LS_IDLE : LS_FETCH;
     const unsigned lt = (1u << lane) - 1u;
 
     for (;;) {
@@ -831,6 +937,7 @@ __device__ __forceinline__ void warp_lanes(const Batch &B, uint8_t *slots, uint8
                 } else {
                     msg = build_tables<W>(Ts, scr, (info >> 2) & 1023u, info >> 12, (info >> 1) & 1u, lane);
                 }
+                if (BIG && !msg) big_build<W>(big_lut, Ts, lut, (info >> 1) & 1u, lane);
                 if (lane == src) {
                     if (msg) {
                         L.d.msg = msg;
@@ -838,7 +945,7 @@ __device__ __forceinline__ void warp_lanes(const Batch &B, uint8_t *slots, uint8
                         st = LS_FETCH;
                     } else {
                         st = LS_SYM;
-                        prime(L);
+                        if (!BIG) prime(L);
                     }
                 }
             }
@@ -868,16 +975,24 @@ __device__ __forceinline__ void warp_lanes(const Batch &B, uint8_t *slots, uint8
             Wp<W>::sync();
         }
         if (!Wp<W>::any(st == LS_SYM)) break;
-        // ---------------- the lock-step symbol loop ----------------
+        if constexpr (BIG) {         // lane 0 alone: plain symbols through the direct tables, the rest in the service section
+            if (st == LS_SYM) {
+                big_run(L, T, lut, big_lut);
+                st = LS_TAIL;
+            }
+            Wp<W>::sync();
+        } else {
+            // ---------------- the lock-step symbol loop ----------------
 #pragma unroll 1
-        for (;;) {               // two codes per vote: a lane that has to leave waits one step at most
-            if (st == LS_SYM) {
-                if (L.d.b.next + 8 > L.d.b.len || !fast_step(L, T, lut)) st = LS_TAIL;
+            for (;;) {           // two codes per vote: a lane that has to leave waits one step at most
+                if (st == LS_SYM) {
+                    if (L.d.b.next + 8 > L.d.b.len || !fast_step(L, T, lut)) st = LS_TAIL;
+                }
+                if (st == LS_SYM) {
+                    if (L.d.b.next + 8 > L.d.b.len || !fast_step(L, T, lut)) st = LS_TAIL;
+                }
+                if (Wp<W>::any(st != LS_SYM && st != LS_IDLE)) break;
             }
-            if (st == LS_SYM) {
-                if (L.d.b.next + 8 > L.d.b.len || !fast_step(L, T, lut)) st = LS_TAIL;
-            }
-            if (Wp<W>::any(st != LS_SYM && st != LS_IDLE)) break;
         }
     }
 }
