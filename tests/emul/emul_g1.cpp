@@ -93,7 +93,8 @@ extern "C" int emul_decode_lane(const uint8_t *in, size_t in_len, uint8_t *out, 
     if (g_big) {                                     // k_big's decoder: lane 0 with the direct tables
         alignas(16) static uint32_t big_lut[lane::BIG_LUT_BYTES / 4];
         memset(big_lut, 0xA5, sizeof big_lut);
-        lane::warp_lanes<1, true>(B, T, scr, ring, lut, 0, big_lut);
+        alignas(16) static lane::seq_t big_q[lane::BIG_QCAP];
+        lane::warp_lanes<1, true>(B, T, scr, ring, lut, 0, big_lut, big_q);
     } else {
         lane::warp_lanes<1>(B, T, scr, ring, lut, 0);
     }

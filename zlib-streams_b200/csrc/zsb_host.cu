@@ -240,18 +240,13 @@ static uint64_t lane_plan(const zsb_member *hm, const uint32_t *horder, size_t n
 // small part's start after the big part's big_seqs sequences) and slices.  Returns the sequences needed.
 static uint64_t plan_parts(const zsb_member *hm, const uint32_t *order, size_t n, size_t nbig, uint64_t arena_seqs,
                            uint64_t *off, std::vector<size_t> &cuts_big, std::vector<size_t> &cuts, uint64_t &big_seqs) {
-    // each part may use the arena in proportion to what it could need
-    double need_big = 0, need_all = 0;
-    for (size_t s = 0; s < n; s++) {
-        const double b = (double)seq_bound(hm[order ? order[s] : s]);
-        need_all += b;
-        if (s < nbig) need_big += b;
-    }
-    uint64_t arena_big = arena_seqs;
-    if (nbig && nbig < n && need_all > (double)arena_seqs)
-        arena_big = (uint64_t)std::max(1.0, (double)arena_seqs * need_big / need_all);
-    big_seqs = nbig ? lane_plan(hm, order, nbig, arena_big, off, cuts_big) : 0;
-    const uint64_t left = arena_seqs > big_seqs ? arena_seqs - big_seqs : 1;
+    // the large members' part needs no arena (k_big keeps its sequences in shared memory): one slice
+    big_seqs = 0;
+    cuts_big.clear();
+    cuts_big.push_back(0);
+    cuts_big.push_back(nbig);
+    for (size_t s = 0; s < nbig; s++) off[s] = 0;
+    const uint64_t left = arena_seqs;
     const uint64_t most = n > nbig ? lane_plan(hm, order ? order + nbig : nullptr, n - nbig, left, off + nbig, cuts) : 0;
     for (size_t s = nbig; s < n; s++) off[s] += big_seqs;
     return big_seqs + most;
@@ -338,13 +333,10 @@ static int launch_lane(zsb_ctx *ctx, zsb_dev &dv, const zsb_member *dm, zsb_resu
             k_big<<<grid, (unsigned)(warps * 32), LUT_BYTES + warps * BIG_PER_WARP, st>>>(B);
             ctx->launches++;
             CK(ctx, cudaGetLastError());
-            if (pb) CK(ctx, cudaEventRecord(pb[1], st));
-            const size_t wpc0 = LZ_THREADS / 32;
-            grid = (unsigned)std::max<size_t>(1, std::min((cnt + wpc0 - 1) / wpc0, (size_t)dv.sm_count * dv.lz_occ));
-            k_lz<<<grid, LZ_THREADS, 0, st>>>(B, counters + 2);
-            ctx->launches++;
-            CK(ctx, cudaGetLastError());
-            if (pb) CK(ctx, cudaEventRecord(pb[2], st));
+            if (pb) {                                  // (k_big resolves its own sequences: no k_lz for this part)
+                CK(ctx, cudaEventRecord(pb[1], st));
+                CK(ctx, cudaEventRecord(pb[2], st));
+            }
             continue;
         }
         if (P.small_ctas || ctx->force_small_ctas) {

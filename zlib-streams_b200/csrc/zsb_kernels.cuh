@@ -288,12 +288,13 @@ __global__ void __launch_bounds__(lane::WARPS * 32, 1) k_lane(lane::Batch B) {
     lane::warp_lanes<32>(B, slots, scr, rings, lut, ln);
 }
 
-// Large members: one member per WARP, lane 0 decodes with direct-indexed tables (lane::big_run); same
-// sequences, same results, consumed by the same k_lz.  Per warp: build scratch, one table slot, 3 KB of
-// direct tables.
+// Large members: one member per WARP; lane 0 decodes with direct-indexed tables (lane::big_run) into a
+// sequence queue in shared memory, the whole warp resolves the queue (lz::resolve_range): same sequences and
+// results as k_lane + k_lz, without the sequence arena.  Per warp: build scratch, one table slot, 3 KB of
+// direct tables, a 4 KB queue.
 constexpr int BIG_WARPS = 16;
 constexpr int BIG_SLOT = 480;                                  // lane::SLOT rounded up to 16
-constexpr size_t BIG_PER_WARP = lane::WSCR + BIG_SLOT + lane::BIG_LUT_BYTES;
+constexpr size_t BIG_PER_WARP = lane::WSCR + BIG_SLOT + lane::BIG_LUT_BYTES + lane::BIG_QCAP * sizeof(lane::seq_t);
 constexpr size_t BIG_SMEM = LUT_BYTES + (size_t)BIG_WARPS * BIG_PER_WARP;
 __global__ void __launch_bounds__(BIG_WARPS * 32, 1) k_big(lane::Batch B) {
     extern __shared__ __align__(16) uint8_t smem[];
@@ -305,7 +306,8 @@ __global__ void __launch_bounds__(BIG_WARPS * 32, 1) k_big(lane::Batch B) {
     uint8_t *scr = base, *slot = base + lane::WSCR;
     uint32_t *big_lut = (uint32_t *)(base + lane::WSCR + BIG_SLOT);
     // (the input ring of k_lane is not used here; lane 0's ring pointer only has to be a shared address)
-    lane::warp_lanes<32, true>(B, slot, scr, (uint32_t *)scr, lut, ln, big_lut);
+    lane::seq_t *big_q = (lane::seq_t *)(base + lane::WSCR + BIG_SLOT + lane::BIG_LUT_BYTES);
+    lane::warp_lanes<32, true>(B, slot, scr, (uint32_t *)scr, lut, ln, big_lut, big_q);
 }
 
 constexpr int LZ_THREADS = 256;

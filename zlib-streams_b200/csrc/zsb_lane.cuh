@@ -71,6 +71,13 @@ struct seq_t {
     uint32_t lo, hi;
 };
 
+}  // namespace lane
+namespace lz {           // zsb_lz.cuh; k_big resolves its queue with it
+template <int W>
+ZSB_DEV uint32_t resolve_range(uint8_t *out, const uint8_t *in, const lane::seq_t *seq, uint32_t nseq, int lane, uint32_t base);
+}
+namespace lane {
+
 // ---- warp primitives, W = 32 on the device, 1 in the host emulation of the test tier ----
 template <int W> struct Wp {
     static ZSB_DEV unsigned ballot(bool p) { return __ballot_sync(0xffffffffu, p); }
@@ -103,6 +110,8 @@ struct Lane {
     uint32_t mode;       // fast_step: 0 = the next code is a literal/length code, 1 = a distance code
     uint32_t pl;         // fast_step: length of the match whose distance code comes next (mode 1)
     uint32_t ring_sa;    // shared-window address of `ring` (device only)
+    seq_t *q0, *qend;    // k_big: the warp's sequence queue in shared memory (NULL in k_lane); L.seq runs inside it
+    uint32_t qbase;      // k_big: output position of the queue's first sequence
 };
 
 ZSB_DEV void emit(Lane &L, uint32_t lo, uint32_t hi) {
@@ -396,6 +405,9 @@ ZSB_DEV bool fast_step(Lane &L, const uint8_t *T, const uint32_t *lut) {
 // ------------------------------------------------------------------------------------------------
 constexpr int BIG_LBITS = 9, BIG_DBITS = 8;
 constexpr int BIG_LUT_BYTES = ((1 << BIG_LBITS) + (1 << BIG_DBITS)) * 4;
+// The warp's sequence queue: lane 0 decodes into it, the whole warp resolves it (lz::resolve_range) whenever
+// it is nearly full or a block / the member ends: no sequence arena and no k_lz pass for these members.
+constexpr int BIG_QCAP = 512, BIG_QMARGIN = 128;    // margin: what the checked path may emit before the next flush
 constexpr uint32_t BK_LIT = 0, BK_BASE = 1, BK_EOB = 2, BK_INVALID = 3;
 
 // entry of the literal/length code at the head of h32 (nb = 1..15 in bits 0-3)
@@ -434,14 +446,16 @@ ZSB_DEV void big_build(uint32_t *LL, const uint8_t *T, const uint32_t *lut, uint
 
 // plain literals and whole matches until something else comes up; leaves the bit input at the start of the
 // first code it did not take
-ZSB_DEV void big_run(Lane &L, const uint8_t *T, const uint32_t *lut, const uint32_t *LL) {
+// Returns true when it stopped only because the queue has to be flushed (the lane stays in the loop).
+ZSB_DEV bool big_run(Lane &L, const uint8_t *T, const uint32_t *lut, const uint32_t *LL) {
     Dec &d = L.d;
     BitIn &b = d.b;
     const uint32_t *DD = LL + (1 << BIG_LBITS);
-    if (b.next + 16 > b.len) return;
+    if (b.next + 16 > b.len) return false;
     uint32_t pre = __ldg((const uint32_t *)(b.p + b.next));                 // the next input word, requested one refill ahead
     for (;;) {
         if (b.next + 16 > b.len) break;
+        if (L.seq + BIG_QMARGIN > L.qend) return true;
         if (b.nbits < 32) {
             b.hold |= (uint64_t)pre << b.nbits;
             b.nbits += 32;
@@ -484,6 +498,25 @@ ZSB_DEV void big_run(Lane &L, const uint8_t *T, const uint32_t *lut, const uint3
         b.hold >>= nb2 + xb2;
         b.nbits -= nb2 + xb2;
         push_match(L, mlen, dist);
+    }
+    return false;
+}
+
+// the warp executes what lane 0 has queued (all lanes call)
+template <int W>
+ZSB_DEV void big_flush(Lane &L, const seq_t *q, int lane) {
+    const uint32_t nq = Wp<W>::shfl(lane == 0 ? (uint32_t)(L.seq - L.q0) : 0u, 0);
+    if (!nq) return;
+    const uint64_t o = (uint64_t)(uintptr_t)L.d.out, i = (uint64_t)(uintptr_t)L.d.b.p;
+    const uint64_t ob = (uint64_t)Wp<W>::shfl((uint32_t)o, 0) | ((uint64_t)Wp<W>::shfl((uint32_t)(o >> 32), 0) << 32);
+    const uint64_t ib = (uint64_t)Wp<W>::shfl((uint32_t)i, 0) | ((uint64_t)Wp<W>::shfl((uint32_t)(i >> 32), 0) << 32);
+    uint32_t base = Wp<W>::shfl(L.qbase, 0);
+    Wp<W>::sync();                                   // lane 0's queue stores are visible to the warp
+    base = lz::resolve_range<W>((uint8_t *)(uintptr_t)ob, (const uint8_t *)(uintptr_t)ib, q, nq, lane, base);
+    Wp<W>::sync();
+    if (lane == 0) {
+        L.qbase = base;
+        L.seq = L.q0;
     }
 }
 
@@ -762,7 +795,7 @@ struct Batch {
 ZSB_DEV void finish(Lane &L, int ev, const Batch &B) {
     flush_literals(L);
     write_result(L.d, L.mm, ev, B.results + L.mm.idx, B.aux + L.mm.idx);
-    B.aux[L.mm.idx].nseq = (uint32_t)(L.seq - L.seq0);
+    B.aux[L.mm.idx].nseq = L.q0 ? 0u : (uint32_t)(L.seq - L.seq0);      // k_big resolves its own sequences
 }
 
 // descriptor + wrapper header of a new member; returns the lane's next state
@@ -874,6 +907,7 @@ ZSB_DEV int lane_block(Lane &L, uint8_t *T, const uint32_t *lut, const Batch &B)
         push_raw(L, spos, slen);
         bi_seek(b, spos + slen);
         d.at_type = 1;
+        if (!cut && L.q0 && L.seq + BIG_QMARGIN > L.qend) return LS_BLOCK;   // k_big: let the warp empty the queue
         if (cut) {                             // input or output ran out inside the block
             b.next = spos + slen;
             b.nbits = 0;
@@ -889,8 +923,11 @@ ZSB_DEV int lane_block(Lane &L, uint8_t *T, const uint32_t *lut, const Batch &B)
 // only help to build tables.
 template <int W, bool BIG = false>
 __device__ __forceinline__ void warp_lanes(const Batch &B, uint8_t *slots, uint8_t *scr, uint32_t *rings, const uint32_t *lut, int lane,
-                                           uint32_t *big_lut = nullptr) {
+                                           uint32_t *big_lut = nullptr, seq_t *big_q = nullptr) {
     Lane L;
+    L.q0 = BIG ? big_q : nullptr;
+    L.qend = BIG ? big_q + BIG_QCAP : nullptr;
+    L.qbase = 0;
     L.ring = rings + lane * (RING_STRIDE == 1 ? RING_WORDS : 1);
     L.d.pos = 0; L.d.cap = 0; L.d.b.p = nullptr; L.d.b.len = 0; L.d.b.next = 0; L.d.b.nbits = 0; L.d.b.hold = 0;
     L.d.d64 = 0; L.d.msg = 0; L.nl = 0; L.lw = 0; L.seq = L.seq0 = nullptr; L.nlen = 0; L.ndist = 0;
@@ -901,12 +938,14 @@ __device__ __forceinline__ void warp_lanes(const Batch &B, uint8_t *slots, uint8
     L.ring_sa = 0;
 #endif
     uint8_t *T = slots + (size_t)lane * SLOT;
+    if (BIG) L.seq = L.seq0 = L.q0;           // an empty queue
     int st = (BIG && lane != 0) ? LS_IDLE : LS_FETCH;
     const unsigned lt = (1u << lane) - 1u;
 
     for (;;) {
         // ---------------- service: until every lane is decoding symbols or out of work ----------------
         for (;;) {
+            if (BIG) big_flush<W>(L, big_q, lane);       // before a new member is fetched, a block is read, the tail goes on
             if (!Wp<W>::any(st != LS_SYM && st != LS_IDLE)) break;
             const unsigned fm = Wp<W>::ballot(st == LS_FETCH);
             if (fm) {
@@ -917,7 +956,13 @@ __device__ __forceinline__ void warp_lanes(const Batch &B, uint8_t *slots, uint8
                 if (st == LS_FETCH) {
                     const uint32_t slot = base + __popc(fm & lt);
                     if (slot >= B.n) st = LS_IDLE;
-                    else st = start_member(L, slot, B);
+                    else {
+                        st = start_member(L, slot, B);
+                        if (BIG) {                       // sequences go to the warp's queue, from output position 0
+                            L.seq = L.seq0 = L.q0;
+                            L.qbase = 0;
+                        }
+                    }
                 }
             }
             if (st == LS_BLOCK) st = lane_block(L, T, lut, B);
@@ -951,6 +996,7 @@ __device__ __forceinline__ void warp_lanes(const Batch &B, uint8_t *slots, uint8
             }
             if (st == LS_SYM && L.d.b.next + 8 > L.d.b.len) st = LS_TAIL;
             while (st == LS_TAIL) {             // the last bytes of a member: every step checked
+                if (BIG && L.seq + 8 > L.qend) break;  // k_big: the queue is emptied at the top of the service loop
                 if (L.mode) L.d.mlen = L.pl;          // the loop stopped between a length and its distance
                 int e2 = careful_symbol(L.d, T, lut, L.mode != 0);
                 L.mode = 0;
@@ -976,11 +1022,9 @@ __device__ __forceinline__ void warp_lanes(const Batch &B, uint8_t *slots, uint8
         }
         if (!Wp<W>::any(st == LS_SYM)) break;
         if constexpr (BIG) {         // lane 0 alone: plain symbols through the direct tables, the rest in the service section
-            if (st == LS_SYM) {
-                big_run(L, T, lut, big_lut);
-                st = LS_TAIL;
-            }
+            if (st == LS_SYM && !big_run(L, T, lut, big_lut)) st = LS_TAIL;
             Wp<W>::sync();
+            big_flush<W>(L, big_q, lane);
         } else {
             // ---------------- the lock-step symbol loop ----------------
 #pragma unroll 1

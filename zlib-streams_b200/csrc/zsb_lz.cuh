@@ -98,10 +98,10 @@ ZSB_DEV void lane_copy16(uint8_t *dst, const uint8_t *src, uint32_t n) {
     }
 }
 
-// all sequences of one member
+// nseq sequences of one member whose first byte goes to out[base]; returns the position after the last.
+// (k_lz runs a member's whole array from 0; k_big runs its shared-memory queue chunk by chunk.)
 template <int W>
-ZSB_DEV void resolve_member(uint8_t *out, const uint8_t *in, const seq_t *seq, uint32_t nseq, int lane) {
-    uint32_t base = 0;
+ZSB_DEV uint32_t resolve_range(uint8_t *out, const uint8_t *in, const seq_t *seq, uint32_t nseq, int lane, uint32_t base) {
     seq_t qn;                                 // the next trip's sequence is requested one trip ahead
     qn.lo = 0;
     qn.hi = 0;
@@ -156,6 +156,13 @@ ZSB_DEV void resolve_member(uint8_t *out, const uint8_t *in, const seq_t *seq, u
             Wp<W>::sync();
         }
     }
+    return base;
+}
+
+// all sequences of one member
+template <int W>
+ZSB_DEV void resolve_member(uint8_t *out, const uint8_t *in, const seq_t *seq, uint32_t nseq, int lane) {
+    resolve_range<W>(out, in, seq, nseq, lane, 0u);
 }
 
 }  // namespace lz

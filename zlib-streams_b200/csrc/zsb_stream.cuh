@@ -248,6 +248,7 @@ ZSB_DEV void stream_decode(State &S, const uint8_t *in, uint32_t in_len, uint32_
     d.out = nullptr; d.pos = 0; d.cap = out_cap; d.d64 = S.d64; d.last = S.last; d.at_type = 0; d.msg = 0;
     d.extent = 0; d.mlen = 0; d.mdist = 0; d.mtrunc = 0;
     L.mm.idx = 0; L.mm.kind = S.kind; L.mm.adler0 = S.check; L.mm.hdr_stop = false; L.mm.hdr_tin = 0; L.mm.hdr_bits = 0;
+    L.q0 = L.qend = nullptr; L.qbase = 0;
     L.seq = L.seq0 = seq; L.lw = 0; L.nl = 0; L.ring = ring; L.hist = S.whave; L.nlen = 0; L.ndist = 0;
     R.phase = S.phase; R.unit = 0; R.stop = EV_NONE; R.last0 = S.last; R.hdr_stop = false; R.hdr_tin = 0; R.hdr_bits = 0;
     if (active && R.phase != PH_HEAD) seek_bit(d.b, S.bit0);
