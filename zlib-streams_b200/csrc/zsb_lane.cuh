@@ -452,54 +452,65 @@ ZSB_DEV bool big_run(Lane &L, const uint8_t *T, const uint32_t *lut, const uint3
     BitIn &b = d.b;
     const uint32_t *DD = LL + (1 << BIG_LBITS);
     if (b.next + 16 > b.len) return false;
-    uint32_t pre = __ldg((const uint32_t *)(b.p + b.next));                 // the next input word, requested one refill ahead
+    // (b.next is word aligned while whole words are left: the invariant bi_loadword relies on)
+    uint32_t pre = __ldg((const uint32_t *)(b.p + b.next));     // the next input word, requested one refill ahead
     for (;;) {
-        if (b.next + 16 > b.len) break;
-        if (L.seq + BIG_QMARGIN > L.qend) return true;
-        if (b.nbits < 32) {
-            b.hold |= (uint64_t)pre << b.nbits;
-            b.nbits += 32;
-            b.next += 4;
-            pre = __ldg((const uint32_t *)(b.p + b.next));
+        // Codes that can be taken without looking at the queue, the end of the input or (for literals) the
+        // capacity again: a code queues at most one sequence, reads at most 8 input bytes and yields at least
+        // one output byte.
+        if (b.next + 16 > b.len) return false;
+        const long qfree = (long)(L.qend - L.seq) - BIG_QMARGIN;
+        if (qfree <= 0) return true;
+        uint32_t budget = (b.len - 16 - b.next) / 8 + 1;
+        if ((long)budget > qfree) budget = (uint32_t)qfree;
+        if (budget > d.cap - d.pos) budget = d.cap - d.pos;
+        if (budget == 0) return false;                   // no room for a literal: the checked path decides
+        while (budget) {
+            budget--;
+            if (b.nbits < 32) {
+                b.hold |= (uint64_t)pre << b.nbits;
+                b.nbits += 32;
+                b.next += 4;
+                pre = __ldg((const uint32_t *)(b.p + b.next));
+            }
+            uint32_t e = LL[(uint32_t)b.hold & ((1u << BIG_LBITS) - 1u)];
+            if (!(e & 15u)) e = big_ll_entry(T, lut, d.d64, (uint32_t)b.hold);
+            const uint32_t nb = e & 15u, kind = (e >> 9) & 3u;
+            if (kind == BK_LIT) {
+                b.hold >>= nb;
+                b.nbits -= nb;
+                push_literal(L, e >> 16);
+                continue;
+            }
+            if (kind != BK_BASE) return false;           // end of block / invalid code: the checked path's
+            const uint64_t h0 = b.hold;                  // a match is taken whole or not at all
+            const uint32_t n0 = b.nbits, x0 = b.next;
+            const uint32_t xb = (e >> 4) & 31u;
+            const uint32_t mlen = (e >> 16) + ((uint32_t)(b.hold >> nb) & ((1u << xb) - 1u));
+            b.hold >>= nb + xb;
+            b.nbits -= nb + xb;
+            if (b.nbits < 32) {
+                b.hold |= (uint64_t)pre << b.nbits;
+                b.nbits += 32;
+                b.next += 4;
+                pre = __ldg((const uint32_t *)(b.p + b.next));
+            }
+            uint32_t f = DD[(uint32_t)b.hold & ((1u << BIG_DBITS) - 1u)];
+            if (!(f & 15u)) f = big_dd_entry(T, lut, d.d64, (uint32_t)b.hold);
+            const uint32_t nb2 = f & 15u, xb2 = (f >> 4) & 31u;
+            const uint32_t dist = (f >> 16) + ((uint32_t)(b.hold >> nb2) & ((1u << xb2) - 1u));
+            if (((f >> 9) & 3u) != BK_BASE || dist > d.pos + L.hist || mlen > d.cap - d.pos) {
+                b.hold = h0;
+                b.nbits = n0;
+                b.next = x0;
+                return false;
+            }
+            b.hold >>= nb2 + xb2;
+            b.nbits -= nb2 + xb2;
+            push_match(L, mlen, dist);
+            if (budget > d.cap - d.pos) budget = d.cap - d.pos;
         }
-        uint32_t e = LL[(uint32_t)b.hold & ((1u << BIG_LBITS) - 1u)];
-        if (!(e & 15u)) e = big_ll_entry(T, lut, d.d64, (uint32_t)b.hold);
-        const uint32_t nb = e & 15u, kind = (e >> 9) & 3u;
-        if (kind == BK_LIT) {
-            if (d.pos >= d.cap) break;
-            b.hold >>= nb;
-            b.nbits -= nb;
-            push_literal(L, e >> 16);
-            continue;
-        }
-        if (kind != BK_BASE) break;                      // end of block / invalid code: the checked path's
-        const uint64_t h0 = b.hold;                      // a match is taken whole or not at all
-        const uint32_t n0 = b.nbits, x0 = b.next;
-        const uint32_t xb = (e >> 4) & 31u;
-        const uint32_t mlen = (e >> 16) + ((uint32_t)(b.hold >> nb) & ((1u << xb) - 1u));
-        b.hold >>= nb + xb;
-        b.nbits -= nb + xb;
-        if (b.nbits < 32) {
-            b.hold |= (uint64_t)pre << b.nbits;
-            b.nbits += 32;
-            b.next += 4;
-            pre = __ldg((const uint32_t *)(b.p + b.next));
-        }
-        uint32_t f = DD[(uint32_t)b.hold & ((1u << BIG_DBITS) - 1u)];
-        if (!(f & 15u)) f = big_dd_entry(T, lut, d.d64, (uint32_t)b.hold);
-        const uint32_t nb2 = f & 15u, xb2 = (f >> 4) & 31u;
-        const uint32_t dist = (f >> 16) + ((uint32_t)(b.hold >> nb2) & ((1u << xb2) - 1u));
-        if (((f >> 9) & 3u) != BK_BASE || dist > d.pos + L.hist || d.pos >= d.cap || mlen > d.cap - d.pos) {
-            b.hold = h0;
-            b.nbits = n0;
-            b.next = x0;
-            break;
-        }
-        b.hold >>= nb2 + xb2;
-        b.nbits -= nb2 + xb2;
-        push_match(L, mlen, dist);
     }
-    return false;
 }
 
 // the warp executes what lane 0 has queued (all lanes call)
