@@ -115,6 +115,11 @@ ZSB_API long zsb_last_launches(const zsb_ctx *ctx);
  * shard index; load[s] (optional) the summed cost per shard.  Deterministic. */
 ZSB_API int zsb_plan_shards(size_t n, const uint64_t *cost, int nshards, int32_t *shard_of, uint64_t *load);
 
+/* Length-aware split inside one GPU (pure host code): of n members given LARGEST FIRST, how many are so much
+ * larger than the rest that they are decoded a warp each (k_big) beside the others (one lane each, k_lane).
+ * 0 for a uniform batch.  The cost model is measured on B200; sm_count = SMs of the device. */
+ZSB_API size_t zsb_plan_big(size_t n, const uint64_t *in_len, const uint64_t *out_cap, int sm_count);
+
 /* Pinned host memory for fast host<->device staging. */
 ZSB_API void *zsb_host_alloc(size_t bytes);
 ZSB_API void zsb_host_free(void *p);

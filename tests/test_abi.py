@@ -48,3 +48,28 @@ def test_no_cpu_fallback_without_device():
         pytest.skip("a device is present")
     with pytest.raises(RuntimeError, match="no CUDA device|zsb_create failed"):
         zsblib.Zsb()
+
+
+def test_plan_big_picks_only_outliers():
+    """The length-aware split inside a GPU (zsb_plan_big): uniform batches keep every member on the lane path,
+    outliers get a warp each, and never more members than two rounds of warps."""
+    import random
+    lib = zsblib.load_product()
+
+    def plan(sizes):
+        sizes = sorted(sizes, reverse=True)
+        n = len(sizes)
+        a = (ctypes.c_uint64 * n)(*[s // 2 for s in sizes])
+        b = (ctypes.c_uint64 * n)(*sizes)
+        return lib.zsb_plan_big(n, a, b, 148)
+    assert plan([65536] * 65536) == 0                          # C2
+    assert plan([65536] * 4096) == 0
+    assert plan([16 << 20] + [65536] * 65535) == 1             # one outlier
+    assert plan([16 << 20] * 5 + [65536] * 20000) == 5
+    rnd = random.Random(4)
+    c4 = [int(1024 * (16384 ** rnd.random())) for _ in range(16384)]       # 1 KiB .. 16 MiB log-uniform
+    k = plan(c4)
+    assert 100 < k <= 2 * 16 * 148
+    c5 = [int(1024 * (256 ** rnd.random())) for _ in range(1 << 20)]       # 1 KiB .. 256 KiB
+    assert plan(c5) == 0
+    assert plan([]) == 0

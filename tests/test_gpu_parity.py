@@ -201,6 +201,9 @@ def test_host_batch_pipelined(eng):
         for k in (3, 8, 40):
             eng.set_option("chunks", k)
             run_cases(eng, 0, items)
+        eng.set_option("chunks", 5)              # the chunks' members through k_big
+        run_cases(eng, "big", items)
+        eng.set_option("split_big", 1)
         # a small sequence arena: the chunks share fewer regions / streams and decode in slices
         arena = eng.get_option("seq_arena_bytes")
         eng.set_option("seq_arena_bytes", 1 << 20)

@@ -214,6 +214,17 @@ static size_t split_big(const zsb_member *hm, const uint32_t *order, size_t n, i
     return best_n;
 }
 
+// the split as a pure host function (include/zsb.h): members given largest first
+extern "C" size_t zsb_plan_big(size_t n, const uint64_t *in_len, const uint64_t *out_cap, int sm_count) {
+    if (!n || !in_len || !out_cap || sm_count < 1) return 0;
+    std::vector<zsb_member> hm(n);
+    for (size_t i = 0; i < n; i++) {
+        hm[i].in_len = (size_t)in_len[i];
+        hm[i].out_cap = (size_t)out_cap[i];
+    }
+    return split_big(hm.data(), nullptr, n, sm_count);
+}
+
 // Per-slot sequence offsets (off[n]) and the slices [cuts[k], cuts[k+1]) of the slot order, cut where the
 // arena of arena_seqs sequences would overflow.  Returns the most sequences a slice needs.
 static uint64_t lane_plan(const zsb_member *hm, const uint32_t *horder, size_t n, uint64_t arena_seqs, uint64_t *off,
