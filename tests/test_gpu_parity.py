@@ -212,3 +212,21 @@ def test_host_batch_pipelined(eng):
         eng.set_option("seq_arena_bytes", arena)
     finally:
         eng.set_option("chunks", 0)
+
+
+def test_pipelined_uniform_batch_stays_on_the_lane_path(eng):
+    """The chunks of a pipelined host batch overlap, so large members are chosen for the batch as a whole: a
+    uniform batch must not send whole chunks to k_big (that serialised the pipeline once: 96 -> 186 ms on C2)."""
+    import gen
+    select(eng, 0)
+    eng.set_option("path", 0)
+    eng.set_option("split_big", 1)
+    data = gen.deflate(gen.word_soup(20000, 5), 6, -15)
+    n, K = 4096, 4
+    try:
+        eng.set_option("chunks", K)
+        got = eng.inflate_batch([data] * n, [-15] * n, [20000] * n)
+        assert all(r.ret == 1 and r.total_out == 20000 for r, _ in got)
+        assert eng.lib.zsb_last_launches(eng.ctx) == 2 * K          # k_lane + k_lz per chunk, no k_big
+    finally:
+        eng.set_option("chunks", 0)

@@ -874,6 +874,27 @@ static int batch_host(zsb_ctx *ctx, size_t n, const zsb_member *m, zsb_result *r
         zsb_result *dr = (zsb_result *)(dm + k);
         // the three stages of every chunk: inputs on copy_stream, decode on the chunk's stream, results and
         // outputs on back_stream
+        // Which members are large is decided for the shard as a whole: the chunks of a pipeline overlap, so what
+        // counts is the batch's time, not a chunk's own (k_big would finish a lone chunk sooner, but the whole
+        // GPU decodes only ~26 bytes/ns that way).  The sort is skipped when the largest member's own lane time
+        // is within the batch's.
+        double big_threshold = 1e300;
+        if (ctx->path == 0 && ctx->split_big == 1 && K > 1) {
+            double total = 0, most = 0;
+            for (uint32_t i : sh.idx) {
+                const double c = (double)m[i].in_len + (double)m[i].out_cap;
+                total += c;
+                most = std::max(most, c);
+            }
+            if (most * 150.0 > total / 190.0) {
+                std::vector<uint32_t> ord(sh.idx);
+                std::stable_sort(ord.begin(), ord.end(), [&](uint32_t a, uint32_t b) {
+                    return m[a].in_len + m[a].out_cap > m[b].in_len + m[b].out_cap;
+                });
+                const size_t nb = split_big(m, ord.data(), ord.size(), dv.sm_count);
+                if (nb) big_threshold = (double)m[ord[nb - 1]].in_len + (double)m[ord[nb - 1]].out_cap;
+            }
+        }
         size_t plan_off = 0;
         std::vector<std::vector<size_t>> cuts_of(K), cuts_big_of(K);
         CK(ctx, cudaMemsetAsync(dv.counters, 0, 8 * (size_t)K * sizeof(uint32_t), dv.copy_stream));
@@ -909,7 +930,11 @@ static int batch_host(zsb_ctx *ctx, size_t n, const zsb_member *m, zsb_result *r
             sc.counters = dv.counters + 8 * c;
             sc.small_ctas = K > 1;
             // the chunk's plan travels with its inputs: slot order, and for the lane path the sequence offsets
-            sc.nbig = (ctx->path == 0 && ctx->split_big) ? (ctx->split_big == 2 ? ch.count : split_big(hmc, hoc, ch.count, dv.sm_count)) : 0;
+            sc.nbig = 0;
+            if (ctx->path == 0 && ctx->split_big == 2) sc.nbig = ch.count;
+            else if (ctx->path == 0 && ctx->split_big && K == 1) sc.nbig = split_big(hmc, hoc, ch.count, dv.sm_count);
+            else if (ctx->path == 0 && ctx->split_big)          // hoc is largest first: the prefix at or above the shard's threshold
+                while (sc.nbig < ch.count && (double)hmc[hoc[sc.nbig]].in_len + (double)hmc[hoc[sc.nbig]].out_cap >= big_threshold) sc.nbig++;
             plan_parts(hmc, hoc, ch.count, sc.nbig, region[c % NS], hs + ch.first, cuts_big_of[c], cuts_of[c], sc.big_seqs);
             sc.cuts = &cuts_of[c];
             sc.cuts_big = &cuts_big_of[c];
