@@ -59,34 +59,66 @@ def peaks():
 
 
 class ClockSampler(threading.Thread):
+    """SM clock and throttle reasons of one GPU while the timed region runs: NVML in-process (a sample every
+    few ms, so even a 0.3 s region is covered on a busy 8-GPU box), nvidia-smi as the fallback."""
+
     def __init__(self, gpu):
         super().__init__(daemon=True)
         self.gpu = gpu
         self.stop = False
         self.sm, self.reasons, self.max_mhz = [], set(), None
+        self.how = "nvml"
+        self.h = None
+        try:
+            import pynvml
+            pynvml.nvmlInit()
+            self.nv = pynvml
+            vis = os.environ.get("CUDA_VISIBLE_DEVICES")
+            idx = int(vis.split(",")[gpu]) if vis and all(x.strip().isdigit() for x in vis.split(",")) else gpu
+            self.h = pynvml.nvmlDeviceGetHandleByIndex(idx)
+            self.max_mhz = float(pynvml.nvmlDeviceGetMaxClockInfo(self.h, pynvml.NVML_CLOCK_SM))
+        except Exception:
+            self.h = None
+            self.how = "nvidia-smi"
 
-    def run(self):
+    def sample_nvml(self):
+        nv = self.nv
+        self.sm.append(float(nv.nvmlDeviceGetClockInfo(self.h, nv.NVML_CLOCK_SM)))
+        r = nv.nvmlDeviceGetCurrentClocksEventReasons(self.h) if hasattr(nv, "nvmlDeviceGetCurrentClocksEventReasons") \
+            else nv.nvmlDeviceGetCurrentClocksThrottleReasons(self.h)
+        for nm, bit in (("hw_slowdown", 0x8), ("sw_thermal_slowdown", 0x20), ("hw_thermal_slowdown", 0x40),
+                        ("sw_power_cap", 0x4)):
+            if r & bit:
+                self.reasons.add(nm)
+
+    def sample_smi(self):
         q = ("clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
              "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
         names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        o = subprocess.run(["nvidia-smi", "-i", str(self.gpu), "--query-gpu=" + q,
+                            "--format=csv,noheader,nounits"], capture_output=True, text=True, timeout=5).stdout
+        f = [x.strip() for x in o.strip().split(",")]
+        self.sm.append(float(f[0]))
+        self.max_mhz = float(f[1])
+        for nm, v in zip(names, f[2:]):
+            if v.lower().startswith("active"):
+                self.reasons.add(nm)
+
+    def run(self):
         while not self.stop:
             try:
-                o = subprocess.run(["nvidia-smi", "-i", str(self.gpu), "--query-gpu=" + q,
-                                    "--format=csv,noheader,nounits"], capture_output=True, text=True, timeout=5).stdout
-                f = [x.strip() for x in o.strip().split(",")]
-                self.sm.append(float(f[0]))
-                self.max_mhz = float(f[1])
-                for nm, v in zip(names, f[2:]):
-                    if v.lower().startswith("active"):
-                        self.reasons.add(nm)
+                if self.h is not None:
+                    self.sample_nvml()
+                else:
+                    self.sample_smi()
             except Exception:
                 pass
-            time.sleep(0.05)
+            time.sleep(0.005 if self.h is not None else 0.05)
 
     def summary(self):
         s = sorted(self.sm)
         return {"sm_mhz": s[len(s) // 2] if s else None, "sm_max_mhz": self.max_mhz, "reasons": sorted(self.reasons),
-                "samples": len(s)}
+                "samples": len(s), "source": self.how}
 
 
 def cpu_reference_run(members, steps, warmup, threads):

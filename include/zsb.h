@@ -98,7 +98,10 @@ ZSB_API int zsb_inflate_batch_device(zsb_ctx *ctx, int dev_index, size_t n, cons
 
 /* Tuning knobs: "path" 0 auto / 1 lane path (one member per lane, k_lane + k_lz) / 2 group path
  * (k_inflate<G>); "profile" 1 = time the decode kernels (zsb_profile_read); "lanes_per_member" G of the group path (1,2,4,8,16,32); "seq_arena_bytes" most
- * sequence scratch the lane path may hold at once (larger batches are decoded in slices). */
+ * sequence scratch the lane path may hold at once (larger batches are decoded in slices; 0, the default = half
+ * of the device's free memory, at least 32 GiB); "split_big" 1 (default) members far larger than the rest of
+ * their batch are decoded a warp each (zsb_plan_big), 0 never; "chunks" pipeline depth of host-buffer batches
+ * (0 = choose). */
 ZSB_API int zsb_set_option(zsb_ctx *ctx, const char *name, long value);
 ZSB_API long zsb_get_option(const zsb_ctx *ctx, const char *name);
 

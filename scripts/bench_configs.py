@@ -80,6 +80,7 @@ def main():
     ap.add_argument("--small", action="store_true")
     ap.add_argument("--no-split", action="store_true", help="option split_big = 0: no k_big for large members")
     ap.add_argument("--steps", type=int, default=3)
+    ap.add_argument("--arena-gib", type=int, default=0, help="option seq_arena_bytes (GiB); 0 = the default")
     args = ap.parse_args()
     import config_runner
     import workloads
@@ -95,6 +96,8 @@ def main():
         eng.set_option("path", args.path)
         if args.no_split:
             eng.set_option("split_big", 0)
+        if args.arena_gib:
+            eng.set_option("seq_arena_bytes", args.arena_gib << 30)
         if args.lanes:
             eng.set_option("lanes_per_member", args.lanes)
         r = config_runner.run(w, eng, steps=args.steps, warmup=2)

@@ -247,6 +247,23 @@ static uint64_t lane_plan(const zsb_member *hm, const uint32_t *horder, size_t n
     return most;
 }
 
+// Most sequence scratch a batch may hold at once: option "seq_arena_bytes", or (0, the default) half of what
+// the device has free, at least 32 GiB: the worst-case bound of seq_bound is ~3x what members write, and every
+// extra slice of a batch of mixed sizes ends with its own tail (C4: 1.76 s in four slices, 1.27 s in one).
+// (cudaMemGetInfo costs milliseconds, so the answer is kept until a batch would not fit it.)
+static size_t arena_bytes(const zsb_ctx *ctx, zsb_dev &dv, bool refresh = false) {
+    if (ctx->seq_arena_bytes) return ctx->seq_arena_bytes;
+    if (!dv.arena_auto || refresh) {
+        size_t fr = 0, tot = 0;
+        if (cudaMemGetInfo(&fr, &tot) != cudaSuccess) {
+            cudaGetLastError();
+            fr = 0;
+        }
+        dv.arena_auto = std::max<size_t>((size_t)32 << 30, (fr + dv.d_seq_cap) / 2);
+    }
+    return dv.arena_auto;
+}
+
 // The plan of a batch whose first nbig slots are its large members: both parts' sequence offsets (off[n]; the
 // small part's start after the big part's big_seqs sequences) and slices.  Returns the sequences needed.
 static uint64_t plan_parts(const zsb_member *hm, const uint32_t *order, size_t n, size_t nbig, uint64_t arena_seqs,
@@ -424,8 +441,11 @@ static int run_device(zsb_ctx *ctx, zsb_dev &dv, size_t n, const zsb_member *dm,
         if (ctx->path != 2) {
             if (ctx->path == 0 && ctx->split_big) nbig = ctx->split_big == 2 ? n : split_big(hm, horder, n, dv.sm_count);
             off_own.resize(n);
-            const uint64_t need = plan_parts(hm, horder, n, nbig, (sc ? sc->seq_bytes : ctx->seq_arena_bytes) / sizeof(lane::seq_t),
-                                             off_own.data(), cuts_big_own, cuts_own, big_seqs);
+            uint64_t need = plan_parts(hm, horder, n, nbig, (sc ? sc->seq_bytes : arena_bytes(ctx, dv)) / sizeof(lane::seq_t),
+                                       off_own.data(), cuts_big_own, cuts_own, big_seqs);
+            if (!sc && cuts_own.size() > 2 && !ctx->seq_arena_bytes)      // sliced: is more memory free by now?
+                need = plan_parts(hm, horder, n, nbig, arena_bytes(ctx, dv, true) / sizeof(lane::seq_t), off_own.data(),
+                                  cuts_big_own, cuts_own, big_seqs);
             if (!sc && (rc = grow(ctx, dv.d_seq, dv.d_seq_cap, (size_t)need * sizeof(lane::seq_t)))) return rc;
             // (a pageable source is staged by the runtime before cudaMemcpyAsync returns, so off_own may go)
             CK(ctx, cudaMemcpyAsync(dseqoff, off_own.data(), n * sizeof(uint64_t), cudaMemcpyHostToDevice, st));
@@ -625,8 +645,8 @@ extern "C" int zsb_set_option(zsb_ctx *ctx, const char *name, long value) {
         ctx->path = (int)value;
         return 0;
     }
-    if (!strcmp(name, "seq_arena_bytes")) {
-        if (value < 4096) return ZSB_E_ARG;
+    if (!strcmp(name, "seq_arena_bytes")) {       // 0 = choose from the device's free memory
+        if (value != 0 && value < 4096) return ZSB_E_ARG;
         ctx->seq_arena_bytes = (size_t)value;
         return 0;
     }
@@ -800,7 +820,7 @@ static int batch_host(zsb_ctx *ctx, size_t n, const zsb_member *m, zsb_result *r
         std::vector<Chunk> chunks(K);
         std::vector<uint64_t> seq_need(K);
         size_t in_total = 0, out_total = 0;
-        const uint64_t arena_seqs = ctx->seq_arena_bytes / sizeof(lane::seq_t);
+        const uint64_t arena_seqs = arena_bytes(ctx, dv) / sizeof(lane::seq_t);
         for (int c = 0; c < K; c++) {
             Chunk &ch = chunks[c];
             ch.first = k * c / K;

@@ -19,6 +19,7 @@ struct zsb_dev {
     uint8_t *fixed_lane = nullptr;     // the same in the lane path's slot format
     uint8_t *d_seq = nullptr;          // LZ sequence arena of the lane path
     size_t d_seq_cap = 0;
+    size_t arena_auto = 0;             // arena chosen from the device's free memory (option seq_arena_bytes = 0)
     uint8_t *d_plan = nullptr;         // per call: slot order (u32) + per-slot sequence offsets (u64)
     size_t d_plan_cap = 0;
     bool lane_configured = false;
@@ -42,7 +43,7 @@ struct zsb_ctx {
     std::vector<zsb_dev> devs;
     int lanes = 16;                    // group path: lanes of a warp that cooperate on one member
     int path = 0;                      // 0 auto, 1 lane path (k_lane + k_lz), 2 group path (k_inflate<G>)
-    size_t seq_arena_bytes = 32ull << 30;   // most sequence scratch one slice of a batch may use
+    size_t seq_arena_bytes = 0;        // most sequence scratch one slice of a batch may use; 0 = from free memory (arena_bytes)
     size_t slab_bytes = 256u << 20;
     int chunks = 0;                    // host batches: pipeline depth (0 = choose from the batch)
     long launches = 0;
