@@ -127,8 +127,35 @@ def test_many_small_and_unaligned(eng):
         wb = rnd.choice([-15, 15, 31, -16])
         enc = -15 if wb == -16 else wb
         items.append(("tiny%d" % k, b"" if k % 97 == 0 else zsblib_gen().deflate(plain, rnd.choice([0, 1, 6, 9]), enc), wb, n + rnd.choice([0, 3])))
-    for lanes in (0, 1, 8, 32):
+    for lanes in (0, "big", 1, 8, 32):
         run_cases(eng, lanes, items)
+
+
+def test_call_level_edge_cases(eng):
+    """Empty batches, NULL buffers, sizes beyond zlib's 32-bit counters, bad arguments: what the reference's
+    entry points would answer (src/inflate.c:186-224 Z_STREAM_ERROR on bad parameters), never a crash."""
+    select(eng, 0)
+    lib = eng.lib
+    assert lib.zsb_inflate_batch(eng.ctx, 0, None, None) == 0
+    assert lib.zsb_inflate_batch(None, 1, None, None) == -100            # ZSB_E_ARG
+    data = zsblib_gen().deflate(b"abc" * 100, 6, -15)
+    ibuf = ctypes.create_string_buffer(data, len(data))
+    obuf = ctypes.create_string_buffer(4 * 300)
+    m = (zsblib.Member * 4)()
+    r = (zsblib.Result * 4)()
+    for i in range(4):
+        m[i].inp, m[i].in_len, m[i].out, m[i].out_cap, m[i].window_bits = (
+            ctypes.addressof(ibuf), len(data), ctypes.addressof(obuf) + 300 * i, 300, -15)
+    m[1].in_len = 1 << 33                      # more than a uInt avail_in can say
+    m[2].window_bits = -17                     # src/inflate.c:159-162
+    m[3].inp = None                            # NULL next_in with avail_in != 0
+    for path in (0, 2):
+        eng.set_option("path", path)
+        assert lib.zsb_inflate_batch(eng.ctx, 4, m, r) == 0
+        assert (r[0].ret, r[0].total_out) == (1, 300) and obuf.raw[:300] == b"abc" * 100
+        assert [r[i].ret for i in (1, 2, 3)] == [-2, -2, -2]
+        assert [r[i].total_out for i in (1, 2, 3)] == [0, 0, 0]
+    eng.set_option("path", 0)
 
 
 def test_lane_path_slices(eng):

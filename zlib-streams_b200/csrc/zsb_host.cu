@@ -742,6 +742,7 @@ static size_t layout_runs(const zsb_member *m, const std::vector<uint32_t> &idx,
         uintptr_t p = out ? (uintptr_t)x.out : (uintptr_t)x.in;
         size_t len = out ? x.out_cap : x.in_len;
         if (len == 0 || p == 0) continue;
+        if (x.in_len > 0xfffffff0ull || x.out_cap > 0xfffffff0ull) continue;   // answered Z_STREAM_ERROR, never staged
         if (open && p >= end && p - end <= gap_limit) {
             off[j] = dev_base + (p - host_base);
         } else {
