@@ -257,3 +257,23 @@ def test_pipelined_uniform_batch_stays_on_the_lane_path(eng):
         assert eng.lib.zsb_last_launches(eng.ctx) == 2 * K          # k_lane + k_lz per chunk, no k_big
     finally:
         eng.set_option("chunks", 0)
+
+
+def test_one_context_over_all_gpus_of_the_box():
+    """zsb_create(devices, N) + ONE zsb_inflate_batch(): members sharded over the box's GPUs by zsb_plan_shards
+    (no collective), results and bytes back in the caller's order.  Skipped on a one-GPU box."""
+    import torch
+    ndev = torch.cuda.device_count()
+    if ndev < 2:
+        pytest.skip("needs at least two GPUs")
+    e = zsblib.Zsb(devices=list(range(ndev)))
+    try:
+        assert e.lib.zsb_num_devices(e.ctx) == ndev
+        items = [(n, d, w, len(p) + 8) for n, d, w, p in cases.valid_streams()]
+        items += cases.damaged_streams(200)[:300]
+        for chunks in (0, 3):
+            e.set_option("chunks", chunks)
+            run_cases(e, 0, items * 4)
+            run_cases(e, "big", items)
+    finally:
+        e.close()

@@ -883,6 +883,8 @@ static int batch_host(zsb_ctx *ctx, size_t n, const zsb_member *m, zsb_result *r
         static const bool trace = getenv("ZSB_TRACE") != nullptr;
         std::vector<cudaEvent_t> tev;
         if (trace) {
+            fprintf(stderr, "zsb trace host: planning done %.2f ms after the call started\n",
+                    std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t_call).count());
             tev.resize(3 * K + 1);
             for (auto &e : tev) CK(ctx, cudaEventCreate(&e));
             CK(ctx, cudaEventRecord(tev[3 * K], dv.copy_stream));
