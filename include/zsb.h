@@ -180,6 +180,15 @@ ZSB_API int zsb_zip_inflate(zsb_ctx *ctx, const void *zip, const zsb_zip_entry *
 ZSB_API int zsb_gunzip_files(zsb_ctx *ctx, size_t n, const void *const *in, const size_t *in_len, void *const *out,
                              const size_t *out_cap, int window_bits, zsb_result *r, uint32_t *members);
 
+/* ---- many z_streams per call ----
+ * rets[i] = inflate(strms[i], flush) for n streams initialised with inflateInit2_() of this library, with
+ * every round of GPU work done for all of them by one set of launches (one CTA per stream) and one pair of
+ * PCIe copies: the shape of the reference's real caller, many TransformStreams feeding <= 32 KiB in / 64 KiB
+ * out per call (src/wasm/api/zlib-streams.js:64-138).  strms is an array of z_streamp (declared void * here so
+ * that this header does not need <zlib.h>); each z_stream is updated exactly as inflate() would.  Returns 0, or
+ * ZSB_E_ARG. */
+ZSB_API int zsb_inflate_streams(size_t n, void **strms, int flush, int *rets);
+
 #define ZSB_E_ZIP   (-103)
 #define ZSB_E_ARG   (-100)
 #define ZSB_E_CUDA  (-101)

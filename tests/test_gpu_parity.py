@@ -210,6 +210,36 @@ def test_zstream_random_chunkings():
         zs_compare(api, name, data, wb, chunks, rnd.choice([5, 300, 65536]))
 
 
+def test_zstream_many_streams_per_call():
+    """zsb_inflate_streams (SURVEY.md §8f rank 2): hundreds of z_streams advance together, one call per tick;
+    every stream's call-by-call trace and output must equal what the reference gives that stream alone."""
+    import random
+    api = zsblib.ZStreamApi()
+    rnd = random.Random(9)
+    jobs, names = [], []
+    for n, d, m in cases.golden_fixtures():
+        jobs.append((d, -16, [32768], 65536))
+        names.append(n)
+    for n, d, w, p in cases.valid_streams():
+        jobs.append((d, w, [32768], 65536))
+        names.append(n)
+    for n, d, w, c in cases.damaged_streams(120)[:120]:
+        jobs.append((d, w, [32768], 65536))
+        names.append(n)
+    for n, d, w, p in cases.valid_streams()[1::5]:           # odd chunkings and small output windows
+        if len(d) <= 30000:
+            jobs.append((d, w, [rnd.choice([1, 7, 500, 4096]) for _ in range(3)], rnd.choice([9, 700, 65536])))
+            names.append(n + "/odd")
+    got = api.stream_multi(jobs)
+    assert len(got) == len(jobs) > 150
+    for name, (data, wb, chunks, ocap), (tb, ob) in zip(names, jobs, got):
+        ta, oa = CHK.stream(data, wb, chunks, ocap, True, max_calls=200000)
+        if ta != tb:
+            k = next((i for i, (x, y) in enumerate(zip(ta, tb)) if x != y), min(len(ta), len(tb)))
+            raise AssertionError((name, wb, chunks, ocap, "call", k, ta[max(k - 1, 0):k + 1], tb[max(k - 1, 0):k + 1]))
+        assert oa == ob, (name, "output differs")
+
+
 def test_zstream_init_codes():
     api = zsblib.ZStreamApi()
     for wb in (-17, -16, -15, -8, -7, 0, 7, 8, 15, 16, 23, 24, 31, 47, 48, 63):

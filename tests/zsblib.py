@@ -16,7 +16,7 @@ EMUL_DIR = os.path.join(ROOT, "tests", "emul")
 API_SYMBOLS = ["zsb_create", "zsb_destroy", "zsb_create_error", "zsb_last_error", "zsb_num_devices",
                "zsb_inflate_batch", "zsb_inflate_batch_device", "zsb_set_option", "zsb_get_option",
                "zsb_last_launches", "zsb_plan_shards", "zsb_host_alloc", "zsb_host_free", "zsb_message",
-               "zsb_profile_read", "zsb_zip_scan", "zsb_zip_members", "zsb_zip_inflate", "zsb_gunzip_files", "zsb_plan_big"]
+               "zsb_profile_read", "zsb_zip_scan", "zsb_zip_members", "zsb_zip_inflate", "zsb_gunzip_files", "zsb_plan_big", "zsb_inflate_streams"]
 ZLIB_SYMBOLS = ["inflateInit_", "inflateInit2_", "inflate", "inflateEnd", "inflateReset", "inflateReset2",
                 "inflateResetKeep"]
 
@@ -280,3 +280,66 @@ class ZStreamApi:
         finally:
             self.lib.inflateEnd(ctypes.byref(s))
         return trace, bytes(out)
+
+
+    def stream_multi(self, jobs, finish=True, max_ticks=1000000):
+        """jobs: [(data, wbits, in_chunks, out_cap)].  All streams advance together: every tick is ONE
+        zsb_inflate_streams() call over the streams still running.  Per stream the driver and the trace format
+        are those of stream() / orclib.Checker.stream()."""
+        n = len(jobs)
+        self.lib.zsb_inflate_streams.argtypes = [ctypes.c_size_t, ctypes.c_void_p, ctypes.c_int, ctypes.c_void_p]
+        st = []
+        for data, wbits, in_chunks, out_cap in jobs:
+            s = ZStreamStruct()
+            rc = self.lib.inflateInit2_(ctypes.byref(s), wbits, b"1.3", ctypes.sizeof(s))
+            st.append(dict(s=s, init=rc, trace=[("init", rc)] if rc else [], out=bytearray(), pos=0, k=0, pending=b"",
+                           buf=ctypes.create_string_buffer(max(out_cap, 1)), done=rc != 0, data=data, chunks=in_chunks,
+                           cap=out_cap, ibuf=None))
+        try:
+            for _ in range(max_ticks):
+                act = [x for x in st if not x["done"]]
+                if not act:
+                    break
+                # streams are grouped by the flush value their driver would pass
+                for flush in (0, 4):
+                    grp = []
+                    for x in act:
+                        if not x["pending"] and x["pos"] < len(x["data"]):
+                            c = x["chunks"][x["k"] % len(x["chunks"])]
+                            x["k"] += 1
+                            x["pending"] = x["data"][x["pos"]:x["pos"] + c]
+                            x["pos"] += len(x["pending"])
+                        f = 4 if (finish and x["pos"] >= len(x["data"])) else 0
+                        if f == flush and not x.get("ticked"):
+                            grp.append(x)
+                    if not grp:
+                        continue
+                    ptrs = (ctypes.c_void_p * len(grp))()
+                    rets = (ctypes.c_int * len(grp))()
+                    for i, x in enumerate(grp):
+                        s = x["s"]
+                        x["ibuf"] = ctypes.create_string_buffer(x["pending"], max(len(x["pending"]), 1))
+                        s.next_in = ctypes.addressof(x["ibuf"])
+                        s.avail_in = len(x["pending"])
+                        s.next_out = ctypes.addressof(x["buf"])
+                        s.avail_out = x["cap"]
+                        ptrs[i] = ctypes.addressof(s)
+                        x["ticked"] = True
+                    rc = self.lib.zsb_inflate_streams(len(grp), ptrs, flush, rets)
+                    assert rc == 0
+                    for i, x in enumerate(grp):
+                        s, ret = x["s"], rets[i]
+                        c, p = len(x["pending"]) - s.avail_in, x["cap"] - s.avail_out
+                        x["out"] += x["buf"].raw[:p]
+                        x["trace"].append((ret, self.msgs.get(s.msg, 0) if s.msg else 0, s.total_in, s.total_out,
+                                           s.adler & 0xffffffff, s.data_type, c, p))
+                        x["pending"] = x["pending"][c:]
+                        if ret not in (0, -5) or (ret == -5 and c == 0 and p == 0 and x["pos"] >= len(x["data"])):
+                            x["done"] = True
+                for x in act:
+                    x["ticked"] = False
+        finally:
+            for x in st:
+                if x["init"] == 0:
+                    self.lib.inflateEnd(ctypes.byref(x["s"]))
+        return [(x["trace"], bytes(x["out"])) for x in st]

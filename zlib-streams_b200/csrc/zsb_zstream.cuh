@@ -13,6 +13,8 @@
 
 namespace zsb {
 
+constexpr uint32_t ZS_CARRY_LIMIT = 128u << 10;     // bytes of an unfinished unit a stream can carry to its next call
+
 __global__ void __launch_bounds__(32) k_zs_decode(zs::State *S, const uint8_t *in, uint32_t in_len, uint32_t out_cap,
                                                   lane::seq_t *seq, const uint8_t *fixed_tab) {
     __shared__ uint32_t lut[LUT_WORDS];
@@ -48,8 +50,68 @@ __global__ void __launch_bounds__(CHK_THREADS) k_zs_finish(zs::State *S, uint8_t
     }
     __syncthreads();
     for (uint32_t i = tid; i < zs::HIST; i += CHK_THREADS) hist[i] = w[produced + i];
-    const uint32_t rb = s_resume, n = s_cpos > s_resume ? s_cpos - s_resume : 0u;
+    uint32_t rb = s_resume, n = s_cpos > s_resume ? s_cpos - s_resume : 0u;
+    if (n > ZS_CARRY_LIMIT) n = ZS_CARRY_LIMIT;           // the host answers Z_MEM_ERROR (a gzip header that long)
     for (uint32_t i = tid; i < n; i += CHK_THREADS) carry[i] = in[rb + i];
+}
+
+// ---- many z_streams per launch (zsb_inflate_streams): one CTA per stream ----
+struct ZsJob {
+    zs::State *S;
+    uint8_t *in;           // [carry bytes | new bytes]: the new bytes are at in + carry_len
+    uint8_t *w;            // [HIST bytes of history | this round's output]
+    lane::seq_t *seq;
+    uint8_t *hist, *carry;
+    uint32_t carry_len, in_len, out_cap;
+    int32_t finish;
+};
+
+__global__ void __launch_bounds__(CHK_THREADS) k_zsm_prep(const ZsJob *jobs) {
+    const ZsJob j = jobs[blockIdx.x];
+    for (uint32_t i = threadIdx.x; i < j.carry_len; i += CHK_THREADS) j.in[i] = j.carry[i];
+    const uint4 *h4 = (const uint4 *)j.hist;
+    uint4 *w4 = (uint4 *)j.w;
+    for (uint32_t i = threadIdx.x; i < zs::HIST / 16; i += CHK_THREADS) w4[i] = h4[i];
+}
+
+__global__ void __launch_bounds__(32) k_zsm_decode(const ZsJob *jobs, const uint8_t *fixed_tab) {
+    __shared__ uint32_t lut[LUT_WORDS];
+    __shared__ __align__(16) uint8_t scr[lane::WSCR];
+    __shared__ uint32_t ring[32 * lane::RING_WORDS];
+    const ZsJob j = jobs[blockIdx.x];
+    init_lut(lut, threadIdx.x, 32);
+    __syncwarp();
+    zs::stream_decode<32>(*j.S, j.in, j.in_len, j.out_cap, j.seq, fixed_tab, scr, ring + threadIdx.x, lut, threadIdx.x);
+}
+
+__global__ void __launch_bounds__(32) k_zsm_lz(const ZsJob *jobs) {
+    const ZsJob j = jobs[blockIdx.x];
+    const uint32_t nseq = j.S->call.nseq;
+    if (nseq) lz::resolve_member<32>(j.w + zs::HIST, j.in, j.seq, nseq, threadIdx.x);
+}
+
+__global__ void __launch_bounds__(CHK_THREADS) k_zsm_finish(const ZsJob *jobs, zs::Call *calls) {
+    __shared__ ChkShared sh;
+    __shared__ uint32_t s_resume, s_cpos;
+    const ZsJob j = jobs[blockIdx.x];
+    zs::State *S = j.S;
+    const int tid = threadIdx.x;
+    chk_init(sh);
+    const uint32_t produced = S->call.produced, kind = S->kind;
+    uint32_t check = S->check;
+    if (kind != 0 && produced) check = cta_check(sh, kind, j.w + zs::HIST, produced, check);
+    if (tid == 0) {
+        zs::finish_call(*S, j.in, j.in_len, check, j.finish != 0);
+        const zs::Call &c = S->call;
+        s_resume = c.resume_byte;
+        s_cpos = c.cpos;
+        calls[blockIdx.x] = c;
+    }
+    __syncthreads();
+    for (uint32_t i = tid; i < zs::HIST; i += CHK_THREADS) j.hist[i] = j.w[produced + i];
+    uint32_t rb = s_resume, n = s_cpos > s_resume ? s_cpos - s_resume : 0u;
+    if (n > ZS_CARRY_LIMIT) n = ZS_CARRY_LIMIT;           // the host answers Z_MEM_ERROR (a gzip header that long)
+    for (uint32_t i = tid; i < n; i += CHK_THREADS) j.carry[i] = j.in[rb + i];
 }
 
 }  // namespace zsb
@@ -59,7 +121,7 @@ __global__ void __launch_bounds__(CHK_THREADS) k_zs_finish(zs::State *S, uint8_t
 // ---------------------------------------------------------------------------------------------------
 namespace {
 
-constexpr uint32_t ZS_IN_SLICE = 1u << 20, ZS_OUT_SLICE = 1u << 20, ZS_CARRY_CAP = 128u << 10;
+constexpr uint32_t ZS_IN_SLICE = 1u << 20, ZS_OUT_SLICE = 1u << 20, ZS_CARRY_CAP = zsb::ZS_CARRY_LIMIT;
 constexpr uint32_t ZS_MAGIC = 0x5a534221u;
 
 // device buffers shared by all z_streams of the process (one inflate() runs at a time)
@@ -71,6 +133,13 @@ struct ZsShared {
     zsb::lane::seq_t *d_seq = nullptr;
     zsb::zs::Call *h_call = nullptr;       // pinned
     bool failed = false;
+    // zsb_inflate_streams: staging for m_cap streams per round
+    size_t m_cap = 0;
+    uint8_t *m_in = nullptr, *m_w = nullptr;
+    zsb::lane::seq_t *m_seq = nullptr;
+    zsb::ZsJob *m_jobs = nullptr, *mh_jobs = nullptr;          // device / pinned
+    zsb::zs::Call *m_calls = nullptr, *mh_calls = nullptr;     // device / pinned
+    uint8_t *mh_in = nullptr, *mh_out = nullptr;               // pinned, compact: ZSM_IN / ZSM_OUT bytes per stream
 };
 ZsShared g_zs;
 
@@ -264,6 +333,36 @@ ZSB_API int inflateEnd(z_streamp strm) {
 
 }  // extern "C"
 
+namespace {
+// what inflate() leaves on the z_stream once its rounds are over (reference src/inflate.c:1253-1274); c is the
+// last round's record
+int zs_exit_bookkeeping(z_streamp strm, ZStream *z, const zsb::zs::Call &c, uInt in0, uInt out0, int flush) {
+    using namespace zsb;
+    int ret = Z_OK;
+    const uInt in_used = in0 - strm->avail_in, out_used = out0 - strm->avail_out;
+    if (c.stop == EV_NEEDDICT) {                                // returns before the exit bookkeeping
+        strm->adler = c.adler;
+        z->phase = zs::PH_NEEDDICT;
+        return Z_NEED_DICT;
+    }
+    strm->total_in += in_used;
+    strm->total_out += out_used;
+    if (z->wrap) strm->adler = c.adler;
+    strm->data_type = (int)c.data_type;
+    if (c.stop == EV_DONE) {
+        ret = Z_STREAM_END;
+        z->phase = zs::PH_DONE;
+    } else if (c.stop == EV_ERR || c.stop == EV_INITERR) {
+        ret = Z_DATA_ERROR;
+        strm->msg = (char *)zsb_message(c.msg);
+        z->phase = zs::PH_BAD;
+    }
+    z->last_dt = c.data_type & 0x7fu;
+    if (((in_used == 0 && out_used == 0) || flush == Z_FINISH) && ret == Z_OK) ret = Z_BUF_ERROR;
+    return ret;
+}
+}  // namespace
+
 // inflate(): reference src/inflate.c:597-1275.  Z_BLOCK / Z_TREES are accepted and treated as
 // Z_NO_FLUSH (they only add early returns the reference's callers never ask for).
 extern "C" ZSB_API int inflate(z_streamp strm, int flush) {
@@ -290,7 +389,7 @@ extern "C" ZSB_API int inflate(z_streamp strm, int flush) {
     for (;;) {
         const uint32_t ni = strm->avail_in < ZS_IN_SLICE ? strm->avail_in : ZS_IN_SLICE;
         const uint32_t no = strm->avail_out < ZS_OUT_SLICE ? strm->avail_out : ZS_OUT_SLICE;
-        if (z->carry_len + ni > ZS_IN_SLICE + ZS_CARRY_CAP) {
+        if (z->carry_len > ZS_CARRY_CAP) {
             ret = Z_MEM_ERROR;                                  // a wrapper header longer than the carry buffer
             break;
         }
@@ -333,25 +432,172 @@ extern "C" ZSB_API int inflate(z_streamp strm, int flush) {
         return Z_MEM_ERROR;
     }
     if (ret == Z_MEM_ERROR) return ret;
-    const uInt in_used = in0 - strm->avail_in, out_used = out0 - strm->avail_out;
-    if (c.stop == EV_NEEDDICT) {                                // returns before the exit bookkeeping
-        strm->adler = c.adler;
-        z->phase = zs::PH_NEEDDICT;
-        return Z_NEED_DICT;
+    return zs_exit_bookkeeping(strm, z, c, in0, out0, flush);
+}
+
+// ---------------------------------------------------------------------------------------------------
+// zsb_inflate_streams(): inflate(strms[i], flush) for n streams, with every round of GPU work (stage, decode,
+// resolve, finish) done for all of them by ONE set of launches, one CTA per stream.  Per stream the result is
+// exactly what inflate() gives: same rounds, same bookkeeping (zs_exit_bookkeeping).  This is the shape of
+// the reference's real caller — many TransformStreams each feeding <= 32 KiB in / 64 KiB out per call
+// (src/wasm/api/zlib-streams.js:64-138) — where a launch and a PCIe round trip per stream and call would
+// dominate.  
+// ---------------------------------------------------------------------------------------------------
+namespace {
+constexpr uint32_t ZSM_IN = 64u << 10, ZSM_OUT = 128u << 10;                 // per stream and round
+constexpr size_t ZSM_IN_STRIDE = ZS_CARRY_CAP + ZSM_IN + 256, ZSM_W_STRIDE = zsb::zs::HIST + ZSM_OUT + 256;
+
+bool zsm_reserve(size_t n) {
+    if (n <= g_zs.m_cap) return true;
+    const size_t cap = n + n / 4 + 16;
+    const size_t seqs = zsb_seq_bound_sizes(ZSM_IN + ZS_CARRY_CAP, ZSM_OUT) + 8;
+    cudaFree(g_zs.m_in); cudaFree(g_zs.m_w); cudaFree(g_zs.m_seq); cudaFree(g_zs.m_jobs); cudaFree(g_zs.m_calls);
+    cudaFreeHost(g_zs.mh_jobs); cudaFreeHost(g_zs.mh_calls); cudaFreeHost(g_zs.mh_in); cudaFreeHost(g_zs.mh_out);
+    g_zs.m_cap = 0;
+    g_zs.m_in = g_zs.m_w = nullptr; g_zs.m_seq = nullptr; g_zs.m_jobs = g_zs.mh_jobs = nullptr;
+    g_zs.m_calls = g_zs.mh_calls = nullptr; g_zs.mh_in = g_zs.mh_out = nullptr;
+    const bool ok = cudaMalloc(&g_zs.m_in, cap * ZSM_IN_STRIDE) == cudaSuccess &&
+                    cudaMalloc(&g_zs.m_w, cap * ZSM_W_STRIDE) == cudaSuccess &&
+                    cudaMalloc(&g_zs.m_seq, cap * seqs * sizeof(zsb::lane::seq_t)) == cudaSuccess &&
+                    cudaMalloc(&g_zs.m_jobs, cap * sizeof(zsb::ZsJob)) == cudaSuccess &&
+                    cudaMalloc(&g_zs.m_calls, cap * sizeof(zsb::zs::Call)) == cudaSuccess &&
+                    cudaHostAlloc(&g_zs.mh_jobs, cap * sizeof(zsb::ZsJob), cudaHostAllocDefault) == cudaSuccess &&
+                    cudaHostAlloc(&g_zs.mh_calls, cap * sizeof(zsb::zs::Call), cudaHostAllocDefault) == cudaSuccess &&
+                    cudaHostAlloc(&g_zs.mh_in, cap * (size_t)ZSM_IN, cudaHostAllocDefault) == cudaSuccess &&
+                    cudaHostAlloc(&g_zs.mh_out, cap * (size_t)ZSM_OUT, cudaHostAllocDefault) == cudaSuccess;
+    if (!ok) {
+        cudaGetLastError();
+        return false;
     }
-    strm->total_in += in_used;
-    strm->total_out += out_used;
-    if (z->wrap) strm->adler = c.adler;
-    strm->data_type = (int)c.data_type;
-    if (c.stop == EV_DONE) {
-        ret = Z_STREAM_END;
-        z->phase = zs::PH_DONE;
-    } else if (c.stop == EV_ERR || c.stop == EV_INITERR) {
-        ret = Z_DATA_ERROR;
-        strm->msg = (char *)zsb_message(c.msg);
-        z->phase = zs::PH_BAD;
+    g_zs.m_cap = cap;
+    return true;
+}
+}  // namespace
+
+extern "C" ZSB_API int zsb_inflate_streams(size_t n, void **strms_v, int flush, int *rets) {
+    using namespace zsb;
+    z_streamp *strms = (z_streamp *)strms_v;
+    if (n && (!strms || !rets)) return ZSB_E_ARG;
+    struct Live {
+        size_t i;
+        ZStream *z;
+        uInt in0, out0;
+        zs::Call c;
+    };
+    std::vector<Live> live;
+    for (size_t i = 0; i < n; i++) {
+        z_streamp strm = strms[i];
+        ZsHandle *h = zs_handle(strm);
+        if (!h || strm->next_out == Z_NULL || (strm->next_in == Z_NULL && strm->avail_in != 0)) {
+            rets[i] = Z_STREAM_ERROR;
+            continue;
+        }
+        ZStream *z = h->zs;
+        if (z->phase == zs::PH_NEEDDICT) {
+            rets[i] = Z_NEED_DICT;
+            continue;
+        }
+        if (z->phase == zs::PH_DONE || z->phase == zs::PH_BAD) {
+            strm->data_type = (int)z->last_dt;
+            rets[i] = z->phase == zs::PH_DONE ? Z_STREAM_END : Z_DATA_ERROR;
+            continue;
+        }
+        if (z->carry_len > ZS_CARRY_CAP) {                      // a wrapper header longer than the carry buffer
+            rets[i] = Z_MEM_ERROR;
+            continue;
+        }
+        Live l;
+        l.i = i; l.z = z; l.in0 = strm->avail_in; l.out0 = strm->avail_out;
+        memset(&l.c, 0, sizeof l.c);
+        live.push_back(l);
+        rets[i] = Z_OK;
     }
-    z->last_dt = c.data_type & 0x7fu;
-    if (((in_used == 0 && out_used == 0) || flush == Z_FINISH) && ret == Z_OK) ret = Z_BUF_ERROR;
-    return ret;
+    if (live.empty()) return 0;
+    std::lock_guard<std::mutex> lk(g_zs.mu);
+    if (!zsm_reserve(live.size())) {
+        for (const Live &l : live) rets[l.i] = Z_MEM_ERROR;
+        return 0;
+    }
+    int cur = 0;
+    cudaGetDevice(&cur);
+    const int dev = g_zs.ctx->devs[0].device;
+    if (cur != dev) cudaSetDevice(dev);
+    cudaStream_t st = g_zs.st;
+    const size_t seqs = zsb_seq_bound_sizes(ZSM_IN + ZS_CARRY_CAP, ZSM_OUT) + 8;
+    std::vector<size_t> round(live.size());           // indices into live of the streams of this round
+    for (size_t k = 0; k < live.size(); k++) round[k] = k;
+    bool cuda_ok = true;
+    while (!round.empty() && cuda_ok) {
+        const size_t m = round.size();
+        std::vector<uint32_t> nis(m);
+        for (size_t k = 0; k < m; k++) {
+            Live &l = live[round[k]];
+            z_streamp strm = strms[l.i];
+            const uint32_t ni = strm->avail_in < ZSM_IN ? strm->avail_in : ZSM_IN;
+            const uint32_t no = strm->avail_out < ZSM_OUT ? strm->avail_out : ZSM_OUT;
+            nis[k] = ni;
+            if (ni) memcpy(g_zs.mh_in + k * (size_t)ZSM_IN, strm->next_in, ni);
+            ZsJob &j = g_zs.mh_jobs[k];
+            j.S = l.z->d_state;
+            j.in = g_zs.m_in + k * ZSM_IN_STRIDE + ZS_CARRY_CAP - l.z->carry_len;   // the carry sits right before the new bytes
+            j.w = g_zs.m_w + k * ZSM_W_STRIDE;
+            j.seq = g_zs.m_seq + k * seqs;
+            j.hist = l.z->d_hist;
+            j.carry = l.z->d_carry;
+            j.carry_len = l.z->carry_len;
+            j.in_len = l.z->carry_len + ni;
+            j.out_cap = no;
+            j.finish = flush == Z_FINISH;
+        }
+        cuda_ok = cudaMemcpyAsync(g_zs.m_jobs, g_zs.mh_jobs, m * sizeof(ZsJob), cudaMemcpyHostToDevice, st) == cudaSuccess &&
+                  cudaMemcpy2DAsync(g_zs.m_in + ZS_CARRY_CAP, ZSM_IN_STRIDE, g_zs.mh_in, ZSM_IN, ZSM_IN, m,
+                                    cudaMemcpyHostToDevice, st) == cudaSuccess;
+        if (!cuda_ok) break;
+        k_zsm_prep<<<(unsigned)m, CHK_THREADS, 0, st>>>(g_zs.m_jobs);
+        k_zsm_decode<<<(unsigned)m, 32, 0, st>>>(g_zs.m_jobs, g_zs.ctx->devs[0].fixed_lane);
+        k_zsm_lz<<<(unsigned)m, 32, 0, st>>>(g_zs.m_jobs);
+        k_zsm_finish<<<(unsigned)m, CHK_THREADS, 0, st>>>(g_zs.m_jobs, g_zs.m_calls);
+        cuda_ok = cudaGetLastError() == cudaSuccess &&
+                  cudaMemcpyAsync(g_zs.mh_calls, g_zs.m_calls, m * sizeof(zs::Call), cudaMemcpyDeviceToHost, st) == cudaSuccess &&
+                  cudaStreamSynchronize(st) == cudaSuccess;
+        if (!cuda_ok) break;
+        uint32_t widest = 0;
+        for (size_t k = 0; k < m; k++) widest = std::max(widest, g_zs.mh_calls[k].produced);
+        if (widest) {
+            cuda_ok = cudaMemcpy2DAsync(g_zs.mh_out, ZSM_OUT, g_zs.m_w + zs::HIST, ZSM_W_STRIDE, widest, m,
+                                        cudaMemcpyDeviceToHost, st) == cudaSuccess &&
+                      cudaStreamSynchronize(st) == cudaSuccess;
+            if (!cuda_ok) break;
+        }
+        std::vector<size_t> next;
+        for (size_t k = 0; k < m; k++) {
+            Live &l = live[round[k]];
+            z_streamp strm = strms[l.i];
+            ZStream *z = l.z;
+            const zs::Call c = g_zs.mh_calls[k];
+            l.c = c;
+            if (c.produced) memcpy(strm->next_out, g_zs.mh_out + k * (size_t)ZSM_OUT, c.produced);
+            const uint32_t in_len = z->carry_len + nis[k];
+            uint32_t cpos = c.cpos;
+            if (c.stop == EV_NEEDDICT) cpos = in_len < 6 ? in_len : 6;   // header + dictionary id were read
+            const uint32_t used = cpos > z->carry_len ? cpos - z->carry_len : 0;
+            strm->next_in += used;
+            strm->avail_in -= used;
+            strm->next_out += c.produced;
+            strm->avail_out -= c.produced;
+            z->carry_len = c.cpos > c.resume_byte ? c.cpos - c.resume_byte : 0;
+            if ((c.stop == EV_STARVE && strm->avail_in > 0) || (c.stop == EV_OUTFULL && strm->avail_out > 0)) {
+                if (z->carry_len > ZS_CARRY_CAP) rets[l.i] = Z_MEM_ERROR;     // a wrapper header longer than the carry buffer
+                else next.push_back(round[k]);
+            }
+        }
+        round.swap(next);
+    }
+    if (cur != dev) cudaSetDevice(cur);
+    if (!cuda_ok) cudaGetLastError();
+    for (Live &l : live) {
+        if (!cuda_ok) rets[l.i] = Z_MEM_ERROR;
+        else if (rets[l.i] != Z_MEM_ERROR) rets[l.i] = zs_exit_bookkeeping(strms[l.i], l.z, l.c, l.in0, l.out0, flush);
+    }
+    return 0;
 }
