@@ -72,6 +72,74 @@ def zip_bench(args):
             "parity": "ok" if (not bad and same) else "MISMATCH", "mismatches": bad[:5], "path": args.path}
 
 
+def streams_bench(args):
+    """N z_streams fed the way the reference's JS wrapper feeds one (32 KiB in, 64 KiB out per call): all of them
+    per tick through zsb_inflate_streams(), against inflate() stream by stream."""
+    import ctypes
+    import time
+    import zlib
+    import gen
+    import zsblib
+    api = zsblib.ZStreamApi()
+    lib = api.lib
+    lib.zsb_inflate_streams.argtypes = [ctypes.c_size_t, ctypes.c_void_p, ctypes.c_int, ctypes.c_void_p]
+    n = 256 if args.small else 1024
+    plain = b"".join(gen.word_soup(65536, 70 + i) for i in range(16))          # 1 MiB
+    comp = gen.deflate(plain, 6, 15)
+    cbuf = ctypes.create_string_buffer(comp, len(comp))
+
+    def run(multi, count):
+        ss = [zsblib.ZStreamStruct() for _ in range(count)]
+        outs = [ctypes.create_string_buffer(65536) for _ in range(count)]
+        for s in ss:
+            assert lib.inflateInit2_(ctypes.byref(s), 15, b"1.3", ctypes.sizeof(s)) == 0
+        ptrs = (ctypes.c_void_p * count)(*[ctypes.addressof(s) for s in ss])
+        rets = (ctypes.c_int * count)()
+        pos = [0] * count
+        total, calls, crc = 0, 0, [0] * count
+        live = list(range(count))
+        t0 = time.perf_counter()
+        while live:
+            for i in live:
+                s = ss[i]
+                if s.avail_in == 0 and pos[i] < len(comp):
+                    k = min(32768, len(comp) - pos[i])
+                    s.next_in = ctypes.addressof(cbuf) + pos[i]
+                    s.avail_in = k
+                    pos[i] += k
+                s.next_out = ctypes.addressof(outs[i])
+                s.avail_out = 65536
+            if multi:
+                sub = (ctypes.c_void_p * len(live))(*[ptrs[i] for i in live])
+                assert lib.zsb_inflate_streams(len(live), sub, 0, rets) == 0
+                rr = [rets[k] for k in range(len(live))]
+            else:
+                rr = [lib.inflate(ctypes.byref(ss[i]), 0) for i in live]
+            calls += 1 if multi else len(live)
+            nxt = []
+            for i, r in zip(live, rr):
+                p = 65536 - ss[i].avail_out
+                total += p
+                crc[i] = zlib.crc32(outs[i].raw[:p], crc[i])
+                assert r in (0, 1), r
+                if r == 0:
+                    nxt.append(i)
+            live = nxt
+        dt = time.perf_counter() - t0
+        ok = all(c == zlib.crc32(plain) for c in crc) and total == count * len(plain)
+        for s in ss:
+            lib.inflateEnd(ctypes.byref(s))
+        return dt, total, calls, ok
+    dm, tm, cm, okm = run(True, n)
+    ds, ts, cs, oks = run(False, max(8, n // 16))
+    return {"config": "STREAMS", "workload": "%d zlib streams of 1 MiB (word soup, level 6), 32 KiB in / 64 KiB out per call "
+            "(src/wasm/api/zlib-streams.js:73-83), driver in Python" % n, "streams": n,
+            "multiplexed": {"seconds": dm, "out_bytes": tm, "calls": cm, "decompressed_gbs": tm / dm / 1e9, "parity": okm},
+            "one_stream_per_call": {"streams": max(8, n // 16), "seconds": ds, "out_bytes": ts, "calls": cs,
+                                    "decompressed_gbs": ts / ds / 1e9, "parity": oks},
+            "parity": "ok" if okm and oks else "MISMATCH"}
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("configs", nargs="*", default=["C3", "C4", "C5"])
@@ -90,6 +158,9 @@ def main():
     for c in args.configs:
         if c == "ZIP":
             print(json.dumps(zip_bench(args)), flush=True)
+            continue
+        if c == "STREAMS":
+            print(json.dumps(streams_bench(args)), flush=True)
             continue
         w = workloads.BUILDERS[c](**(small if args.small else full)[c])
         eng = zsblib.Zsb(devices=[0])
