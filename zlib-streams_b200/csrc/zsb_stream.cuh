@@ -62,6 +62,7 @@ struct Run {               // lane 0's bookkeeping during one call
     uint32_t last0;        // BFINAL as it was when the current block header unit started
     bool hdr_stop;
     uint32_t hdr_tin, hdr_bits;
+    const uint32_t *big_lut;   // direct tables of the current block (lane::big_build), or NULL
 };
 
 ZSB_DEV uint64_t bitpos(const BitIn &b) { return 8ull * b.next - b.nbits; }
@@ -208,6 +209,9 @@ ZSB_DEV int run_serial(State &S, Lane &L, Run &R, uint8_t *T, const uint32_t *lu
             break;
         }
         case PH_SYM: {
+            // plain literals and whole matches through the direct tables (the loop of k_big); it stops at a
+            // symbol boundary, and whatever stopped it is decoded by the checked path below
+            if (R.big_lut) lane::big_run(L, T, lut, R.big_lut);
             R.unit = bitpos(b);
             const int ev = lane::careful_symbol(d, T, lut);
             if (ev == EV_LIT) {
@@ -237,7 +241,8 @@ ZSB_DEV int run_serial(State &S, Lane &L, Run &R, uint8_t *T, const uint32_t *lu
 // One call's decode: all W lanes enter, lane 0 owns the stream.
 template <int W>
 ZSB_DEV void stream_decode(State &S, const uint8_t *in, uint32_t in_len, uint32_t out_cap, seq_t *seq,
-                           const uint8_t *fixed_tab, uint8_t *scr, uint32_t *ring, const uint32_t *lut, int ln) {
+                           const uint8_t *fixed_tab, uint8_t *scr, uint32_t *ring, const uint32_t *lut, int ln,
+                           uint32_t *big_lut = nullptr) {
     Lane L;
     Run R;
     Dec &d = L.d;
@@ -248,10 +253,14 @@ ZSB_DEV void stream_decode(State &S, const uint8_t *in, uint32_t in_len, uint32_
     d.out = nullptr; d.pos = 0; d.cap = out_cap; d.d64 = S.d64; d.last = S.last; d.at_type = 0; d.msg = 0;
     d.extent = 0; d.mlen = 0; d.mdist = 0; d.mtrunc = 0;
     L.mm.idx = 0; L.mm.kind = S.kind; L.mm.adler0 = S.check; L.mm.hdr_stop = false; L.mm.hdr_tin = 0; L.mm.hdr_bits = 0;
-    L.q0 = L.qend = nullptr; L.qbase = 0;
+    L.q0 = nullptr; L.qend = seq + (1u << 30); L.qbase = 0;     // big_run's queue guard: the call's array is bounded by the host
     L.seq = L.seq0 = seq; L.lw = 0; L.nl = 0; L.ring = ring; L.hist = S.whave; L.nlen = 0; L.ndist = 0;
     R.phase = S.phase; R.unit = 0; R.stop = EV_NONE; R.last0 = S.last; R.hdr_stop = false; R.hdr_tin = 0; R.hdr_bits = 0;
     if (active && R.phase != PH_HEAD) seek_bit(d.b, S.bit0);
+    R.big_lut = big_lut;
+    // a call that resumes inside a block: its tables are in S.tables, the direct tables are rebuilt from them
+    if (big_lut && (S.phase == PH_SYM || S.phase == PH_PENDLIT || S.phase == PH_PENDMATCH))
+        lane::big_build<W>(big_lut, T, lut, S.d64, ln);
     for (;;) {
         int want = 0;
         if (active) want = run_serial(S, L, R, T, lut, primed);
@@ -266,6 +275,7 @@ ZSB_DEV void stream_decode(State &S, const uint8_t *in, uint32_t in_len, uint32_
         } else {
             msg = lane::build_tables<W>(T, scr, info & 1023u, info >> 12, S.d64 != 0, ln);
         }
+        if (big_lut && !msg) lane::big_build<W>(big_lut, T, lut, S.d64, ln);
         if (active) {
             if (msg) {
                 d.msg = msg;

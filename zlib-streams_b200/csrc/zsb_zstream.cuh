@@ -20,9 +20,10 @@ __global__ void __launch_bounds__(32) k_zs_decode(zs::State *S, const uint8_t *i
     __shared__ uint32_t lut[LUT_WORDS];
     __shared__ __align__(16) uint8_t scr[lane::WSCR];
     __shared__ uint32_t ring[32 * lane::RING_WORDS];
+    __shared__ uint32_t big_lut[lane::BIG_LUT_BYTES / 4];
     init_lut(lut, threadIdx.x, 32);
     __syncwarp();
-    zs::stream_decode<32>(*S, in, in_len, out_cap, seq, fixed_tab, scr, ring + threadIdx.x, lut, threadIdx.x);
+    zs::stream_decode<32>(*S, in, in_len, out_cap, seq, fixed_tab, scr, ring + threadIdx.x, lut, threadIdx.x, big_lut);
 }
 
 __global__ void __launch_bounds__(32) k_zs_lz(const zs::State *S, uint8_t *out, const uint8_t *in, const lane::seq_t *seq) {
@@ -78,10 +79,11 @@ __global__ void __launch_bounds__(32) k_zsm_decode(const ZsJob *jobs, const uint
     __shared__ uint32_t lut[LUT_WORDS];
     __shared__ __align__(16) uint8_t scr[lane::WSCR];
     __shared__ uint32_t ring[32 * lane::RING_WORDS];
+    __shared__ uint32_t big_lut[lane::BIG_LUT_BYTES / 4];
     const ZsJob j = jobs[blockIdx.x];
     init_lut(lut, threadIdx.x, 32);
     __syncwarp();
-    zs::stream_decode<32>(*j.S, j.in, j.in_len, j.out_cap, j.seq, fixed_tab, scr, ring + threadIdx.x, lut, threadIdx.x);
+    zs::stream_decode<32>(*j.S, j.in, j.in_len, j.out_cap, j.seq, fixed_tab, scr, ring + threadIdx.x, lut, threadIdx.x, big_lut);
 }
 
 __global__ void __launch_bounds__(32) k_zsm_lz(const ZsJob *jobs) {
