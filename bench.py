@@ -19,6 +19,8 @@ import os
 # more hardware work queues than the default 8, so that every chunk of a pipelined host batch (the e2e leg)
 # decodes on a stream of its own; must be in the environment before CUDA starts
 os.environ.setdefault("CUDA_DEVICE_MAX_CONNECTIONS", "32")
+# stdout carries the ONE JSON line: NCCL's own log (the "NCCL version" line of NCCL_DEBUG=VERSION included) goes to stderr
+os.environ.setdefault("NCCL_DEBUG_FILE", "/dev/stderr")
 import subprocess
 import sys
 import threading

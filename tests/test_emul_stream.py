@@ -19,7 +19,7 @@ class EmulStream(orclib.Checker):
 
     def __init__(self):
         zsblib.emul()                      # builds libemul.so
-        self.lib = ctypes.CDLL(os.path.join(zsblib.EMUL_DIR, "libemul.so"))
+        self.lib = zsblib.emul().lib
         self._open = self.lib.emulzs_open
         self._open.argtypes = [ctypes.c_int, ctypes.POINTER(ctypes.c_int)]
         self._open.restype = ctypes.c_void_p

@@ -168,8 +168,9 @@ class Zsb:
 
 class Emul:
     def __init__(self):
-        path = os.path.join(EMUL_DIR, "libemul.so")
-        subprocess.run(["make", "-s", "-C", EMUL_DIR], check=True)
+        name = "libemul_asan.so" if os.environ.get("ZSB_EMUL_SANITIZE") else "libemul.so"   # ASan build: LD_PRELOAD libasan
+        path = os.path.join(EMUL_DIR, name)
+        subprocess.run(["make", "-s", "-C", EMUL_DIR, path], check=True)
         self.lib = ctypes.CDLL(path)
         self.lib.emul_decode.argtypes = [ctypes.c_char_p, ctypes.c_size_t, ctypes.c_void_p, ctypes.c_size_t,
                                          ctypes.c_int, ctypes.POINTER(Result), ctypes.c_void_p]
@@ -187,7 +188,7 @@ class Emul:
     def oneshot(self, data, out_cap, wbits, lane=False):
         import zlib
         # copy the input to a word-aligned buffer (the decoder reads whole aligned words)
-        buf_in = ctypes.create_string_buffer(data, max(len(data), 1))
+        buf_in = ctypes.create_string_buffer(data, max((len(data) + 3) & ~3, 4))      # whole aligned words, as on the device
         buf = ctypes.create_string_buffer(max(out_cap, 1))
         r = Result()
         aux = (ctypes.c_uint32 * 4)()

@@ -158,7 +158,7 @@ ZSB_DEV int code_census(const uint8_t *lens, uint32_t n, uint16_t *cnt, uint16_t
     if (maxl == 0) return 1;
     int left = 1;
     for (uint32_t l = 1; l <= 15; l++) {
-        left = (left << 1) - (int)cnt[l];
+        left = left * 2 - (int)cnt[l];
         if (left < 0) return -1;
     }
     uint32_t code = 0;

@@ -685,7 +685,7 @@ ZSB_DEV int census_sort(const uint8_t *lens, uint32_t n, uint8_t *scr, int lane,
     maxl = 0;
     for (uint32_t l = 1; l <= 15; l++) {
         const uint32_t c = cnt[l];
-        left = (left << 1) - (int)c;
+        left = left * 2 - (int)c;            // may already be negative (no shift of a negative value)
         if (left < 0) bad = 1;
         if (c) maxl = l;
         if (lane == 0) {
