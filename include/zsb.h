@@ -180,6 +180,29 @@ ZSB_API int zsb_zip_inflate(zsb_ctx *ctx, const void *zip, const zsb_zip_entry *
 ZSB_API int zsb_gunzip_files(zsb_ctx *ctx, size_t n, const void *const *in, const size_t *in_len, void *const *out,
                              const size_t *out_cap, int window_bits, zsb_result *r, uint32_t *members);
 
+/* ---- gzip header fields ----
+ * What inflateGetHeader() surfaces while inflate() walks a gzip header (reference src/inflate.c:678-816 fills
+ * gz_header; :1341-1356 registers it): a host-side parse of the member that starts at `in`, the data itself is
+ * not touched.  Offsets are relative to `in`; a field that is absent has length 0 and offset 0; name and comment
+ * lengths do not count their terminating NUL.  Returns 0 with h filled when the header is complete (the deflate
+ * data starts at in + h->header_len), Z_BUF_ERROR (-5) when the buffer ends inside the header, Z_DATA_ERROR (-3)
+ * with h->msg_id = the zsb_message() index inflate() would report there ("incorrect header check", "unknown
+ * compression method", "unknown header flags set", "header crc mismatch"), or ZSB_E_ARG. */
+typedef struct zsb_gz_header {
+    uint32_t text;        /* FTEXT: the compressor believed the data is text */
+    uint32_t time;        /* MTIME */
+    uint32_t xflags;      /* XFL */
+    uint32_t os;          /* OS */
+    uint32_t extra_off, extra_len;
+    uint32_t name_off, name_len;
+    uint32_t comment_off, comment_len;
+    uint32_t hcrc;        /* 1 = a header CRC is present (and was verified) */
+    uint32_t header_len;
+    int32_t msg_id;       /* 0 unless the return value is Z_DATA_ERROR */
+    uint32_t reserved;
+} zsb_gz_header;
+ZSB_API int zsb_gzip_header(const void *in, size_t len, zsb_gz_header *h);
+
 /* ---- many z_streams per call ----
  * rets[i] = inflate(strms[i], flush) for n streams initialised with inflateInit2_() of this library, with
  * every round of GPU work done for all of them by one set of launches (one CTA per stream) and one pair of

@@ -16,7 +16,7 @@ EMUL_DIR = os.path.join(ROOT, "tests", "emul")
 API_SYMBOLS = ["zsb_create", "zsb_destroy", "zsb_create_error", "zsb_last_error", "zsb_num_devices",
                "zsb_inflate_batch", "zsb_inflate_batch_device", "zsb_set_option", "zsb_get_option",
                "zsb_last_launches", "zsb_plan_shards", "zsb_host_alloc", "zsb_host_free", "zsb_message",
-               "zsb_profile_read", "zsb_zip_scan", "zsb_zip_members", "zsb_zip_inflate", "zsb_gunzip_files", "zsb_plan_big", "zsb_inflate_streams"]
+               "zsb_profile_read", "zsb_zip_scan", "zsb_zip_members", "zsb_zip_inflate", "zsb_gunzip_files", "zsb_plan_big", "zsb_inflate_streams", "zsb_gzip_header"]
 ZLIB_SYMBOLS = ["inflateInit_", "inflateInit2_", "inflate", "inflateEnd", "inflateReset", "inflateReset2",
                 "inflateResetKeep"]
 

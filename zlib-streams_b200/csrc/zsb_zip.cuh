@@ -180,3 +180,62 @@ extern "C" int zsb_gunzip_files(zsb_ctx *ctx, size_t n, const void *const *in, c
     }
     return 0;
 }
+
+// gzip member header -> fields (include/zsb.h; the states HEAD..HCRC of the reference's inflate(), src/inflate.c:678-816)
+namespace zsbgz {
+static uint32_t crc32_bytes(const uint8_t *p, size_t n) {          // a header is tens of bytes: bit at a time
+    uint32_t c = 0xffffffffu;
+    for (size_t i = 0; i < n; i++) {
+        c ^= p[i];
+        for (int k = 0; k < 8; k++) c = (c >> 1) ^ (0xedb88320u & (0u - (c & 1u)));
+    }
+    return ~c;
+}
+}  // namespace zsbgz
+
+extern "C" int zsb_gzip_header(const void *in, size_t len, zsb_gz_header *h) {
+    if (!h || (len && !in)) return ZSB_E_ARG;
+    memset(h, 0, sizeof *h);
+    const uint8_t *z = (const uint8_t *)in;
+    auto bad = [&](int msg) { h->msg_id = msg; return -3; };
+    if (len < 2) return -5;
+    if (z[0] != 0x1f || z[1] != 0x8b) return bad(zsb::M_HDRCHECK);
+    if (len < 4) return -5;
+    if (z[2] != 8) return bad(zsb::M_METHOD);
+    const uint32_t flg = z[3];
+    if (flg & 0xe0) return bad(zsb::M_GZFLAGS);
+    if (len < 10) return -5;
+    h->text = flg & 1;
+    h->time = zsbzip::rd32(z + 4);
+    h->xflags = z[8];
+    h->os = z[9];
+    uint64_t p = 10;
+    if (flg & 4) {                                                  // FEXTRA: 2-byte length, then the field
+        if (len - p < 2) return -5;
+        const uint32_t xl = zsbzip::rd16(z + p);
+        p += 2;
+        if (len - p < xl) return -5;
+        h->extra_len = xl;
+        h->extra_off = xl ? (uint32_t)p : 0;
+        p += xl;
+    }
+    for (int f = 0; f < 2; f++) {                                   // FNAME, FCOMMENT: NUL-terminated
+        if (!(flg & (f ? 16 : 8))) continue;
+        const void *e = memchr(z + p, 0, (size_t)(len - p));
+        if (!e) return -5;
+        const uint64_t n = (uint64_t)((const uint8_t *)e - (z + p));
+        if (n > 0xffffffffull || p > 0xffffffffull) return ZSB_E_ARG;
+        (f ? h->comment_len : h->name_len) = (uint32_t)n;
+        (f ? h->comment_off : h->name_off) = n ? (uint32_t)p : 0;
+        p += n + 1;
+    }
+    if (flg & 2) {                                                  // FHCRC: low 16 bits of the CRC-32 of all before it
+        if (len - p < 2) return -5;
+        if (zsbzip::rd16(z + p) != (zsbgz::crc32_bytes(z, (size_t)p) & 0xffffu)) return bad(zsb::M_HCRC);
+        h->hcrc = 1;
+        p += 2;
+    }
+    if (p > 0xffffffffull) return ZSB_E_ARG;
+    h->header_len = (uint32_t)p;
+    return 0;
+}
