@@ -162,7 +162,6 @@ def main():
     ap.add_argument("--distinct", type=int, default=1024)
     ap.add_argument("--lanes", type=int, default=0, help="0 = lane path (k_lane + k_lz); else group path k_inflate<G>")
     ap.add_argument("--no-e2e", action="store_true")
-    ap.add_argument("--lead-big", type=int, default=None, help="diagnostic: leading chunks of the e2e leg through k_big")
     ap.add_argument("--small-ctas", action="store_true", help="diagnostic: device-resident leg with k_lane in small CTAs")
     ap.add_argument("--chunk-sweep", default="", help="comma list of pipeline depths to time the e2e leg with (diagnostic)")
     ap.add_argument("--no-cpu", action="store_true")
@@ -231,8 +230,6 @@ def main():
         eng.set_option("path", 0)           # the default: lane path (k_lane + k_lz)
         if args.small_ctas:
             eng.set_option("small_ctas", 1)
-        if args.lead_big is not None:
-            eng.set_option("lead_big", args.lead_big)
     lib = eng.lib
 
     def descriptors(in_base, out_base):

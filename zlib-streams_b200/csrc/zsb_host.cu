@@ -636,11 +636,6 @@ extern "C" int zsb_set_option(zsb_ctx *ctx, const char *name, long value) {
         ctx->split_big = (int)value;          // 2: every member (tests of k_big)
         return 0;
     }
-    if (!strcmp(name, "lead_big")) {          // leading chunks of a pipelined host batch through k_big (0 = none)
-        if (value < 0 || value > 16) return ZSB_E_ARG;
-        ctx->lead_big = (int)value;
-        return 0;
-    }
     if (!strcmp(name, "small_ctas")) {        // diagnostic: k_lane in the small CTAs of the pipelined host path
         ctx->force_small_ctas = value != 0;
         return 0;
@@ -959,7 +954,7 @@ static int batch_host(zsb_ctx *ctx, size_t n, const zsb_member *m, zsb_result *r
             sc.small_ctas = K > 1;
             // the chunk's plan travels with its inputs: slot order, and for the lane path the sequence offsets
             sc.nbig = 0;
-            if (ctx->path == 0 && (ctx->split_big == 2 || (c < ctx->lead_big && K >= 4 * ctx->lead_big))) sc.nbig = ch.count;
+            if (ctx->path == 0 && ctx->split_big == 2) sc.nbig = ch.count;
             else if (ctx->path == 0 && ctx->split_big && K == 1) sc.nbig = split_big(hmc, hoc, ch.count, dv.sm_count);
             else if (ctx->path == 0 && ctx->split_big)          // hoc is largest first: the prefix at or above the shard's threshold
                 while (sc.nbig < ch.count && (double)hmc[hoc[sc.nbig]].in_len + (double)hmc[hoc[sc.nbig]].out_cap >= big_threshold) sc.nbig++;

@@ -48,7 +48,6 @@ struct zsb_ctx {
     int chunks = 0;                    // host batches: pipeline depth (0 = choose from the batch)
     long launches = 0;
     bool force_small_ctas = false;
-    int lead_big = 0;                  // pipelined host batches: this many leading chunks decode in k_big (first output sooner)
     int split_big = 1;                 // path 0: 1 = members far larger than the rest get a warp each (k_big,
                                        // split_big()), 0 = never, 2 = every member (tests)
     int profile = 0;                   // 1: record per-kernel events (zsb_profile_read)
