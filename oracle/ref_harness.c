@@ -46,6 +46,26 @@ int ref_oneshot(const uint8_t *in, size_t in_len, uint8_t *out, size_t out_cap, 
     return ret;
 }
 
+/* inflateCodesUsed() (reference src/inflate.c:1532) after a one-shot decode: the number of table entries the
+ * reference's inflate_table() allocated for the last block's codes.  Test hook for the table-space limits
+ * (src/inftrees.c:211-228,295-297). */
+long ref_codes_used(const uint8_t *in, size_t in_len, int wbits, orc_result *r) {
+    z_stream s;
+    static uint8_t sink[1024];
+    memset(&s, 0, sizeof s);
+    int ret = inflateInit2_(&s, wbits, ZLIB_VERSION, (int)sizeof(z_stream));
+    if (ret != Z_OK) return -1;
+    s.next_in = (Bytef *)in;
+    s.avail_in = (uInt)in_len;
+    s.next_out = sink;
+    s.avail_out = sizeof sink;
+    ret = inflate(&s, Z_FINISH);
+    if (r) fill_result(&s, ret, r);
+    long used = (long)inflateCodesUsed(&s);
+    inflateEnd(&s);
+    return used;
+}
+
 void *ref_open(int wbits, int *init_ret) {
     z_stream *s = (z_stream *)calloc(1, sizeof(z_stream));
     int ret = inflateInit2_(s, wbits, ZLIB_VERSION, (int)sizeof(z_stream));

@@ -61,6 +61,18 @@ def probe_vectors():
     st = gen.deflate(random.Random(5).randbytes(70000), 0, -15)
     v.append(("stored_70000_deflate", st, -15, 80000, (1, 0, 70010, 70000)))
     v.append(("stored_70000_d64", st, -16, 80000, (1, 0, 70010, 70000)))
+    # code sets at the reference's table-space limits (SURVEY.md §8 a6'(ii); tests/tablespace.py): a literal/length
+    # set needing exactly 852 entries and a 32-symbol distance set needing 594 are rejected by Deflate64 mode only
+    # (src/inftrees.c:211-212,226-228,295-297); results as the compiled reference gave them
+    import tablespace
+    want = {("286sym_root9_852", -15): (1, 0, 37, 0), ("286sym_root9_852", -16): (-3, 12, 35, 0),
+            ("286sym_root9_850", -15): (1, 0, 39, 0), ("286sym_root9_850", -16): (1, 0, 39, 0),
+            ("30sym_root6_592", -15): (1, 0, 23, 0), ("30sym_root6_592", -16): (1, 0, 23, 0),
+            ("32sym_root6_592", -15): (-3, 8, 3, 0), ("32sym_root6_592", -16): (1, 0, 23, 0),
+            ("32sym_root6_594", -15): (-3, 8, 3, 0), ("32sym_root6_594", -16): (-3, 13, 23, 0)}
+    for name, data, wb, cap in tablespace.probe_cases():
+        key = name[len("tabspace_"):name.rindex("_wb")]
+        v.append((name, data, wb, cap, want[(key, wb)]))
     return v
 
 

@@ -228,7 +228,8 @@ extern "C" int emulzs_step(void *hh, const uint8_t *in, size_t in_len_new, uint8
     std::vector<lane::seq_t> seq(bound + 2);
     uint32_t ring[lane::RING_WORDS] = {0, 0, 0, 0};
     alignas(16) static uint32_t big_lut[lane::BIG_LUT_BYTES / 4];
-    zs::stream_decode<1>(z->S, ib, len, (uint32_t)out_cap, seq.data(), fixed, scr, ring, lut, 0, big_lut);
+    zs::stream_decode<1>(z->S, ib, len, (uint32_t)out_cap, seq.data(), fixed, scr, ring, lut, 0, big_lut,
+                         flush == 5 ? zs::FL_BLOCK : flush == 6 ? zs::FL_TREES : zs::FL_NONE);
     if (z->S.call.nseq > bound) abort();
     if (z->S.call.nseq) lz::resolve_member<1>(w + zs::HIST, ib, seq.data(), z->S.call.nseq, 0);
     const uint32_t prod = z->S.call.produced;

@@ -55,6 +55,14 @@ class Checker:
                                 ctypes.POINTER(ctypes.c_uint64), ctypes.POINTER(ctypes.c_uint64)]
         self._bench.restype = ctypes.c_double
 
+    def codes_used(self, data, wbits):
+        """(reference build only) inflateCodesUsed() after a one-shot decode -> (entries, Result)."""
+        f = self.lib.ref_codes_used
+        f.argtypes = [ctypes.c_char_p, ctypes.c_size_t, ctypes.c_int, ctypes.POINTER(Result)]
+        f.restype = ctypes.c_long
+        r = Result()
+        return f(data, len(data), wbits, ctypes.byref(r)), r
+
     def oneshot(self, data, out_cap, wbits):
         """inflateInit2(wbits) + inflate(Z_FINISH) + inflateEnd -> (Result, output bytes)."""
         buf = ctypes.create_string_buffer(max(out_cap, 1))
@@ -69,9 +77,9 @@ class Checker:
             self._close(h)
         return rc.value
 
-    def stream(self, data, wbits, in_chunks, out_cap, finish=True, max_calls=1000000):
+    def stream(self, data, wbits, in_chunks, out_cap, finish=True, max_calls=1000000, flush=Z_NO_FLUSH):
         """Feed `data` in the given input chunk sizes (cycled) with an `out_cap`-byte rolling output
-        buffer, Z_NO_FLUSH while input remains, then Z_FINISH; returns the per-call trace
+        buffer, `flush` (Z_NO_FLUSH, or Z_BLOCK / Z_TREES) while input remains, then Z_FINISH; returns the per-call trace
         [(ret,msg,total_in,total_out,adler,data_type,consumed,produced)...] and the output."""
         rc = ctypes.c_int()
         h = self._open(wbits, ctypes.byref(rc))
@@ -89,8 +97,8 @@ class Checker:
                     k += 1
                     pending = data[pos:pos + n]
                     pos += len(pending)
-                flush = Z_FINISH if (finish and pos >= len(data)) else Z_NO_FLUSH
-                ret = self._step(h, pending, len(pending), buf, out_cap, flush,
+                fl = Z_FINISH if (finish and pos >= len(data)) else flush
+                ret = self._step(h, pending, len(pending), buf, out_cap, fl,
                                  ctypes.byref(c), ctypes.byref(p), ctypes.byref(r))
                 out += buf.raw[:p.value]
                 trace.append(r.astuple() + (c.value, p.value))

@@ -42,9 +42,9 @@ def pool():
     return p
 
 
-def compare(name, data, wb, chunks, ocap, finish=True):
-    ta, oa = CHK.stream(data, wb, chunks, ocap, finish, max_calls=400000)
-    tb, ob = EM.stream(data, wb, chunks, ocap, finish, max_calls=400000)
+def compare(name, data, wb, chunks, ocap, finish=True, flush=0):
+    ta, oa = CHK.stream(data, wb, chunks, ocap, finish, max_calls=400000, flush=flush)
+    tb, ob = EM.stream(data, wb, chunks, ocap, finish, max_calls=400000, flush=flush)
     if ta != tb:
         k = next((i for i, (x, y) in enumerate(zip(ta, tb)) if x != y), min(len(ta), len(tb)))
         raise AssertionError((name, wb, chunks, ocap, "call", k, ta[k - 1:k + 1], tb[k - 1:k + 1]))
@@ -72,3 +72,22 @@ def test_stream_byte_at_a_time():
         if len(data) <= 20000:
             compare(name, data, wb, [1], 1)
             compare(name, data, wb, [1], 70000)
+
+
+def test_stream_block_and_trees_flush():
+    """inflate(Z_BLOCK) / inflate(Z_TREES): the early returns at block boundaries and header ends and the
+    128 / 256 bits of data_type (reference src/inflate.c:832,854-857,883,1032,1269-1271), call by call."""
+    rnd = random.Random(56)
+    stops = {5: 0, 6: 0}
+    for name, data, wb, plain in pool()[::3]:
+        for flush in (5, 6):
+            chunks = [rnd.choice([1, 3, 64, 1000, 32768, 1 << 20]) for _ in range(4)]
+            ocap = rnd.choice([5, 300, 65536, 1 << 20])
+            compare(name, data, wb, chunks, ocap, finish=rnd.random() < 0.5, flush=flush)
+    # the fixtures whole: every block boundary is a stop
+    for name, data, m in cases.golden_fixtures():
+        for flush in (5, 6):
+            compare(name, data, -16, [len(data)], m["out_len"] + 10, finish=False, flush=flush)
+            t, _ = EM.stream(data, -16, [len(data)], m["out_len"] + 10, finish=False, flush=flush)
+            stops[flush] += sum(1 for c in t if c[0] == 0 and (c[5] & 0x180))
+    assert stops[5] > 10 and stops[6] > stops[5]

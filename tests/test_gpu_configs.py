@@ -1,12 +1,12 @@
-"""BASELINE.json configs C3, C4, C5 at their full member counts on the GPU: every member's
-result record and output bytes are compared with the oracle's for its distinct member (tests/config_runner.py).
+"""BASELINE.json configs C2, C3, C4, C5 at their full member counts on the GPU: every member's
+result record and output bytes are compared with the oracle's for its distinct member (tests/batchlib.py).
 The default engine path is used: lane path, members handed out largest first, members far larger than the
-rest of their batch decoded by k_big (a warp each); C4 also runs without that split."""
+rest of their batch decoded by the large-member path; C4 also runs without that split."""
 import os
 
 import pytest
 
-import config_runner
+import batchlib
 import workloads
 import zsblib
 
@@ -14,20 +14,40 @@ pytestmark = pytest.mark.gpu
 SCALE = os.environ.get("ZSB_CONFIG_SCALE", "full")      # "small" shrinks the batches 16x for quick runs
 
 
-def _run(w, split=True):
+def _run(w, split=True, options=()):
+    import torch
     eng = zsblib.Zsb(devices=[0])
     eng.set_option("split_big", 1 if split else 0)
+    for k, v in options:
+        eng.set_option(k, v)
     try:
-        r = config_runner.run(w, eng, steps=1, warmup=1)
+        dev = torch.device("cuda", 0)
+        b = batchlib.DeviceBatch(w, dev).to_device()
+        st = torch.cuda.current_stream(dev)
+        b.step(eng, st)
+        torch.cuda.synchronize(dev)
+        b.clear_outputs()
+        b.step(eng, st)
+        torch.cuda.synchronize(dev)
+        launches = eng.lib.zsb_last_launches(eng.ctx)
+        bad = b.verify()
+        non_ok = int((b.rec["ret"][b.d] != 1).sum())
     finally:
         eng.close()
-    assert not r["mismatches"], r["mismatches"]
-    assert r["gpu_launches_per_step"] >= 2
-    return r
+    assert not bad, bad
+    assert launches >= 2
+    return {"gpu_launches_per_step": int(launches), "non_ok_members": non_ok, "members": b.n}
+
+
+def test_c2_64kib_raw_deflate_members():
+    """The headline configuration: 65,536 x 64 KiB level-6 raw-deflate members, 1,024 distinct."""
+    w = workloads.c2(distinct=1024, tiles=64 if SCALE == "full" else 4)
+    r = _run(w)
+    assert r["non_ok_members"] == 0 and r["members"] == 1024 * w["tiles"]
 
 
 def test_c3_deflate64_4mib_members():
-    w = workloads.c3(distinct=8, tiles=512 if SCALE == "full" else 32)
+    w = workloads.c3(distinct=64 if SCALE == "full" else 8, tiles=64 if SCALE == "full" else 4)
     r = _run(w)
     assert r["non_ok_members"] == 0
 
@@ -38,15 +58,15 @@ def test_c4_wrapped_mixed_sizes_with_checksums():
     assert r["non_ok_members"] > 0          # the damaged ~1 % report the oracle's error codes
 
 
-def test_c4_large_members_get_a_warp_each():
+def test_c4_large_members_get_their_own_path():
     w = workloads.c4(distinct=512, tiles=2)
     r = _run(w, split=True)
-    assert r["gpu_launches_per_step"] >= 4   # k_big beside k_lane + k_lz, then k_check
+    assert r["gpu_launches_per_step"] >= 4   # the large-member kernels beside k_lane + k_lz, then k_check
     r = _run(w, split=False)
     assert r["gpu_launches_per_step"] == 3
 
 
 def test_c5_zip_like_mix():
-    w = workloads.c5(distinct=2048, tiles=512 if SCALE == "full" else 32)
+    w = workloads.c5(distinct=8192 if SCALE == "full" else 512, tiles=128 if SCALE == "full" else 64)
     r = _run(w)
     assert r["non_ok_members"] == 0

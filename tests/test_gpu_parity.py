@@ -271,6 +271,46 @@ def test_host_batch_pipelined(eng):
         eng.set_option("chunks", 0)
 
 
+def test_host_batch_member_bound_above_the_arena_option(eng):
+    """A member whose own sequence bound exceeds "seq_arena_bytes" (the option's minimum, 4096 bytes) through the
+    pipelined host path: its stream's region must still hold it (round-1 advisor finding: sequences were written
+    past the region).  Incompressible 64 KiB members write close to their bound."""
+    import random
+    rnd = random.Random(77)
+    items = []
+    for i in range(24):
+        plain = rnd.randbytes(65536) if i % 2 else zsblib_gen().word_soup(65536, 900 + i)
+        items.append(("arena%d" % i, zsblib_gen().deflate(plain, 6 if i % 4 else 1, -15), -15, 65536))
+    arena = eng.get_option("seq_arena_bytes")
+    try:
+        eng.set_option("seq_arena_bytes", 4096)
+        for k in (1, 4):
+            eng.set_option("chunks", k)
+            run_cases(eng, 0, items)
+    finally:
+        eng.set_option("seq_arena_bytes", arena)
+        eng.set_option("chunks", 0)
+
+
+def test_zstream_block_and_trees_flush():
+    """inflate(strm, Z_BLOCK) / inflate(strm, Z_TREES): the early returns and the 128 / 256 bits of data_type
+    (reference src/inflate.c:832,854-857,883,1032,1269-1271), call by call against the oracle."""
+    import random
+    api = zsblib.ZStreamApi()
+    rnd = random.Random(56)
+    stops = 0
+    pool = [(n, d, w) for n, d, w, p in cases.valid_streams()[2::9]] + [(n, d, -16) for n, d, m in cases.golden_fixtures()]
+    for name, data, wb in pool:
+        for flush in (5, 6):
+            chunks = [len(data)] if rnd.random() < 0.5 else [rnd.choice([3, 64, 1000, 32768]) for _ in range(3)]
+            ocap = rnd.choice([300, 65536, 1 << 20])
+            ta, oa = CHK.stream(data, wb, chunks, ocap, False, max_calls=100000, flush=flush)
+            tb, ob = api.stream(data, wb, chunks, ocap, False, max_calls=100000, flush=flush)
+            assert ta == tb and oa == ob, (name, wb, flush, chunks, ocap)
+            stops += sum(1 for c in tb if c[0] == 0 and (c[5] & 0x180))
+    assert stops > 20
+
+
 def test_pipelined_uniform_batch_stays_on_the_lane_path(eng):
     """The chunks of a pipelined host batch overlap, so large members are chosen for the batch as a whole: a
     uniform batch must not send whole chunks to k_big (that serialised the pipeline once: 96 -> 186 ms on C2)."""
@@ -305,5 +345,25 @@ def test_one_context_over_all_gpus_of_the_box():
             e.set_option("chunks", chunks)
             run_cases(e, 0, items * 4)
             run_cases(e, "big", items)
+        # members already resident in the HBM of different GPUs: each is decoded by the device that owns it
+        select(e, 0)
+        e.set_option("path", 0)
+        e.set_option("split_big", 1)
+        keep, mem = [], (zsblib.Member * len(items))()
+        for i, (name, data, wb, cap) in enumerate(items):
+            dv = torch.device("cuda", i % ndev)
+            ti = torch.frombuffer(bytearray(data) or bytearray(1), dtype=torch.uint8).to(dv)
+            to = torch.zeros(max(cap, 1), dtype=torch.uint8, device=dv)
+            keep.append((ti, to))
+            mem[i].inp, mem[i].in_len, mem[i].out, mem[i].out_cap = ti.data_ptr(), len(data), to.data_ptr(), cap
+            mem[i].window_bits, mem[i].flags = wb, 0
+        res = (zsblib.Result * len(items))()
+        torch.cuda.synchronize()
+        rc = e.lib.zsb_inflate_batch(e.ctx, len(items), mem, res)
+        assert rc == 0, e.error()
+        for i, (name, data, wb, cap) in enumerate(items):
+            a, ao = CHK.oneshot(data, cap, wb)
+            assert a.astuple() == res[i].astuple(), (name, a, res[i])
+            assert keep[i][1][:a.total_out].cpu().numpy().tobytes() == ao, name
     finally:
         e.close()

@@ -46,6 +46,21 @@ def log_uniform(rnd, lo, hi):
 
 
 # ---------------------------------------------------------------------------------------------------
+# C2: 64 KiB word-soup members, raw deflate, zlib level 6 (the headline configuration)
+# ---------------------------------------------------------------------------------------------------
+def _c2_member(seed):
+    plain = gen.word_soup(65536, seed)
+    return gen.deflate(plain, 6, -15), -15, plain
+
+
+def c2(distinct=1024, tiles=64, seed_base=1000):
+    with ProcessPoolExecutor(min(os.cpu_count() or 1, 32)) as ex:
+        mem = list(ex.map(_c2_member, [seed_base + i for i in range(distinct)], chunksize=16))
+    return {"name": "C2", "desc": "%d x 64 KiB synthetic raw-deflate (zlib level 6, word-soup) members" % (distinct * tiles),
+            "distinct": mem, "tiles": tiles}
+
+
+# ---------------------------------------------------------------------------------------------------
 # C3: Deflate64 members with a 64 KiB window and long matches (tests/d64enc.py, the test-only encoder)
 # ---------------------------------------------------------------------------------------------------
 def _c3_member(args):
@@ -147,4 +162,4 @@ def c5(distinct=2048, tiles=512, lo=1024, hi=256 << 10):
         distinct * tiles, lo, hi >> 10), "distinct": mem, "tiles": tiles}
 
 
-BUILDERS = {"C3": c3, "C4": c4, "C5": c5}
+BUILDERS = {"C2": c2, "C3": c3, "C4": c4, "C5": c5}

@@ -245,8 +245,9 @@ class ZStreamApi:
             self.lib.inflateEnd(ctypes.byref(s))
         return rc
 
-    def stream(self, data, wbits, in_chunks, out_cap, finish=True, max_calls=1000000):
+    def stream(self, data, wbits, in_chunks, out_cap, finish=True, max_calls=1000000, flush=0):
         """Same driver and trace format as orclib.Checker.stream()."""
+        mid_flush = flush
         s = ZStreamStruct()
         rc = self.lib.inflateInit2_(ctypes.byref(s), wbits, b"1.3", ctypes.sizeof(s))
         if rc != 0:
@@ -262,7 +263,7 @@ class ZStreamApi:
                     k += 1
                     pending = data[pos:pos + n]
                     pos += len(pending)
-                flush = 4 if (finish and pos >= len(data)) else 0
+                flush = 4 if (finish and pos >= len(data)) else mid_flush
                 ibuf = ctypes.create_string_buffer(pending, max(len(pending), 1))
                 s.next_in = ctypes.addressof(ibuf)
                 s.avail_in = len(pending)

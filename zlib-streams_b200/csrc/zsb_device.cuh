@@ -19,7 +19,8 @@ namespace zsb {
 
 // ---- events produced by the decoder leader lane ----
 enum : int { EV_NONE = 0, EV_MATCH = 1, EV_EOB = 2, EV_ERR = 3, EV_STARVE = 4, EV_OUTFULL = 5,
-             EV_DONE = 6, EV_NEEDDICT = 7, EV_INITERR = 8, EV_LIT = 9 };
+             EV_DONE = 6, EV_NEEDDICT = 7, EV_INITERR = 8, EV_LIT = 9,
+             EV_BLOCKSTOP = 10 };    // z_stream surface only: inflate(Z_BLOCK / Z_TREES) left at a block boundary / header end
 
 // ---- message ids (index into zsb_message(); same order as the reference's strm->msg strings) ----
 enum : int { M_HDRCHECK = 1, M_METHOD = 2, M_WINDOW = 3, M_GZFLAGS = 4, M_HCRC = 5, M_BTYPE = 6,
@@ -890,6 +891,14 @@ ZSB_DEV void write_result(const Dec &d, const Mem &mm, int ev, zsb_result *res, 
         if (mm.hdr_stop) { tin = mm.hdr_tin; bits = mm.hdr_bits; }
         else { tin = b.len; bits = b.nbits; extra128 = d.at_type ? 128 : 0; }
         break;
+    case EV_BLOCKSTOP: {                       // src/inflate.c:832,854-857,883,1032: Z_OK with the bits held back
+        r.ret = 0;
+        const uint64_t bp = bi_bitpos(b);
+        tin = (uint32_t)((bp + 7) >> 3);
+        bits = (uint32_t)(8ull * tin - bp);
+        extra128 = d.at_type ? 128 : 256;      // mode TYPE, or LEN_ / COPY_ (src/inflate.c:1269-1271)
+        break;
+    }
     default:                                   // EV_OUTFULL
         r.ret = -5;
         break;

@@ -248,7 +248,7 @@ static uint64_t lane_plan(const zsb_member *hm, const uint32_t *horder, size_t n
 }
 
 // Most sequence scratch a batch may hold at once: option "seq_arena_bytes", or (0, the default) half of what
-// the device has free, at least 32 GiB: the worst-case bound of seq_bound is ~3x what members write, and every
+// the device has free: the worst-case bound of seq_bound is ~3x what members write, and every
 // extra slice of a batch of mixed sizes ends with its own tail (C4: 1.76 s in four slices, 1.27 s in one).
 // (cudaMemGetInfo costs milliseconds, so the answer is kept until a batch would not fit it.)
 static size_t arena_bytes(const zsb_ctx *ctx, zsb_dev &dv, bool refresh = false) {
@@ -259,7 +259,8 @@ static size_t arena_bytes(const zsb_ctx *ctx, zsb_dev &dv, bool refresh = false)
             cudaGetLastError();
             fr = 0;
         }
-        dv.arena_auto = std::max<size_t>((size_t)32 << 30, (fr + dv.d_seq_cap) / 2);
+        // half of what is free (our own arena counts as free); when the query fails, a modest 4 GiB
+        dv.arena_auto = fr ? std::max<size_t>((size_t)64 << 20, (fr + dv.d_seq_cap) / 2) : ((size_t)4 << 30);
     }
     return dv.arena_auto;
 }
@@ -446,7 +447,32 @@ static int run_device(zsb_ctx *ctx, zsb_dev &dv, size_t n, const zsb_member *dm,
             if (!sc && cuts_own.size() > 2 && !ctx->seq_arena_bytes)      // sliced: is more memory free by now?
                 need = plan_parts(hm, horder, n, nbig, arena_bytes(ctx, dv, true) / sizeof(lane::seq_t), off_own.data(),
                                   cuts_big_own, cuts_own, big_seqs);
-            if (!sc && (rc = grow(ctx, dv.d_seq, dv.d_seq_cap, (size_t)need * sizeof(lane::seq_t)))) return rc;
+            if (!sc) {
+                // the arena: when the device cannot give it (another process took the memory since the last query),
+                // decode in more slices of half the size rather than fail
+                uint64_t arena = (uint64_t)arena_bytes(ctx, dv) / sizeof(lane::seq_t);
+                for (;;) {
+                    if ((size_t)need * sizeof(lane::seq_t) <= dv.d_seq_cap) break;
+                    if (dv.d_seq) CK(ctx, cudaFree(dv.d_seq));
+                    dv.d_seq = nullptr;
+                    dv.d_seq_cap = 0;
+                    const size_t want = (size_t)need * sizeof(lane::seq_t) + (size_t)need + 4096;
+                    if (cudaMalloc(&dv.d_seq, want) == cudaSuccess) {
+                        dv.d_seq_cap = want;
+                        break;
+                    }
+                    cudaGetLastError();
+                    uint64_t largest = 0;
+                    for (size_t s = nbig; s < n; s++) largest = std::max(largest, seq_bound(hm[horder[s]]));
+                    if (arena <= largest || ctx->seq_arena_bytes) {
+                        snprintf(ctx->err, sizeof ctx->err, "out of device memory for %zu bytes of sequence scratch", want);
+                        return ZSB_E_CUDA;
+                    }
+                    arena = std::max(largest, std::min(arena, need) / 2);
+                    dv.arena_auto = (size_t)arena * sizeof(lane::seq_t);
+                    need = plan_parts(hm, horder, n, nbig, arena, off_own.data(), cuts_big_own, cuts_own, big_seqs);
+                }
+            }
             // (a pageable source is staged by the runtime before cudaMemcpyAsync returns, so off_own may go)
             CK(ctx, cudaMemcpyAsync(dseqoff, off_own.data(), n * sizeof(uint64_t), cudaMemcpyHostToDevice, st));
         }
@@ -695,6 +721,16 @@ extern "C" int zsb_inflate_batch_device(zsb_ctx *ctx, int dev_index, size_t n, c
     int cur = 0;
     cudaGetDevice(&cur);
     if (cur != dv.device) CK(ctx, cudaSetDevice(dv.device));
+    // what the other batch paths check: sizes the 32-bit decoders cannot hold are an argument error here (the
+    // device descriptors are the caller's, so they cannot be rewritten to answer Z_STREAM_ERROR per member), and
+    // any member that asks for a copy or a CRC (ZSB_M_*) needs k_check whatever the caller said about wrappers
+    for (size_t i = 0; i < n; i++) {
+        if (h_members[i].in_len > 0xfffffff0ull || h_members[i].out_cap > 0xfffffff0ull) {
+            snprintf(ctx->err, sizeof ctx->err, "member %zu: in_len / out_cap above 0xfffffff0", i);
+            return ZSB_E_ARG;
+        }
+        if (h_members[i].flags) flags = (flags & ~ZSB_RAW_ONLY) | ZSB_HAS_WRAPPED;
+    }
     ctx->launches = 0;
     int rc = run_device(ctx, dv, n, d_members, d_results, h_members, h_order, flags, (cudaStream_t)cuda_stream);
     if (cur != dv.device) cudaSetDevice(cur);
@@ -831,9 +867,15 @@ static int batch_host(zsb_ctx *ctx, size_t n, const zsb_member *m, zsb_result *r
             ch.out_base = out_total;
             in_total += (layout_runs(m, ch.idx, false, 4095, ch.in_off, ch.in_runs) + 511) & ~(size_t)255;
             out_total += (layout_runs(m, ch.idx, true, 0, ch.out_off, ch.out_runs) + 511) & ~(size_t)255;
-            uint64_t sq = 0;
-            for (uint32_t i : ch.idx) sq += seq_bound(m[i]);
-            seq_need[c] = std::min<uint64_t>(sq, arena_seqs);
+            // a region holds the chunk's whole bound, or (sliced by plan_parts) the arena option — but never less than
+            // the largest single member's bound: lane_plan places such a member alone in a slice at offset 0
+            uint64_t sq = 0, largest = 0;
+            for (uint32_t i : ch.idx) {
+                const uint64_t b = seq_bound(m[i]);
+                sq += b;
+                largest = std::max(largest, b);
+            }
+            seq_need[c] = std::max(std::min<uint64_t>(sq, arena_seqs), largest);
         }
         // Chunk c decodes on stream c % NS with sequence region c % NS; the regions together stay inside
         // the arena (fewer streams if they would not).
@@ -844,7 +886,7 @@ static int batch_host(zsb_ctx *ctx, size_t n, const zsb_member *m, zsb_result *r
             for (int c = 0; c < K; c++) region[c % NS] = std::max(region[c % NS], seq_need[c]);
             uint64_t sum = 0;
             for (uint64_t v : region) sum += v;
-            if (sum <= arena_seqs || NS == 1) break;
+            if (sum <= std::max<uint64_t>(arena_seqs, region[0]) || NS == 1) break;
         }
         std::vector<uint64_t> region_off(NS, 0);
         uint64_t seq_total = 0;
@@ -1009,32 +1051,130 @@ static int batch_host(zsb_ctx *ctx, size_t n, const zsb_member *m, zsb_result *r
     return 0;
 }
 
-static int batch_device_ptrs(zsb_ctx *ctx, size_t n, const zsb_member *m, zsb_result *r) {
-    zsb_dev &dv = ctx->devs[0];
-    CK(ctx, cudaSetDevice(dv.device));
-    int rc;
-    const size_t desc_bytes = n * (sizeof(zsb_member) + sizeof(zsb_result) + sizeof(uint32_t)) + 64;
-    if ((rc = grow(ctx, dv.d_desc, dv.d_desc_cap, desc_bytes))) return rc;
-    zsb_member *dm = (zsb_member *)dv.d_desc;
-    zsb_result *dr = (zsb_result *)(dm + n);
-    std::vector<uint32_t> ord(n);
-    bool raw_only = true;
-    for (size_t i = 0; i < n; i++) {
-        ord[i] = (uint32_t)i;
-        raw_only &= m[i].window_bits < 0 && m[i].flags == 0;
+// Which CUDA device owns a device pointer, answered from a cache of allocation ranges: members of a batch live
+// in a few large allocations, so one runtime query per allocation serves a million members.  The range comes from
+// the driver's cuMemGetAddressRange, reached through the runtime (cudaGetDriverEntryPoint): libzsb.so does not
+// link libcuda, so it still loads where no driver is installed (the CPU-only test tier).
+struct PtrOwner {
+    struct Range { uintptr_t lo, hi; int device; };
+    std::vector<Range> ranges;
+    size_t last = 0;
+    typedef int (*range_fn)(unsigned long long *, size_t *, unsigned long long);
+    range_fn get_range = nullptr;
+    bool looked = false;
+    // -1: not a device pointer
+    int device_of(const void *p) {
+        const uintptr_t a = (uintptr_t)p;
+        if (last < ranges.size() && a >= ranges[last].lo && a < ranges[last].hi) return ranges[last].device;
+        for (size_t k = 0; k < ranges.size(); k++)
+            if (a >= ranges[k].lo && a < ranges[k].hi) {
+                last = k;
+                return ranges[k].device;
+            }
+        cudaPointerAttributes at;
+        if (cudaPointerGetAttributes(&at, p) != cudaSuccess) {
+            cudaGetLastError();
+            return -1;
+        }
+        if (at.type != cudaMemoryTypeDevice && at.type != cudaMemoryTypeManaged) return -1;
+        if (!looked) {
+            looked = true;
+            void *fn = nullptr;
+            cudaDriverEntryPointQueryResult qr;
+            if (cudaGetDriverEntryPoint("cuMemGetAddressRange", &fn, cudaEnableDefault, &qr) == cudaSuccess && fn &&
+                qr == cudaDriverEntryPointSuccess)
+                get_range = (range_fn)fn;
+            else
+                cudaGetLastError();
+        }
+        Range r{a, a + 1, at.device};
+        unsigned long long base = 0;
+        size_t size = 0;
+        if (get_range && get_range(&base, &size, (unsigned long long)a) == 0 && size) {
+            r.lo = (uintptr_t)base;
+            r.hi = (uintptr_t)base + size;
+        }
+        ranges.push_back(r);
+        last = ranges.size() - 1;
+        return r.device;
     }
-    std::stable_sort(ord.begin(), ord.end(), [&](uint32_t a, uint32_t b) {
-        return m[a].in_len + m[a].out_cap > m[b].in_len + m[b].out_cap;
-    });
-    std::vector<zsb_member> mm(m, m + n);
-    for (auto &x : mm)
-        if (x.in_len > 0xfffffff0ull || x.out_cap > 0xfffffff0ull) x.window_bits = 1000;
-    cudaStream_t st = dv.stream;
-    CK(ctx, cudaMemcpyAsync(dm, mm.data(), n * sizeof(zsb_member), cudaMemcpyHostToDevice, st));
+};
+
+// Members whose buffers are already in HBM, on ANY device of the context ("inputs are placed directly
+// in the owning GPU's HBM; outputs stay there"): every member is decoded by the device that owns its buffers, all
+// devices are enqueued before any is drained, results return in the caller's order.  A member on a device the
+// context does not hold is an argument error.
+static int batch_device_ptrs(zsb_ctx *ctx, size_t n, const zsb_member *m, zsb_result *r) {
+    const int nd = (int)ctx->devs.size();
+    PtrOwner owner;
+    std::vector<int> dev_index_of;                   // CUDA ordinal -> index in ctx->devs
+    for (int s = 0; s < nd; s++) {
+        if ((int)dev_index_of.size() <= ctx->devs[s].device) dev_index_of.resize(ctx->devs[s].device + 1, -1);
+        dev_index_of[ctx->devs[s].device] = s;
+    }
+    std::vector<std::vector<uint32_t>> part(nd);
+    for (size_t i = 0; i < n; i++) {
+        const void *p = m[i].in ? m[i].in : m[i].out;
+        int s = 0;
+        if (p) {
+            const int d = owner.device_of(p);
+            s = (d >= 0 && d < (int)dev_index_of.size()) ? dev_index_of[d] : -1;
+            if (s < 0) {
+                snprintf(ctx->err, sizeof ctx->err, "member %zu: its buffers are not in the memory of a device of this context", i);
+                return ZSB_E_ARG;
+            }
+        }
+        part[s].push_back((uint32_t)i);
+    }
     ctx->launches = 0;
-    if ((rc = run_device(ctx, dv, n, dm, dr, mm.data(), ord.data(), raw_only ? ZSB_RAW_ONLY : ZSB_HAS_WRAPPED, st))) return rc;
-    CK(ctx, cudaMemcpyAsync(r, dr, n * sizeof(zsb_result), cudaMemcpyDeviceToHost, st));
-    CK(ctx, cudaStreamSynchronize(st));
+    // (results come back through the device's pinned descriptor buffer: a copy to pageable memory would block the
+    // host until the device has finished, and the devices would run one after the other)
+    struct Pending { std::vector<zsb_member> mm; std::vector<uint32_t> ord; zsb_result *hr = nullptr; };
+    std::vector<Pending> pend(nd);
+    for (int s = 0; s < nd; s++) {
+        const size_t k = part[s].size();
+        if (!k) continue;
+        zsb_dev &dv = ctx->devs[s];
+        CK(ctx, cudaSetDevice(dv.device));
+        int rc;
+        const size_t desc_bytes = k * (sizeof(zsb_member) + sizeof(zsb_result) + sizeof(uint32_t)) + 64;
+        if ((rc = grow(ctx, dv.d_desc, dv.d_desc_cap, desc_bytes))) return rc;
+        zsb_member *dm = (zsb_member *)dv.d_desc;
+        zsb_result *dr = (zsb_result *)(dm + k);
+        Pending &P = pend[s];
+        P.mm.resize(k);
+        P.ord.resize(k);
+        if (k * sizeof(zsb_result) > dv.h_desc_cap) {
+            if (dv.h_desc) CK(ctx, cudaFreeHost(dv.h_desc));
+            dv.h_desc = nullptr;
+            dv.h_desc_cap = 0;
+            const size_t want = k * sizeof(zsb_result) + k * sizeof(zsb_result) / 8 + 4096;
+            CK(ctx, cudaHostAlloc(&dv.h_desc, want, cudaHostAllocDefault));
+            dv.h_desc_cap = want;
+        }
+        P.hr = (zsb_result *)dv.h_desc;
+        bool raw_only = true;
+        for (size_t j = 0; j < k; j++) {
+            P.mm[j] = m[part[s][j]];
+            P.ord[j] = (uint32_t)j;
+            raw_only &= P.mm[j].window_bits < 0 && P.mm[j].flags == 0;
+            if (P.mm[j].in_len > 0xfffffff0ull || P.mm[j].out_cap > 0xfffffff0ull) P.mm[j].window_bits = 1000;   // -> Z_STREAM_ERROR
+        }
+        std::stable_sort(P.ord.begin(), P.ord.end(), [&](uint32_t a, uint32_t b) {
+            return P.mm[a].in_len + P.mm[a].out_cap > P.mm[b].in_len + P.mm[b].out_cap;
+        });
+        cudaStream_t st = dv.stream;
+        CK(ctx, cudaMemcpyAsync(dm, P.mm.data(), k * sizeof(zsb_member), cudaMemcpyHostToDevice, st));
+        if ((rc = run_device(ctx, dv, k, dm, dr, P.mm.data(), P.ord.data(), raw_only ? ZSB_RAW_ONLY : ZSB_HAS_WRAPPED, st))) return rc;
+        CK(ctx, cudaMemcpyAsync(P.hr, dr, k * sizeof(zsb_result), cudaMemcpyDeviceToHost, st));
+    }
+    for (int s = 0; s < nd; s++) {
+        const size_t k = part[s].size();
+        if (!k) continue;
+        CK(ctx, cudaSetDevice(ctx->devs[s].device));
+        CK(ctx, cudaStreamSynchronize(ctx->devs[s].stream));
+        for (size_t j = 0; j < k; j++) r[part[s][j]] = pend[s].hr[j];
+    }
     return 0;
 }
 

@@ -63,7 +63,10 @@ struct Run {               // lane 0's bookkeeping during one call
     bool hdr_stop;
     uint32_t hdr_tin, hdr_bits;
     const uint32_t *big_lut;   // direct tables of the current block (lane::big_build), or NULL
+    uint32_t flush_mode;       // 0, FL_BLOCK (inflate(Z_BLOCK)) or FL_TREES (inflate(Z_TREES))
 };
+// inflate()'s flush values that add early returns (reference src/inflate.c:832,854-857,883,1032)
+enum : uint32_t { FL_NONE = 0, FL_BLOCK = 1, FL_TREES = 2 };
 
 ZSB_DEV uint64_t bitpos(const BitIn &b) { return 8ull * b.next - b.nbits; }
 
@@ -108,6 +111,12 @@ ZSB_DEV int run_serial(State &S, Lane &L, Run &R, uint8_t *T, const uint32_t *lu
         case PH_BLOCK: {
             R.unit = bitpos(b);
             R.last0 = d.last;
+            // mode TYPE reached inside this call (header end, end of a block): Z_BLOCK / Z_TREES leave here
+            // (src/inflate.c:831-832); a call that STARTS here goes on (TYPE -> TYPEDO, src/inflate.c:625)
+            if (R.flush_mode && d.at_type) {
+                R.stop = EV_BLOCKSTOP;
+                return 0;
+            }
             if (d.last) {
                 bi_drop(b, b.nbits & 7);
                 R.unit = bitpos(b);
@@ -155,6 +164,11 @@ ZSB_DEV int run_serial(State &S, Lane &L, Run &R, uint8_t *T, const uint32_t *lu
             S.rem = v & 0xffffu;
             seek_bit(b, 8ull * (bytepos + 4));
             R.phase = PH_STORED;
+            if (R.flush_mode == FL_TREES) {           // mode COPY_ (src/inflate.c:882-883)
+                R.unit = bitpos(b);
+                R.stop = EV_BLOCKSTOP;
+                return 0;
+            }
             break;
         }
         case PH_STORED: {
@@ -242,7 +256,7 @@ ZSB_DEV int run_serial(State &S, Lane &L, Run &R, uint8_t *T, const uint32_t *lu
 template <int W>
 ZSB_DEV void stream_decode(State &S, const uint8_t *in, uint32_t in_len, uint32_t out_cap, seq_t *seq,
                            const uint8_t *fixed_tab, uint8_t *scr, uint32_t *ring, const uint32_t *lut, int ln,
-                           uint32_t *big_lut = nullptr) {
+                           uint32_t *big_lut = nullptr, uint32_t flush_mode = FL_NONE) {
     Lane L;
     Run R;
     Dec &d = L.d;
@@ -258,6 +272,7 @@ ZSB_DEV void stream_decode(State &S, const uint8_t *in, uint32_t in_len, uint32_
     R.phase = S.phase; R.unit = 0; R.stop = EV_NONE; R.last0 = S.last; R.hdr_stop = false; R.hdr_tin = 0; R.hdr_bits = 0;
     if (active && R.phase != PH_HEAD) seek_bit(d.b, S.bit0);
     R.big_lut = big_lut;
+    R.flush_mode = flush_mode;
     // a call that resumes inside a block: its tables are in S.tables, the direct tables are rebuilt from them
     if (big_lut && (S.phase == PH_SYM || S.phase == PH_PENDLIT || S.phase == PH_PENDMATCH))
         lane::big_build<W>(big_lut, T, lut, S.d64, ln);
@@ -282,9 +297,13 @@ ZSB_DEV void stream_decode(State &S, const uint8_t *in, uint32_t in_len, uint32_
                 R.stop = EV_ERR;
             } else {
                 R.phase = PH_SYM;
+                if (flush_mode == FL_TREES) {             // mode LEN_ (src/inflate.c:854-857, 1031-1032)
+                    R.unit = bitpos(d.b);
+                    R.stop = EV_BLOCKSTOP;
+                }
             }
         }
-        if (lane::Wp<W>::shfl((uint32_t)msg, 0)) break;
+        if (lane::Wp<W>::shfl((uint32_t)msg, 0) || flush_mode == FL_TREES) break;
     }
     if (!active) return;
     // ---- what the reference leaves on the stream at this stop (write_result, zsb_device.cuh) ----
@@ -312,7 +331,7 @@ ZSB_DEV void stream_decode(State &S, const uint8_t *in, uint32_t in_len, uint32_
     // ---- resume point ----
     S.last = d.last;
     if (R.stop == EV_STARVE && R.phase == PH_BLOCK) S.last = R.last0;   // the header is read again
-    if (R.stop == EV_STARVE || R.stop == EV_OUTFULL) {
+    if (R.stop == EV_STARVE || R.stop == EV_OUTFULL || R.stop == EV_BLOCKSTOP) {
         uint64_t rb = R.unit;
         if (R.stop == EV_STARVE && R.phase == PH_STORED) rb = 8ull * in_len;
         c.resume_byte = (uint32_t)(rb >> 3);

@@ -16,14 +16,14 @@ namespace zsb {
 constexpr uint32_t ZS_CARRY_LIMIT = 128u << 10;     // bytes of an unfinished unit a stream can carry to its next call
 
 __global__ void __launch_bounds__(32) k_zs_decode(zs::State *S, const uint8_t *in, uint32_t in_len, uint32_t out_cap,
-                                                  lane::seq_t *seq, const uint8_t *fixed_tab) {
+                                                  lane::seq_t *seq, const uint8_t *fixed_tab, uint32_t flush_mode) {
     __shared__ uint32_t lut[LUT_WORDS];
     __shared__ __align__(16) uint8_t scr[lane::WSCR];
     __shared__ uint32_t ring[32 * lane::RING_WORDS];
     __shared__ uint32_t big_lut[lane::BIG_LUT_BYTES / 4];
     init_lut(lut, threadIdx.x, 32);
     __syncwarp();
-    zs::stream_decode<32>(*S, in, in_len, out_cap, seq, fixed_tab, scr, ring + threadIdx.x, lut, threadIdx.x, big_lut);
+    zs::stream_decode<32>(*S, in, in_len, out_cap, seq, fixed_tab, scr, ring + threadIdx.x, lut, threadIdx.x, big_lut, flush_mode);
 }
 
 __global__ void __launch_bounds__(32) k_zs_lz(const zs::State *S, uint8_t *out, const uint8_t *in, const lane::seq_t *seq) {
@@ -65,6 +65,7 @@ struct ZsJob {
     uint8_t *hist, *carry;
     uint32_t carry_len, in_len, out_cap;
     int32_t finish;
+    uint32_t flush_mode;   // zs::FL_*
 };
 
 __global__ void __launch_bounds__(CHK_THREADS) k_zsm_prep(const ZsJob *jobs) {
@@ -83,7 +84,7 @@ __global__ void __launch_bounds__(32) k_zsm_decode(const ZsJob *jobs, const uint
     const ZsJob j = jobs[blockIdx.x];
     init_lut(lut, threadIdx.x, 32);
     __syncwarp();
-    zs::stream_decode<32>(*j.S, j.in, j.in_len, j.out_cap, j.seq, fixed_tab, scr, ring + threadIdx.x, lut, threadIdx.x, big_lut);
+    zs::stream_decode<32>(*j.S, j.in, j.in_len, j.out_cap, j.seq, fixed_tab, scr, ring + threadIdx.x, lut, threadIdx.x, big_lut, j.flush_mode);
 }
 
 __global__ void __launch_bounds__(32) k_zsm_lz(const ZsJob *jobs) {
@@ -365,8 +366,8 @@ int zs_exit_bookkeeping(z_streamp strm, ZStream *z, const zsb::zs::Call &c, uInt
 }
 }  // namespace
 
-// inflate(): reference src/inflate.c:597-1275.  Z_BLOCK / Z_TREES are accepted and treated as
-// Z_NO_FLUSH (they only add early returns the reference's callers never ask for).
+// inflate(): reference src/inflate.c:597-1275, including the early returns of Z_BLOCK / Z_TREES
+// (:832,854-857,883,1032) and the bits they add to data_type (:1269-1271).
 extern "C" ZSB_API int inflate(z_streamp strm, int flush) {
     using namespace zsb;
     ZsHandle *h = zs_handle(strm);
@@ -402,7 +403,8 @@ extern "C" ZSB_API int inflate(z_streamp strm, int flush) {
                   cudaMemcpyAsync(g_zs.d_in + z->carry_len, strm->next_in, ni, cudaMemcpyHostToDevice, st) == cudaSuccess);
         cuda_ok = cuda_ok && cudaMemcpyAsync(g_zs.d_w, z->d_hist, zs::HIST, cudaMemcpyDeviceToDevice, st) == cudaSuccess;
         if (!cuda_ok) break;
-        k_zs_decode<<<1, 32, 0, st>>>(z->d_state, g_zs.d_in, in_len, no, g_zs.d_seq, g_zs.ctx->devs[0].fixed_lane);
+        k_zs_decode<<<1, 32, 0, st>>>(z->d_state, g_zs.d_in, in_len, no, g_zs.d_seq, g_zs.ctx->devs[0].fixed_lane,
+                                      flush == Z_BLOCK ? zs::FL_BLOCK : flush == Z_TREES ? zs::FL_TREES : zs::FL_NONE);
         k_zs_lz<<<1, 32, 0, st>>>(z->d_state, g_zs.d_w + zs::HIST, g_zs.d_in, g_zs.d_seq);
         k_zs_finish<<<1, CHK_THREADS, 0, st>>>(z->d_state, g_zs.d_in, in_len, g_zs.d_w, z->d_hist, z->d_carry,
                                                flush == Z_FINISH);
@@ -550,6 +552,7 @@ extern "C" ZSB_API int zsb_inflate_streams(size_t n, void **strms_v, int flush, 
             j.in_len = l.z->carry_len + ni;
             j.out_cap = no;
             j.finish = flush == Z_FINISH;
+            j.flush_mode = flush == Z_BLOCK ? zs::FL_BLOCK : flush == Z_TREES ? zs::FL_TREES : zs::FL_NONE;
         }
         cuda_ok = cudaMemcpyAsync(g_zs.m_jobs, g_zs.mh_jobs, m * sizeof(ZsJob), cudaMemcpyHostToDevice, st) == cudaSuccess &&
                   cudaMemcpy2DAsync(g_zs.m_in + ZS_CARRY_CAP, ZSM_IN_STRIDE, g_zs.mh_in, ZSM_IN, ZSM_IN, m,
