@@ -4,8 +4,9 @@ A workload (tests/workloads.py) is K distinct seeded members and a member count 
 g is distinct member g % K (tile g // K).  `DeviceBatch` takes the list of global members ONE rank decodes
 (all of them at N = 1, its zsb_plan_shards() share otherwise), gives every member its own compressed bytes in
 HBM (the k-th member of a rank that is distinct member d reads copy k of the distinct blob, so no two members
-share input cache lines) and its own output range, laid out by distinct member so that all outputs of one
-distinct member are adjacent rows of one matrix.  verify() then checks EVERY member: the whole result record
+share input cache lines) and its own output range, laid out copy by copy ("tile" by tile, the order of the descriptors too, so that neighbouring
+members have adjacent buffers as in a real archive); the outputs of one distinct member are then a strided column
+block of the (copies x tile bytes) output matrix.  verify() then checks EVERY member: the whole result record
 against the oracle's record for its distinct member, and every output byte [0, total_out) against the
 oracle's bytes (one broadcast comparison per distinct member on the GPU).  Nothing here is used by the product.
 """
@@ -83,33 +84,37 @@ class DeviceBatch:
         lens = np.array([len(m[0]) for m in distinct], dtype=np.int64)
         caps = np.array([len(m[2]) for m in distinct], dtype=np.int64)
         wbs = np.array([m[1] for m in distinct], dtype=np.int32)
-        # members sorted by distinct id; copy index = occurrence number of the distinct member on this rank
-        d = members % K
-        order = np.argsort(d, kind="stable")
+        # copy index = occurrence number of the distinct member on this rank; members are ordered copy-major
+        # (the order of a tiled batch), so that consecutive members have adjacent input and output buffers
+        d0 = members % K
+        o0 = np.argsort(d0, kind="stable")
+        count = np.bincount(d0, minlength=K).astype(np.int64)
+        first = np.concatenate(([0], np.cumsum(count)))[:-1]
+        copy0 = np.empty(len(members), dtype=np.int64)
+        copy0[o0] = np.arange(len(members), dtype=np.int64) - first[d0[o0]]
+        order = np.lexsort((d0, copy0))
         self.global_ids = members[order]
-        d = d[order]
+        d, copy = d0[order], copy0[order]
         n = len(d)
         self.n = n
-        count = np.bincount(d, minlength=K).astype(np.int64)
-        first = np.concatenate(([0], np.cumsum(count)))[:-1]
-        copy = np.arange(n, dtype=np.int64) - first[d]
-        self.count, self.first, self.d = count, first, d
+        self.count, self.d = count, d
         ncopies = int(count.max()) if n else 0
         ioff = np.concatenate(([0], np.cumsum((lens + 15) & ~15)))
         blob = np.zeros(int(ioff[-1]), dtype=np.uint8)
         for i, m in enumerate(distinct):
             blob[ioff[i]:ioff[i] + lens[i]] = np.frombuffer(m[0], dtype=np.uint8)
         self.blob, self.blob_len, self.ncopies, self.ioff = blob, int(ioff[-1]), ncopies, ioff
-        ooff_d = np.concatenate(([0], np.cumsum(count * caps)))          # start of each distinct member's output rows
-        self.ooff_d, self.caps, self.lens, self.wbs = ooff_d, caps, lens, wbs
+        ooff1 = np.concatenate(([0], np.cumsum(caps)))                   # output offsets inside one copy ("tile")
+        self.ooff1, self.tile_bytes = ooff1, int(ooff1[-1])
+        self.caps, self.lens, self.wbs = caps, lens, wbs
         self.in_off = ioff[d] + copy * self.blob_len
-        self.out_off = ooff_d[d] + copy * caps[d]
+        self.out_off = ooff1[d] + copy * self.tile_bytes
         self.in_len = lens[d]
         self.out_cap = caps[d]
         self.wb = wbs[d]
         self.sum_in = int(self.in_len.sum())
         self.sum_out = int(self.rec["tout"][d].sum())
-        self.out_bytes_total = int(ooff_d[-1])
+        self.out_bytes_total = ncopies * self.tile_bytes
         self.raw_only = bool((wbs < 0).all())
         self.t_in = self.t_out = self.t_desc = self.t_res = None
 
@@ -164,11 +169,12 @@ class DeviceBatch:
         exp_cat = np.frombuffer(b"".join(self.outs), dtype=np.uint8)
         t_exp = torch.from_numpy(exp_cat.copy()).to(self.dev) if len(exp_cat) else None
         eoff = np.concatenate(([0], np.cumsum([len(o) for o in self.outs])))
+        tiles = self.t_out[:self.ncopies * self.tile_bytes].view(max(self.ncopies, 1), -1) if self.n else None
         for di in range(self.K):
             c, cap, e = int(self.count[di]), int(self.caps[di]), len(self.outs[di])
             if c == 0 or e == 0:
                 continue
-            rows = self.t_out[int(self.ooff_d[di]):int(self.ooff_d[di]) + c * cap].view(c, cap)[:, :e]
+            rows = tiles[:c, int(self.ooff1[di]):int(self.ooff1[di]) + e]
             want = t_exp[int(eoff[di]):int(eoff[di]) + e]
             if not bool((rows == want.unsqueeze(0)).all()):
                 neq = (rows != want.unsqueeze(0)).nonzero()[0]
@@ -199,12 +205,13 @@ class DeviceBatch:
     def verify_host(self):
         res = self.hres[:self.n * 32].view(RES_DT)
         bad = self.verify_records(res)
+        htiles = np.ctypeslib.as_array((ctypes.c_uint8 * max(self.out_bytes_total, 1)).from_address(self.h_out))
+        htiles = htiles[:self.ncopies * self.tile_bytes].reshape(max(self.ncopies, 1), -1)
         for di in range(self.K):
             c, cap, e = int(self.count[di]), int(self.caps[di]), len(self.outs[di])
             if c == 0 or e == 0:
                 continue
-            buf = np.ctypeslib.as_array((ctypes.c_uint8 * (c * cap)).from_address(self.h_out + int(self.ooff_d[di])))
-            rows = buf.reshape(c, cap)[:, :e]
+            rows = htiles[:c, int(self.ooff1[di]):int(self.ooff1[di]) + e]
             want = np.frombuffer(self.outs[di], dtype=np.uint8)
             if not (rows == want[None, :]).all():
                 bad.append("host bytes: distinct %d" % di)

@@ -67,13 +67,44 @@ extern "C" void zsb_host_free(void *p) {
     if (p) cudaFreeHost(p);
 }
 
+// Stable sort of the indices idx[0..n) by key, largest first (LSD radix, 11 bits a pass over the bits the keys
+// use): the schedulers order 10^6 members per call, where a comparison sort costs ~100 ms of host time per batch.
+template <typename KeyOf> static void sort_largest_first(uint32_t *idx, size_t n, KeyOf key_of) {
+    if (n < 2) return;
+    std::vector<uint64_t> key(n);
+    uint64_t all = 0;
+    for (size_t i = 0; i < n; i++) {
+        key[i] = key_of(idx[i]);
+        all |= key[i];
+    }
+    int bits = 0;
+    while (bits < 64 && (all >> bits)) bits++;
+    std::vector<uint32_t> tmp_i(n);
+    std::vector<uint64_t> tmp_k(n);
+    uint32_t *src_i = idx, *dst_i = tmp_i.data();
+    uint64_t *src_k = key.data(), *dst_k = tmp_k.data();
+    for (int sh = 0; sh < bits; sh += 11) {
+        size_t cnt[2049] = {0};
+        for (size_t i = 0; i < n; i++) cnt[2047 - ((src_k[i] >> sh) & 2047) + 1]++;      // descending digit order
+        for (int b = 0; b < 2048; b++) cnt[b + 1] += cnt[b];
+        for (size_t i = 0; i < n; i++) {
+            const size_t at = cnt[2047 - ((src_k[i] >> sh) & 2047)]++;
+            dst_i[at] = src_i[i];
+            dst_k[at] = src_k[i];
+        }
+        std::swap(src_i, dst_i);
+        std::swap(src_k, dst_k);
+    }
+    if (src_i != idx) memcpy(idx, src_i, n * sizeof(uint32_t));
+}
+
 // ---- length-aware sharding: longest processing time first --------------------------------------
 extern "C" int zsb_plan_shards(size_t n, const uint64_t *cost, int nshards, int32_t *shard_of, uint64_t *load) {
     if (nshards < 1 || (n && (!cost || !shard_of))) return ZSB_E_ARG;
     std::vector<uint64_t> ld((size_t)nshards, 0);
     std::vector<uint32_t> idx(n);
     for (size_t i = 0; i < n; i++) idx[i] = (uint32_t)i;
-    std::stable_sort(idx.begin(), idx.end(), [&](uint32_t a, uint32_t b) { return cost[a] > cost[b]; });
+    sort_largest_first(idx.data(), n, [&](uint32_t a) { return cost[a]; });
     for (size_t k = 0; k < n; k++) {
         int best = 0;
         for (int s = 1; s < nshards; s++)
@@ -432,9 +463,7 @@ static int run_device(zsb_ctx *ctx, zsb_dev &dv, size_t n, const zsb_member *dm,
             own.resize(n);
             for (size_t i = 0; i < n; i++) own[i] = (uint32_t)i;
             if (ctx->path == 0)          // largest first: lanes finish together, and the split needs it
-                std::stable_sort(own.begin(), own.end(), [&](uint32_t a, uint32_t b) {
-                    return hm[a].in_len + hm[a].out_cap > hm[b].in_len + hm[b].out_cap;
-                });
+                sort_largest_first(own.data(), n, [&](uint32_t a) { return (uint64_t)hm[a].in_len + hm[a].out_cap; });
             horder = own.data();
         }
         CK(ctx, cudaMemcpyAsync(dorder, horder, n * sizeof(uint32_t), cudaMemcpyHostToDevice, st));
@@ -953,9 +982,7 @@ static int batch_host(zsb_ctx *ctx, size_t n, const zsb_member *m, zsb_result *r
             }
             if (most * 150.0 > total / 190.0) {
                 std::vector<uint32_t> ord(sh.idx);
-                std::stable_sort(ord.begin(), ord.end(), [&](uint32_t a, uint32_t b) {
-                    return m[a].in_len + m[a].out_cap > m[b].in_len + m[b].out_cap;
-                });
+                sort_largest_first(ord.data(), ord.size(), [&](uint32_t a) { return (uint64_t)m[a].in_len + m[a].out_cap; });
                 const size_t nb = split_big(m, ord.data(), ord.size(), dv.sm_count);
                 if (nb) big_threshold = (double)m[ord[nb - 1]].in_len + (double)m[ord[nb - 1]].out_cap;
             }
@@ -976,9 +1003,7 @@ static int batch_host(zsb_ctx *ctx, size_t n, const zsb_member *m, zsb_result *r
                 hoc[j] = (uint32_t)j;
             }
             // largest first: the decoder's lanes then finish together
-            std::stable_sort(hoc, hoc + ch.count, [&](uint32_t a, uint32_t b) {
-                return hmc[a].in_len + hmc[a].out_cap > hmc[b].in_len + hmc[b].out_cap;
-            });
+            sort_largest_first(hoc, ch.count, [&](uint32_t a) { return (uint64_t)hmc[a].in_len + hmc[a].out_cap; });
             cudaEvent_t ev_in = dv.pipe_ev[2 * c], ev_dec = dv.pipe_ev[2 * c + 1];
             cudaStream_t dst = dv.pipe_streams[c % NS];
             CK(ctx, cudaMemcpyAsync(dm + ch.first, hm + ch.first, ch.count * sizeof(zsb_member), cudaMemcpyHostToDevice,
@@ -1160,9 +1185,7 @@ static int batch_device_ptrs(zsb_ctx *ctx, size_t n, const zsb_member *m, zsb_re
             raw_only &= P.mm[j].window_bits < 0 && P.mm[j].flags == 0;
             if (P.mm[j].in_len > 0xfffffff0ull || P.mm[j].out_cap > 0xfffffff0ull) P.mm[j].window_bits = 1000;   // -> Z_STREAM_ERROR
         }
-        std::stable_sort(P.ord.begin(), P.ord.end(), [&](uint32_t a, uint32_t b) {
-            return P.mm[a].in_len + P.mm[a].out_cap > P.mm[b].in_len + P.mm[b].out_cap;
-        });
+        sort_largest_first(P.ord.data(), k, [&](uint32_t a) { return (uint64_t)P.mm[a].in_len + P.mm[a].out_cap; });
         cudaStream_t st = dv.stream;
         CK(ctx, cudaMemcpyAsync(dm, P.mm.data(), k * sizeof(zsb_member), cudaMemcpyHostToDevice, st));
         if ((rc = run_device(ctx, dv, k, dm, dr, P.mm.data(), P.ord.data(), raw_only ? ZSB_RAW_ONLY : ZSB_HAS_WRAPPED, st))) return rc;
