@@ -8,6 +8,19 @@
  *        inflate           replaces reference src/inflate.c:597-1275
  *        inflateEnd        replaces reference src/inflate.c:1277-1287
  *        inflateReset/inflateReset2/inflateResetKeep   reference src/inflate.c:112-184
+ *      and the auxiliary entry points of the inflate side:
+ *        inflatePrime          src/inflate.c:231    inflateGetDictionary  :1289    inflateSetDictionary :1309
+ *        inflateGetHeader      :1341                inflateSync           :1386    inflateSyncPoint     :1444
+ *        inflateCopy           :1452                inflateUndermine      :1494    inflateValidate      :1509
+ *        inflateMark           :1521                inflateCodesUsed      :1532
+ *      inflate() honours Z_BLOCK and Z_TREES (early returns + the 128 / 256 bits of data_type).
+ *      Deviations, all of them in states the reference's callers never enter: (a) inflatePrime answers
+ *      Z_STREAM_ERROR when the stream stopped inside a block header or a symbol (the unit is decoded again
+ *      from its first bit here, so bits cannot be spliced into it) or before the header of a zlib / gzip
+ *      stream; at a block boundary, at the start of a raw stream and after an earlier inflatePrime it works
+ *      as in the reference; (b) the fields of a gz_header registered with inflateGetHeader are filled when the
+ *      header is complete (done = 1), not field by field while it arrives; (c) inflateCodesUsed reports the
+ *      code-length code's table only once the block header is complete.
  *      They are declared by the system <zlib.h> (the same header the reference compiles against) and
  *      are exactly what src/wasm/inflate_stream_wasm.c:26,33,41,49-53, src/wasm/inflate9_stream_wasm.c:
  *      19,27-30, src/wasm/wasm_stream_common.c:58 and test/payload_decompress.c:124,156,192 call.

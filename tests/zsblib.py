@@ -18,7 +18,9 @@ API_SYMBOLS = ["zsb_create", "zsb_destroy", "zsb_create_error", "zsb_last_error"
                "zsb_last_launches", "zsb_plan_shards", "zsb_host_alloc", "zsb_host_free", "zsb_message",
                "zsb_profile_read", "zsb_zip_scan", "zsb_zip_members", "zsb_zip_inflate", "zsb_gunzip_files", "zsb_plan_big", "zsb_inflate_streams", "zsb_gzip_header"]
 ZLIB_SYMBOLS = ["inflateInit_", "inflateInit2_", "inflate", "inflateEnd", "inflateReset", "inflateReset2",
-                "inflateResetKeep"]
+                "inflateResetKeep", "inflatePrime", "inflateGetDictionary", "inflateSetDictionary", "inflateGetHeader",
+                "inflateSync", "inflateSyncPoint", "inflateCopy", "inflateUndermine", "inflateValidate", "inflateMark",
+                "inflateCodesUsed"]
 
 ZSB_RAW_ONLY = 4
 ZSB_HAS_WRAPPED = 1

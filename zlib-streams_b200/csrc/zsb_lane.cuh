@@ -643,6 +643,8 @@ ZSB_DEV int lane_dynamic_header(Lane &L, uint8_t *T, const uint32_t *lut) {
 constexpr int W_FIRST = 800;              // u32[16] first canonical code per length
 constexpr int W_LIM = 864;                // u32[16] (first+count) left-aligned to 15 bits
 constexpr int W_OFF0 = 928;               // u32[16] index of the first symbol of each length in code order
+// (entry 0 of W_LIM / W_OFF0 is no length's: after build_tables they hold the table entries the reference's
+//  inflate_table() would have allocated for the literal/length and the distance code: inflateCodesUsed())
 
 // Table space the reference's two-level builder would use with `root` index bits: the root plus one
 // sub-table per root prefix that carries longer codes, sized by the longest code under the prefix
@@ -733,7 +735,12 @@ ZSB_DEV bool build_litlen_tab(uint8_t *T, uint8_t *scr, const uint8_t *lens, uin
     const uint32_t *first = (const uint32_t *)(scr + W_FIRST), *lim = (const uint32_t *)(scr + W_LIM);
     const uint32_t *off0 = (const uint32_t *)(scr + W_OFF0);
     const uint16_t *sorted = (const uint16_t *)(scr + W_SORT);
-    if (maxl > 9 && ref_table_space(cnt, first, 9, maxl) > (d64 ? 851u : 852u)) return false;
+    uint32_t minl = 1;
+    while (minl < maxl && !cnt[minl]) minl++;
+    const uint32_t root = 9u < maxl ? (9u > minl ? 9u : minl) : maxl;      // src/inftrees.c:126-142
+    const uint32_t used = maxl > root ? ref_table_space(cnt, first, root, maxl) : (1u << root);
+    if (used > (d64 ? 851u : 852u)) return false;
+    if (lane == 0) ((uint32_t *)(scr + W_LIM))[0] = used;       // what inflateCodesUsed() would count for this code
     for (int j = lane; j < 15; j += W) {
         const uint32_t l = j + 1;
         ((uint16_t *)(T + S_LLIM))[j] = (uint16_t)lim[l];
@@ -755,6 +762,7 @@ ZSB_DEV bool build_dist_tab(uint8_t *T, uint8_t *scr, const uint8_t *lens, uint3
     if (k == 1) {                                           // no codes at all: src/inftrees.c:131-139
         if (d64) return false;
         for (int j = lane; j < 15; j += W) ((uint16_t *)(T + S_DLIM))[j] = 0;      // every pattern: invalid, one bit
+        if (lane == 0) ((uint32_t *)(scr + W_OFF0))[0] = 2;
         Wp<W>::sync();
         return true;
     }
@@ -762,7 +770,12 @@ ZSB_DEV bool build_dist_tab(uint8_t *T, uint8_t *scr, const uint8_t *lens, uint3
     const uint32_t *first = (const uint32_t *)(scr + W_FIRST), *lim = (const uint32_t *)(scr + W_LIM);
     const uint32_t *off0 = (const uint32_t *)(scr + W_OFF0);
     const uint16_t *sorted = (const uint16_t *)(scr + W_SORT);
-    if (d64 && maxl > 6 && ref_table_space(cnt, first, 6, maxl) > 593u) return false;
+    uint32_t minl = 1;
+    while (minl < maxl && !cnt[minl]) minl++;
+    const uint32_t root = 6u < maxl ? (6u > minl ? 6u : minl) : maxl;
+    const uint32_t used = maxl > root ? ref_table_space(cnt, first, root, maxl) : (1u << root);
+    if (d64 && used > 593u) return false;
+    if (lane == 0) ((uint32_t *)(scr + W_OFF0))[0] = used;
     for (int j = lane; j < 15; j += W) {
         const uint32_t l = j + 1;
         ((uint16_t *)(T + S_DLIM))[j] = (uint16_t)lim[l];

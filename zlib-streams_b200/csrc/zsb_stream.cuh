@@ -18,7 +18,8 @@ namespace zsb {
 namespace zs {
 
 enum : uint32_t { PH_HEAD = 0, PH_BLOCK = 1, PH_STORED = 2, PH_SYM = 3, PH_PENDLIT = 4, PH_PENDMATCH = 5,
-                  PH_CHECK = 6, PH_LENGTH = 7, PH_DONE = 8, PH_BAD = 9, PH_NEEDDICT = 10 };
+                  PH_CHECK = 6, PH_LENGTH = 7, PH_DONE = 8, PH_BAD = 9, PH_NEEDDICT = 10,
+                  PH_DICTSET = 11 };      // inflateSetDictionary() answered Z_NEED_DICT: mode TYPE is entered in the next call
 
 constexpr uint32_t HIST = 65536;          // bytes of history kept in front of every call's output
 
@@ -34,7 +35,14 @@ struct Call {
     uint32_t nseq;
     uint32_t trailer_pos;  // when need_trailer: byte offset of the trailer
     uint32_t need_trailer;
-    uint32_t pad[2];
+    int32_t mark;          // inflateMark()'s value at this stop (src/inflate.c:1521-1530)
+    uint32_t codes_used;   // inflateCodesUsed()'s value (src/inflate.c:1532)
+    uint32_t sync_point;   // inflateSyncPoint(): waiting for a stored block's length bytes with no bits held
+    uint32_t whave;        // history bytes the reference's window would hold (inflateGetDictionary)
+    uint32_t hdr_len;      // nonzero in the call that completed the zlib / gzip header: its length in bytes
+    uint32_t hdr_kind;     // 1 zlib, 2 gzip (with hdr_len)
+    uint32_t bit0;         // bit offset of the resume point inside the first carried byte
+    uint32_t pad[3];
 };
 
 struct State {
@@ -47,6 +55,10 @@ struct State {
     uint32_t check;        // running Adler-32 / CRC-32 of all output
     uint32_t total_lo;     // output so far, modulo 2^32 (gzip ISIZE)
     uint32_t last_dt;      // data_type low bits of the last stop (for calls after the end)
+    uint32_t noverify;     // inflateValidate(strm, 0) / inflateSync(): wrap & 4 cleared — no check value is computed or compared
+    uint32_t was;          // full length of the match being copied (inflateMark)
+    int32_t back;          // bits of the current symbol's codes consumed so far, -1 outside symbols (inflateMark)
+    uint32_t codes_used;
     uint32_t pad;
     Call call;
     alignas(16) uint8_t tables[lane::SLOT];
@@ -63,6 +75,8 @@ struct Run {               // lane 0's bookkeeping during one call
     bool hdr_stop;
     uint32_t hdr_tin, hdr_bits;
     const uint32_t *big_lut;   // direct tables of the current block (lane::big_build), or NULL
+    uint32_t sync_point;
+    uint32_t hdr_len, hdr_kind;
     uint32_t flush_mode;       // 0, FL_BLOCK (inflate(Z_BLOCK)) or FL_TREES (inflate(Z_TREES))
 };
 // inflate()'s flush values that add early returns (reference src/inflate.c:832,854-857,883,1032)
@@ -87,6 +101,11 @@ ZSB_DEV int run_serial(State &S, Lane &L, Run &R, uint8_t *T, const uint32_t *lu
     BitIn &b = d.b;
     for (;;) {
         switch (R.phase) {
+        case PH_DICTSET:                           // src/inflate.c:822-830: DICT with the dictionary set -> TYPE
+            L.mm.kind = 1;
+            d.at_type = 1;
+            R.phase = PH_BLOCK;
+            break;
         case PH_HEAD: {
             HeadOut h = parse_wrapper(b.p, b.len, S.wbits_arg);
             L.mm.kind = h.kind;
@@ -102,8 +121,10 @@ ZSB_DEV int run_serial(State &S, Lane &L, Run &R, uint8_t *T, const uint32_t *lu
             }
             S.kind = h.kind;
             S.check = h.adler;
+            R.hdr_len = h.pos;
+            R.hdr_kind = h.kind;
             if (S.wbits == 0) S.wbits = h.kind == 1 ? (uint32_t)(b.p[0] >> 4) + 8u : 15u;
-            seek_bit(b, 8ull * h.pos);
+            seek_bit(b, 8ull * h.pos + (h.kind == 0 ? S.bit0 : 0u));      // (a raw stream may have been primed: inflatePrime)
             d.at_type = h.kind != 0;
             R.phase = PH_BLOCK;
             break;
@@ -149,6 +170,7 @@ ZSB_DEV int run_serial(State &S, Lane &L, Run &R, uint8_t *T, const uint32_t *lu
             bi_drop(b, b.nbits & 7);
             const uint32_t bytepos = b.next - (b.nbits >> 3);
             if (b.len - bytepos < 4) {
+                R.sync_point = b.len == bytepos;      // mode STORED with an empty bit buffer (inflateSyncPoint)
                 b.nbits = 8 * (b.len - bytepos);
                 b.next = b.len;
                 R.stop = EV_STARVE;
@@ -228,15 +250,20 @@ ZSB_DEV int run_serial(State &S, Lane &L, Run &R, uint8_t *T, const uint32_t *lu
             if (R.big_lut) lane::big_run(L, T, lut, R.big_lut);
             R.unit = bitpos(b);
             const int ev = lane::careful_symbol(d, T, lut);
+            // the bits of this symbol's codes consumed so far: what the reference keeps in state->back
+            // (src/inflate.c:1046-1142); a symbol the direct-table loop took whole leaves no trace, as inflate_fast()
+            S.back = (int32_t)(bitpos(b) - R.unit);
             if (ev == EV_LIT) {
                 S.plit = d.mdist;
                 R.phase = PH_PENDLIT;
             } else if (ev == EV_MATCH) {
                 S.rem = d.mlen;
+                S.was = d.mlen;
                 S.mdist = d.mdist;
                 R.phase = PH_PENDMATCH;
             } else if (ev == EV_EOB) {
                 d.at_type = 1;
+                S.back = -1;
                 R.phase = PH_BLOCK;
             } else {
                 R.stop = ev;                      // EV_ERR or EV_STARVE (the unit is decoded again later)
@@ -272,6 +299,9 @@ ZSB_DEV void stream_decode(State &S, const uint8_t *in, uint32_t in_len, uint32_
     R.phase = S.phase; R.unit = 0; R.stop = EV_NONE; R.last0 = S.last; R.hdr_stop = false; R.hdr_tin = 0; R.hdr_bits = 0;
     if (active && R.phase != PH_HEAD) seek_bit(d.b, S.bit0);
     R.big_lut = big_lut;
+    R.sync_point = 0;
+    R.hdr_len = 0;
+    R.hdr_kind = 0;
     R.flush_mode = flush_mode;
     // a call that resumes inside a block: its tables are in S.tables, the direct tables are rebuilt from them
     if (big_lut && (S.phase == PH_SYM || S.phase == PH_PENDLIT || S.phase == PH_PENDMATCH))
@@ -292,11 +322,17 @@ ZSB_DEV void stream_decode(State &S, const uint8_t *in, uint32_t in_len, uint32_
         }
         if (big_lut && !msg) lane::big_build<W>(big_lut, T, lut, S.d64, ln);
         if (active) {
+            // inflateCodesUsed(): entries of the tables the reference built last (src/inflate.c:992-1027); a rejected
+            // literal/length set leaves none, a rejected distance set leaves the literal/length table's
+            if (want == 1)
+                S.codes_used = msg == M_LITLENS ? 0u : ((const uint32_t *)(scr + lane::W_LIM))[0] +
+                               (msg == M_DISTS ? 0u : ((const uint32_t *)(scr + lane::W_OFF0))[0]);
             if (msg) {
                 d.msg = msg;
                 R.stop = EV_ERR;
             } else {
                 R.phase = PH_SYM;
+                S.back = -1;                              // a block starts: the reference left -1 at the last end of block
                 if (flush_mode == FL_TREES) {             // mode LEN_ (src/inflate.c:854-857, 1031-1032)
                     R.unit = bitpos(d.b);
                     R.stop = EV_BLOCKSTOP;
@@ -324,6 +360,21 @@ ZSB_DEV void stream_decode(State &S, const uint8_t *in, uint32_t in_len, uint32_
     c.nseq = (uint32_t)(L.seq - L.seq0);
     c.need_trailer = a.need_trailer;
     c.trailer_pos = a.trailer_pos;
+    c.sync_point = R.sync_point;
+    c.bit0 = 0;
+    c.hdr_len = R.hdr_len;
+    c.hdr_kind = R.hdr_kind;
+    c.codes_used = S.codes_used;
+    // inflateMark(): (back << 16) + bytes of the current stored block still to copy (mode COPY) / bytes of the current
+    // match already copied (mode MATCH)
+    {
+        const bool in_symbol = R.phase == PH_SYM || R.phase == PH_PENDLIT || R.phase == PH_PENDMATCH;
+        if (!in_symbol) S.back = -1;
+        int32_t low = 0;
+        if (R.phase == PH_STORED && R.stop != EV_BLOCKSTOP && R.stop != EV_ERR) low = (int32_t)S.rem;
+        if (R.phase == PH_PENDMATCH && R.stop != EV_ERR) low = (int32_t)(S.was - S.rem);
+        c.mark = (int32_t)((uint32_t)S.back << 16) + low;
+    }
     if (R.phase == PH_CHECK || R.phase == PH_LENGTH) {     // resumed inside the trailer
         c.need_trailer = 1;
         c.trailer_pos = 0;
@@ -336,6 +387,7 @@ ZSB_DEV void stream_decode(State &S, const uint8_t *in, uint32_t in_len, uint32_
         if (R.stop == EV_STARVE && R.phase == PH_STORED) rb = 8ull * in_len;
         c.resume_byte = (uint32_t)(rb >> 3);
         S.bit0 = (uint32_t)(rb & 7);
+        c.bit0 = S.bit0;
         S.phase = R.phase;
         if (c.resume_byte > c.cpos) c.resume_byte = c.cpos;
     } else if (R.stop == EV_DONE) {
@@ -357,7 +409,7 @@ ZSB_DEV void finish_call(State &S, const uint8_t *in, uint32_t in_len, uint32_t 
     Call c = S.call;
     const uint32_t produced = c.produced, kind = S.kind;
     S.total_lo += produced;
-    if (kind != 0) {                  // kind is only set once the wrapper header has been read
+    if (kind != 0 && !S.noverify) {   // kind is only set once the wrapper header has been read
         S.check = check;
         c.adler = check;
     }
@@ -372,7 +424,7 @@ ZSB_DEV void finish_call(State &S, const uint8_t *in, uint32_t in_len, uint32_t 
                 uint32_t v = le32(in + pos);
                 if (kind == 1) v = (v >> 24) | ((v >> 8) & 0xff00u) | ((v & 0xff00u) << 8) | (v << 24);
                 pos += 4;
-                if (v != check) {
+                if (!S.noverify && v != check) {
                     c.stop = EV_ERR; c.msg = M_DATACHECK; c.cpos = pos; c.resume_byte = pos; c.data_type = 32 + 64;
                     S.phase = PH_BAD;
                     done = true;
@@ -389,7 +441,7 @@ ZSB_DEV void finish_call(State &S, const uint8_t *in, uint32_t in_len, uint32_t 
             } else {
                 const uint32_t isz = le32(in + pos);
                 pos += 4;
-                if (isz != S.total_lo) {
+                if (!S.noverify && isz != S.total_lo) {
                     c.stop = EV_ERR; c.msg = M_LENCHECK; c.cpos = pos; c.resume_byte = pos; c.data_type = 32 + 64;
                     S.phase = PH_BAD;
                     done = true;
@@ -408,6 +460,7 @@ ZSB_DEV void finish_call(State &S, const uint8_t *in, uint32_t in_len, uint32_t 
         const uint64_t h = (uint64_t)S.whave + produced;
         S.whave = h > S.wsize ? S.wsize : (uint32_t)h;
     }
+    c.whave = S.whave;
     S.call = c;
 }
 

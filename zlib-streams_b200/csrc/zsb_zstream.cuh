@@ -153,6 +153,20 @@ struct ZStream {                           // host mirror of one stream
     uint32_t phase = zsb::zs::PH_HEAD;
     uint32_t last_dt = 0;
     int wrap = 0, wbits_arg = 0;
+    // ---- what the auxiliary entry points need (reference src/inflate.c:231-258, 1289-1537) ----
+    std::vector<uint8_t> carry_shadow;     // host copy of the carried bytes (the device's d_carry): inflateSync looks into
+                                           // the held bytes, inflateGetHeader at the header, inflatePrime appends to them
+    uint32_t bit0 = 0;                     // bit offset of the resume point inside carry_shadow[0]
+    uint32_t held_bits = 0;                // the reference's state->bits at the last return
+    bool header_seen = false;              // state->flags != -1
+    uint32_t kind = 0;                     // 0 raw / unknown yet, 1 zlib, 2 gzip
+    gz_headerp head = nullptr;             // inflateGetHeader()
+    uint32_t dictid = 0;                   // Adler-32 the stream asked for with Z_NEED_DICT
+    long mark = -65536;                    // inflateMark()
+    unsigned long codes_used = 0;          // inflateCodesUsed()
+    uint32_t sync_point = 0, whave = 0;
+    bool in_sync = false;                  // mode SYNC: inflateSync() has started a search
+    uint32_t sync_have = 0;
 };
 
 // what strm->state points to; allocated with the caller's zalloc (reference src/inflate.c:210-214)
@@ -211,13 +225,19 @@ bool zs_decode_wbits(int windowBits, int &wrap, int &d64, int &wbits) {
     return true;
 }
 
-int zs_reset_device(ZStream *z, int window_bits_arg, int d64, int wbits) {
+// keep_window: inflateResetKeep() leaves the sliding window alone (src/inflate.c:112-133); inflateReset() empties it
+int zs_reset_device(ZStream *z, int window_bits_arg, int d64, int wbits, bool keep_window = false) {
     zsb::zs::State s0;
     memset(&s0, 0, offsetof(zsb::zs::State, tables));
     s0.phase = zsb::zs::PH_HEAD;
     s0.d64 = (uint32_t)d64;
     s0.wbits_arg = window_bits_arg;
     s0.wbits = (uint32_t)wbits;
+    s0.back = -1;
+    const uint32_t whave = keep_window ? z->whave : 0u;
+    s0.whave = whave;
+    s0.wsize = whave ? 1u << (wbits ? wbits : 15) : 0u;
+    s0.noverify = (z->wrap && !(z->wrap & 4)) ? 1u : 0u;     // inflateValidate(strm, 0) survives inflateReset (state->wrap does)
     std::lock_guard<std::mutex> lk(g_zs.mu);
     if (cudaMemcpyAsync(z->d_state, &s0, offsetof(zsb::zs::State, tables), cudaMemcpyHostToDevice, g_zs.st) != cudaSuccess ||
         cudaStreamSynchronize(g_zs.st) != cudaSuccess) {
@@ -227,7 +247,97 @@ int zs_reset_device(ZStream *z, int window_bits_arg, int d64, int wbits) {
     z->carry_len = 0;
     z->phase = zsb::zs::PH_HEAD;
     z->last_dt = 0;
+    z->carry_shadow.clear();
+    z->head = nullptr;                     // inflateResetKeep drops the registered gz_header (src/inflate.c:125)
+    z->bit0 = 0; z->held_bits = 0; z->header_seen = false; z->kind = 0; z->dictid = 0; z->mark = -65536;
+    z->codes_used = 0; z->sync_point = 0; z->whave = whave; z->in_sync = false; z->sync_have = 0;
     return Z_OK;
+}
+
+// Adler-32 (RFC 1950) of a dictionary on the host: inflateSetDictionary()'s identifier check
+uint32_t zs_adler32(const uint8_t *p, size_t n) {
+    uint32_t a = 1, b = 0;
+    while (n) {
+        size_t k = n < 5552 ? n : 5552;
+        n -= k;
+        while (k--) {
+            a += *p++;
+            b += a;
+        }
+        a %= 65521u;
+        b %= 65521u;
+    }
+    return (b << 16) | a;
+}
+
+// After one round of GPU work: advance the caller's buffers, keep the host copy of the carried bytes, fill the
+// registered gz_header when the header was completed, mirror what the auxiliary entry points report.
+// ni = new input bytes offered this round (from strm->next_in).
+void zs_after_round(z_streamp strm, ZStream *z, const zsb::zs::Call &c, uint32_t ni) {
+    using namespace zsb;
+    const uint32_t old_carry = z->carry_len, in_len = old_carry + ni;
+    uint32_t cpos = c.cpos;
+    if (c.stop == EV_NEEDDICT) cpos = in_len < 6 ? in_len : 6;      // header + dictionary id were read
+    auto byte_at = [&](uint32_t i) -> uint8_t { return i < old_carry ? z->carry_shadow[i] : strm->next_in[i - old_carry]; };
+    if (c.hdr_len) {
+        z->header_seen = true;
+        z->kind = c.hdr_kind;
+        if (z->head) {
+            if (c.hdr_kind == 2) {
+                std::vector<uint8_t> hb(c.hdr_len);
+                for (uint32_t i = 0; i < c.hdr_len; i++) hb[i] = byte_at(i);
+                zsb_gz_header g;
+                if (zsb_gzip_header(hb.data(), hb.size(), &g) == 0) {          // reference src/inflate.c:678-816
+                    gz_headerp hd = z->head;
+                    hd->text = (int)g.text;
+                    hd->time = g.time;
+                    hd->xflags = (int)g.xflags;
+                    hd->os = (int)g.os;
+                    const uint32_t flg = hb[3];
+                    if (flg & 4) hd->extra_len = g.extra_len;
+                    if ((flg & 4) && hd->extra != Z_NULL && g.extra_len)
+                        memcpy(hd->extra, hb.data() + g.extra_off, std::min<uInt>(g.extra_len, hd->extra_max));
+                    auto text_field = [&](Bytef *dst, uInt dst_max, uint32_t off, uint32_t len, bool present) {
+                        if (dst == Z_NULL) return;
+                        if (!present) return;
+                        // the field with its terminating NUL, cut to dst_max (src/inflate.c:757-783)
+                        const uInt n = std::min<uInt>(len + 1, dst_max);
+                        if (n) memcpy(dst, hb.data() + (len ? off : 0), len ? std::min<uInt>(len, n) : 0);
+                        if (len < n) dst[len] = 0;
+                    };
+                    if (flg & 8) text_field(hd->name, hd->name_max, g.name_off, g.name_len, true);
+                    else hd->name = Z_NULL;
+                    if (flg & 16) text_field(hd->comment, hd->comm_max, g.comment_off, g.comment_len, true);
+                    else hd->comment = Z_NULL;
+                    if (!(flg & 4)) hd->extra = Z_NULL;
+                    hd->hcrc = (int)((flg >> 1) & 1);
+                    hd->done = 1;
+                }
+            } else {
+                z->head->done = -1;                                            // a zlib header: src/inflate.c:662-664
+            }
+        }
+    }
+    const uint32_t used = cpos > old_carry ? cpos - old_carry : 0;
+    const uint32_t ncarry = c.cpos > c.resume_byte ? c.cpos - c.resume_byte : 0;
+    if (ncarry <= ZS_CARRY_CAP) {
+        std::vector<uint8_t> nc(ncarry);
+        for (uint32_t i = 0; i < ncarry; i++) nc[i] = byte_at(c.resume_byte + i);
+        z->carry_shadow.swap(nc);
+    }
+    strm->next_in += used;
+    strm->avail_in -= used;
+    strm->next_out += c.produced;
+    strm->avail_out -= c.produced;
+    z->carry_len = ncarry;
+    z->bit0 = c.bit0;
+    z->held_bits = c.data_type & 63u;
+    z->mark = (long)c.mark;
+    z->codes_used = c.codes_used;
+    z->sync_point = c.sync_point;
+    z->whave = c.whave;
+    z->in_sync = false;
+    if (c.stop == EV_NEEDDICT) z->dictid = c.adler;
 }
 
 }  // namespace
@@ -239,13 +349,19 @@ ZSB_API int inflateResetKeep(z_streamp strm) {
     if (!h) return Z_STREAM_ERROR;
     int wrap, d64, wbits;
     zs_decode_wbits(h->zs->wbits_arg, wrap, d64, wbits);
+    wrap = h->zs->wrap;                                 // (inflateValidate / inflateSync may have changed it)
     strm->total_in = strm->total_out = 0;
     strm->msg = Z_NULL;
     if (wrap) strm->adler = (uLong)(wrap & 1);
-    return zs_reset_device(h->zs, h->zs->wbits_arg, d64, wbits);
+    return zs_reset_device(h->zs, h->zs->wbits_arg, d64, wbits, true);
 }
 
-ZSB_API int inflateReset(z_streamp strm) { return inflateResetKeep(strm); }
+ZSB_API int inflateReset(z_streamp strm) {              // src/inflate.c:135-145: the window is emptied first
+    ZsHandle *h = zs_handle(strm);
+    if (!h) return Z_STREAM_ERROR;
+    h->zs->whave = 0;
+    return inflateResetKeep(strm);
+}
 
 ZSB_API int inflateReset2(z_streamp strm, int windowBits) {
     ZsHandle *h = zs_handle(strm);
@@ -418,14 +534,7 @@ extern "C" ZSB_API int inflate(z_streamp strm, int flush) {
                       cudaStreamSynchronize(st) == cudaSuccess;
             if (!cuda_ok) break;
         }
-        uint32_t cpos = c.cpos;
-        if (c.stop == EV_NEEDDICT) cpos = in_len < 6 ? in_len : 6;   // header + dictionary id were read
-        const uint32_t used = cpos > z->carry_len ? cpos - z->carry_len : 0;
-        strm->next_in += used;
-        strm->avail_in -= used;
-        strm->next_out += c.produced;
-        strm->avail_out -= c.produced;
-        z->carry_len = c.cpos > c.resume_byte ? c.cpos - c.resume_byte : 0;
+        zs_after_round(strm, z, c, ni);
         if (c.stop == EV_STARVE && strm->avail_in > 0) continue;
         if (c.stop == EV_OUTFULL && strm->avail_out > 0) continue;
         break;
@@ -582,15 +691,7 @@ extern "C" ZSB_API int zsb_inflate_streams(size_t n, void **strms_v, int flush, 
             const zs::Call c = g_zs.mh_calls[k];
             l.c = c;
             if (c.produced) memcpy(strm->next_out, g_zs.mh_out + k * (size_t)ZSM_OUT, c.produced);
-            const uint32_t in_len = z->carry_len + nis[k];
-            uint32_t cpos = c.cpos;
-            if (c.stop == EV_NEEDDICT) cpos = in_len < 6 ? in_len : 6;   // header + dictionary id were read
-            const uint32_t used = cpos > z->carry_len ? cpos - z->carry_len : 0;
-            strm->next_in += used;
-            strm->avail_in -= used;
-            strm->next_out += c.produced;
-            strm->avail_out -= c.produced;
-            z->carry_len = c.cpos > c.resume_byte ? c.cpos - c.resume_byte : 0;
+            zs_after_round(strm, z, c, nis[k]);
             if ((c.stop == EV_STARVE && strm->avail_in > 0) || (c.stop == EV_OUTFULL && strm->avail_out > 0)) {
                 if (z->carry_len > ZS_CARRY_CAP) rets[l.i] = Z_MEM_ERROR;     // a wrapper header longer than the carry buffer
                 else next.push_back(round[k]);
@@ -606,3 +707,323 @@ extern "C" ZSB_API int zsb_inflate_streams(size_t n, void **strms_v, int flush, 
     }
     return 0;
 }
+
+
+// ---------------------------------------------------------------------------------------------------
+// The remaining zlib entry points of the inflate side (reference src/inflate.c:231-258,
+// 1289-1537).  The stream lives on the device as {phase, resume bit, carried bytes, history}; these functions
+// edit that state (small kernels / copies on the z_stream surface's own CUDA stream) and the host mirror.
+// Where the reference's bit-granular state cannot be expressed (inflatePrime in the middle of a block header
+// or symbol) the call answers Z_STREAM_ERROR; include/zsb.h lists those cases.
+// ---------------------------------------------------------------------------------------------------
+namespace zsb {
+// history <- (history ++ dict)[-HIST:], and the window accounting of updatewindow() (src/inflate.c:375-419)
+__global__ void __launch_bounds__(CHK_THREADS) k_zs_setdict(zs::State *S, uint8_t *hist, const uint8_t *dict, uint32_t n, int leave_dict_mode) {
+    const int tid = threadIdx.x;
+    if (n >= zs::HIST) {
+        for (uint32_t i = tid; i < zs::HIST; i += CHK_THREADS) hist[i] = dict[n - zs::HIST + i];
+    } else {
+        // shift down by n in chunks (a chunk is read completely before it is written)
+        for (uint32_t c0 = 0; c0 < zs::HIST - n; c0 += CHK_THREADS) {
+            const uint32_t i = c0 + tid;
+            uint8_t v = 0;
+            if (i < zs::HIST - n) v = hist[i + n];
+            __syncthreads();
+            if (i < zs::HIST - n) hist[i] = v;
+            __syncthreads();
+        }
+        for (uint32_t i = tid; i < n; i += CHK_THREADS) hist[zs::HIST - n + i] = dict[i];
+    }
+    if (tid == 0) {
+        S->wsize = 1u << (S->wbits ? S->wbits : 15u);
+        const uint64_t h = (uint64_t)S->whave + n;
+        S->whave = h > S->wsize ? S->wsize : (uint32_t)h;
+        S->call.whave = S->whave;
+        if (leave_dict_mode) {               // mode DICT -> the next inflate() enters TYPE (src/inflate.c:822-830)
+            S->phase = zs::PH_DICTSET;
+            S->kind = 1;
+            S->check = 1;                    // adler32(0L, Z_NULL, 0)
+            S->bit0 = 0;
+        }
+    }
+}
+}  // namespace zsb
+
+namespace {
+// one word of the device State
+template <typename T> bool zs_poke(ZStream *z, size_t offset, const T &v) {
+    return cudaMemcpyAsync((uint8_t *)z->d_state + offset, &v, sizeof(T), cudaMemcpyHostToDevice, g_zs.st) == cudaSuccess &&
+           cudaStreamSynchronize(g_zs.st) == cudaSuccess;
+}
+struct ZsDeviceGuard {                     // the z_stream surface runs on the context's first device
+    int cur = 0, dev = 0;
+    ZsDeviceGuard() {
+        cudaGetDevice(&cur);
+        dev = g_zs.ctx->devs[0].device;
+        if (cur != dev) cudaSetDevice(dev);
+    }
+    ~ZsDeviceGuard() {
+        if (cur != dev) cudaSetDevice(cur);
+    }
+};
+}  // namespace
+
+extern "C" {
+
+// reference src/inflate.c:1309-1339
+ZSB_API int inflateSetDictionary(z_streamp strm, const Bytef *dictionary, uInt dictLength) {
+    using namespace zsb;
+    ZsHandle *h = zs_handle(strm);
+    if (!h) return Z_STREAM_ERROR;
+    ZStream *z = h->zs;
+    if (z->wrap != 0 && z->phase != zs::PH_NEEDDICT) return Z_STREAM_ERROR;
+    if (z->phase == zs::PH_NEEDDICT && zs_adler32(dictionary, dictLength) != z->dictid) return Z_DATA_ERROR;
+    std::lock_guard<std::mutex> lk(g_zs.mu);
+    ZsDeviceGuard dg;
+    // only the last 64 KiB can ever be referenced
+    const uint32_t n = dictLength > zs::HIST ? zs::HIST : dictLength;
+    const Bytef *src = dictionary + (dictLength - n);
+    bool ok = n == 0 || cudaMemcpyAsync(g_zs.d_in, src, n, cudaMemcpyHostToDevice, g_zs.st) == cudaSuccess;
+    if (ok) {
+        // (dictLength, not n, feeds the accounting: whave saturates at the window size either way)
+        k_zs_setdict<<<1, CHK_THREADS, 0, g_zs.st>>>(z->d_state, z->d_hist, g_zs.d_in, n, z->phase == zs::PH_NEEDDICT);
+        ok = cudaGetLastError() == cudaSuccess &&
+             cudaMemcpyAsync(g_zs.h_call, &z->d_state->call, sizeof(zs::Call), cudaMemcpyDeviceToHost, g_zs.st) == cudaSuccess &&
+             cudaStreamSynchronize(g_zs.st) == cudaSuccess;
+    }
+    if (!ok) {
+        cudaGetLastError();
+        z->phase = zs::PH_BAD;
+        return Z_MEM_ERROR;
+    }
+    z->whave = g_zs.h_call->whave;
+    if (z->phase == zs::PH_NEEDDICT) {
+        z->phase = zs::PH_DICTSET;
+        z->kind = 1;
+        z->header_seen = true;
+    }
+    return Z_OK;
+}
+
+// reference src/inflate.c:1289-1307
+ZSB_API int inflateGetDictionary(z_streamp strm, Bytef *dictionary, uInt *dictLength) {
+    using namespace zsb;
+    ZsHandle *h = zs_handle(strm);
+    if (!h) return Z_STREAM_ERROR;
+    ZStream *z = h->zs;
+    if (z->whave && dictionary != Z_NULL) {
+        std::lock_guard<std::mutex> lk(g_zs.mu);
+        ZsDeviceGuard dg;
+        if (cudaMemcpyAsync(dictionary, z->d_hist + (zs::HIST - z->whave), z->whave, cudaMemcpyDeviceToHost, g_zs.st) != cudaSuccess ||
+            cudaStreamSynchronize(g_zs.st) != cudaSuccess) {
+            cudaGetLastError();
+            return Z_MEM_ERROR;
+        }
+    }
+    if (dictLength != Z_NULL) *dictLength = z->whave;
+    return Z_OK;
+}
+
+// reference src/inflate.c:1341-1354
+ZSB_API int inflateGetHeader(z_streamp strm, gz_headerp head) {
+    ZsHandle *h = zs_handle(strm);
+    if (!h) return Z_STREAM_ERROR;
+    if ((h->zs->wrap & 2) == 0) return Z_STREAM_ERROR;
+    h->zs->head = head;
+    head->done = 0;
+    return Z_OK;
+}
+
+// reference src/inflate.c:1386-1434 (syncsearch :1368-1384)
+ZSB_API int inflateSync(z_streamp strm) {
+    using namespace zsb;
+    ZsHandle *h = zs_handle(strm);
+    if (!h) return Z_STREAM_ERROR;
+    ZStream *z = h->zs;
+    if (strm->avail_in == 0 && z->held_bits < 8) return Z_BUF_ERROR;
+    auto search = [&](const uint8_t *buf, unsigned len) {
+        unsigned got = z->sync_have, next = 0;
+        while (next < len && got < 4) {
+            if (buf[next] == (got < 2 ? 0 : 0xff)) got++;
+            else if (buf[next]) got = 0;
+            else got = 4 - got;
+            next++;
+        }
+        z->sync_have = got;
+        return next;
+    };
+    if (!z->in_sync) {                       // first time: the whole bytes still in the bit buffer are searched first
+        z->in_sync = true;
+        z->sync_have = 0;
+        const uint32_t nb = z->held_bits >> 3;
+        if (nb && z->carry_shadow.size() >= nb) search(z->carry_shadow.data() + (z->carry_shadow.size() - nb), nb);
+        z->held_bits = 0;
+    }
+    const unsigned len = search(strm->next_in, strm->avail_in);
+    strm->avail_in -= len;
+    strm->next_in += len;
+    strm->total_in += len;
+    if (z->sync_have != 4) return Z_DATA_ERROR;
+    // found: restart at a block boundary; no header yet -> raw, else the wrapper stays but its check is not computed
+    const bool header_seen = z->header_seen;
+    const uint32_t kind = header_seen ? z->kind : 0;
+    if (!header_seen) z->wrap = 0;
+    else z->wrap &= ~4;
+    const uLong in = strm->total_in, out = strm->total_out;
+    int wrap_unused, d64, wbits;
+    zs_decode_wbits(z->wbits_arg, wrap_unused, d64, wbits);
+    strm->total_in = strm->total_out = 0;
+    strm->msg = Z_NULL;
+    if (z->wrap) strm->adler = (uLong)(z->wrap & 1);
+    const int saved_wrap = z->wrap;
+    if (zs_reset_device(z, z->wbits_arg, d64, wbits) != Z_OK) return Z_MEM_ERROR;
+    z->wrap = saved_wrap;
+    z->header_seen = header_seen;
+    z->kind = kind;
+    strm->total_in = in;
+    strm->total_out = out;
+    {
+        std::lock_guard<std::mutex> lk(g_zs.mu);
+        ZsDeviceGuard dg;
+        struct { uint32_t phase, bit0, last, d64; int32_t wbits_arg; uint32_t kind; } head6 = {zs::PH_BLOCK, 0u, 0u, (uint32_t)d64, z->wbits_arg, kind};
+        bool ok = cudaMemcpyAsync(z->d_state, &head6, sizeof head6, cudaMemcpyHostToDevice, g_zs.st) == cudaSuccess;
+        const uint32_t one = 1, chk = (uint32_t)(z->wrap & 1);
+        ok = ok && zs_poke(z, offsetof(zs::State, noverify), one) && zs_poke(z, offsetof(zs::State, check), chk);
+        if (!ok) {
+            cudaGetLastError();
+            return Z_MEM_ERROR;
+        }
+    }
+    z->phase = zs::PH_BLOCK;
+    return Z_OK;
+}
+
+// reference src/inflate.c:1444-1450
+ZSB_API int inflateSyncPoint(z_streamp strm) {
+    ZsHandle *h = zs_handle(strm);
+    if (!h) return Z_STREAM_ERROR;
+    return (int)h->zs->sync_point;
+}
+
+// reference src/inflate.c:1452-1492
+ZSB_API int inflateCopy(z_streamp dest, z_streamp source) {
+    using namespace zsb;
+    ZsHandle *hs = zs_handle(source);
+    if (!hs || dest == Z_NULL) return Z_STREAM_ERROR;
+    ZsHandle *hd = (ZsHandle *)source->zalloc(source->opaque, 1, sizeof(ZsHandle));
+    if (hd == nullptr) return Z_MEM_ERROR;
+    ZStream *z = new (std::nothrow) ZStream(*hs->zs);
+    bool ok = z != nullptr;
+    if (ok) {
+        z->d_state = nullptr; z->d_hist = nullptr; z->d_carry = nullptr;
+        std::lock_guard<std::mutex> lk(g_zs.mu);
+        ZsDeviceGuard dg;
+        ok = cudaMalloc(&z->d_state, sizeof(zs::State)) == cudaSuccess && cudaMalloc(&z->d_hist, zs::HIST) == cudaSuccess &&
+             cudaMalloc(&z->d_carry, ZS_CARRY_CAP) == cudaSuccess &&
+             cudaMemcpyAsync(z->d_state, hs->zs->d_state, sizeof(zs::State), cudaMemcpyDeviceToDevice, g_zs.st) == cudaSuccess &&
+             cudaMemcpyAsync(z->d_hist, hs->zs->d_hist, zs::HIST, cudaMemcpyDeviceToDevice, g_zs.st) == cudaSuccess &&
+             cudaMemcpyAsync(z->d_carry, hs->zs->d_carry, ZS_CARRY_CAP, cudaMemcpyDeviceToDevice, g_zs.st) == cudaSuccess &&
+             cudaStreamSynchronize(g_zs.st) == cudaSuccess;
+        if (!ok) {
+            cudaGetLastError();
+            cudaFree(z->d_state); cudaFree(z->d_hist); cudaFree(z->d_carry);
+        }
+    }
+    if (!ok) {
+        delete z;
+        source->zfree(source->opaque, hd);
+        return Z_MEM_ERROR;
+    }
+    memcpy((void *)dest, (const void *)source, sizeof(z_stream));
+    hd->strm = dest;
+    hd->magic = ZS_MAGIC;
+    hd->zs = z;
+    dest->state = (struct internal_state *)hd;
+    return Z_OK;
+}
+
+// reference src/inflate.c:231-248.  Bits are inserted in front of the input still to come; the carried bytes are
+// rewritten so that they end with the reference's bit buffer followed by the new bits.  That needs the carried bytes
+// to BE the bit buffer (a stream at a block boundary, at its start, or primed before): in the middle of a block
+// header or symbol the unit is decoded again from its first bit here, and the call answers Z_STREAM_ERROR.
+ZSB_API int inflatePrime(z_streamp strm, int bits, int value) {
+    using namespace zsb;
+    ZsHandle *h = zs_handle(strm);
+    if (!h) return Z_STREAM_ERROR;
+    if (bits == 0) return Z_OK;
+    ZStream *z = h->zs;
+    if (z->wrap && z->phase == zs::PH_HEAD && !z->header_seen) return Z_STREAM_ERROR;   // (a wrapper header is parsed bytewise here)
+    const uint32_t held = z->held_bits;
+    const bool exact = (uint64_t)z->carry_len * 8 - z->bit0 == held && z->carry_shadow.size() == z->carry_len;
+    uint64_t hold = 0;
+    uint32_t nbits = held;
+    if (bits < 0) {
+        if (!exact && held) return Z_STREAM_ERROR;
+        nbits = 0;
+    } else {
+        if (bits > 16 || held + (uInt)bits > 32) return Z_STREAM_ERROR;
+        if (!exact) return Z_STREAM_ERROR;
+        for (uint32_t i = 0; i < z->carry_len; i++) hold |= (uint64_t)z->carry_shadow[i] << (8 * i);
+        hold >>= z->bit0;
+        hold |= (uint64_t)((unsigned)value & ((1u << bits) - 1u)) << held;
+        nbits = held + (uint32_t)bits;
+    }
+    // the new carried bytes: nbits bits ending at a byte boundary
+    const uint32_t nbytes = (nbits + 7) / 8, bit0 = nbytes * 8 - nbits;
+    std::vector<uint8_t> nc(nbytes);
+    const uint64_t v = hold << bit0;
+    for (uint32_t i = 0; i < nbytes; i++) nc[i] = (uint8_t)(v >> (8 * i));
+    std::lock_guard<std::mutex> lk(g_zs.mu);
+    ZsDeviceGuard dg;
+    bool ok = nbytes == 0 || cudaMemcpyAsync(z->d_carry, nc.data(), nbytes, cudaMemcpyHostToDevice, g_zs.st) == cudaSuccess;
+    ok = ok && zs_poke(z, offsetof(zs::State, bit0), bit0);
+    if (!ok) {
+        cudaGetLastError();
+        return Z_MEM_ERROR;
+    }
+    z->carry_shadow.swap(nc);
+    z->carry_len = nbytes;
+    z->bit0 = bit0;
+    z->held_bits = nbits;
+    return Z_OK;
+}
+
+// reference src/inflate.c:1494-1507: built without INFLATE_ALLOW_INVALID_DISTANCE_TOOFAR_ARRR, as the reference is
+ZSB_API int inflateUndermine(z_streamp strm, int subvert) {
+    (void)subvert;
+    return zs_handle(strm) ? Z_DATA_ERROR : Z_STREAM_ERROR;
+}
+
+// reference src/inflate.c:1509-1519
+ZSB_API int inflateValidate(z_streamp strm, int check) {
+    using namespace zsb;
+    ZsHandle *h = zs_handle(strm);
+    if (!h) return Z_STREAM_ERROR;
+    ZStream *z = h->zs;
+    if (check && z->wrap) z->wrap |= 4;
+    else z->wrap &= ~4;
+    const uint32_t nv = (z->wrap & 4) ? 0u : 1u;
+    std::lock_guard<std::mutex> lk(g_zs.mu);
+    ZsDeviceGuard dg;
+    if (!zs_poke(z, offsetof(zs::State, noverify), nv)) {
+        cudaGetLastError();
+        return Z_MEM_ERROR;
+    }
+    return Z_OK;
+}
+
+// reference src/inflate.c:1521-1530
+ZSB_API long inflateMark(z_streamp strm) {
+    ZsHandle *h = zs_handle(strm);
+    if (!h) return -(1L << 16);
+    return h->zs->mark;
+}
+
+// reference src/inflate.c:1532-1537
+ZSB_API unsigned long inflateCodesUsed(z_streamp strm) {
+    ZsHandle *h = zs_handle(strm);
+    if (!h) return (unsigned long)-1;
+    return h->zs->codes_used;
+}
+
+}  // extern "C"
