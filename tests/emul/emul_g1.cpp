@@ -237,7 +237,7 @@ extern "C" int emulzs_step(void *hh, const uint8_t *in, size_t in_len_new, uint8
     if (z->S.kind && prod) check = z->S.kind == 2 ? emul_crc(check, w + zs::HIST, prod) : emul_adler(check, w + zs::HIST, prod);
     zs::finish_call(z->S, ib, len, check, flush == 4);
     const zs::Call c = z->S.call;
-    memcpy(z->hist.data(), w + prod, zs::HIST);
+    memcpy(z->hist.data(), w + c.wprod, zs::HIST);
     if (prod) memcpy(out, w + zs::HIST, prod);
     uint32_t cpos = c.cpos;
     if (c.stop == EV_NEEDDICT) cpos = len < 6 ? len : 6;
@@ -261,4 +261,13 @@ extern "C" int emulzs_step(void *hh, const uint8_t *in, size_t in_len_new, uint8
     z->last_dt = c.data_type & 0x7fu;
     if (((used == 0 && made == 0) || flush == 4) && ret == 0) ret = -5;
     return fill();
+}
+
+// what inflateMark() / inflateCodesUsed() / inflateSyncPoint() report after the last emulzs_step (zs::Call)
+extern "C" void emulzs_aux(void *hh, long *out3) {
+    EmulZs *z = (EmulZs *)hh;
+    const bool fresh = z->total_in == 0 && z->total_out == 0 && z->S.phase == zsb::zs::PH_HEAD && z->carry_len == 0 && z->S.call.cpos == 0;
+    out3[0] = fresh ? -65536 : (long)z->S.call.mark;
+    out3[1] = (long)z->S.call.codes_used;
+    out3[2] = (long)z->S.call.sync_point;
 }

@@ -21,10 +21,30 @@ if __import__("os").environ.get("ZSB_AUX_SELFTEST"):     # harness check without
 needs_ref = pytest.mark.skipif(REF is None, reason="oracle/_ref not built")
 
 
-def both(fn):
+def first_diff(a, b, path=""):
+    """Path and values of the first leaf where two nested observations differ."""
+    if type(a) != type(b):
+        return "%s: %r != %r" % (path, a, b)
+    if isinstance(a, (list, tuple)):
+        if len(a) != len(b):
+            return "%s: lengths %d != %d (%r ... | %r ...)" % (path, len(a), len(b), a[-1:], b[-1:])
+        for i, (x, y) in enumerate(zip(a, b)):
+            if x != y:
+                return first_diff(x, y, "%s[%d]" % (path, i))
+    if isinstance(a, dict):
+        for k in a:
+            if a[k] != b.get(k):
+                return first_diff(a[k], b.get(k), "%s[%r]" % (path, k))
+    if isinstance(a, bytes) and a != b:
+        i = next((i for i, (x, y) in enumerate(zip(a, b)) if x != y), min(len(a), len(b)))
+        return "%s: bytes differ at %d of %d/%d: %r != %r" % (path, i, len(a), len(b), a[i:i + 12], b[i:i + 12])
+    return "%s: %r != %r" % (path, a, b)
+
+
+def both(fn, what=""):
     """Run fn(lib) on the reference and on the product; the two observations must be equal."""
     a, b = fn(REF), fn(ZSB)
-    assert a == b, (a if len(repr(a)) < 2000 else "reference", b if len(repr(b)) < 2000 else "product")
+    assert a == b, "%s reference != product at %s" % (what, first_diff(a, b))
     return b
 
 
@@ -45,7 +65,7 @@ def test_mark_codes_used_sync_point_after_every_call():
                 t, out = z.drive(data, chunks, ocap, flush=flush, max_calls=40000)
                 z.end()
                 return t, out
-            both(run)
+            both(run, "%s wb=%d flush=%d chunks=%r ocap=%d" % (name, wb, flush, chunks, ocap))
 
 
 @needs_ref

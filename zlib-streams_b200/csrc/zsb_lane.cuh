@@ -588,6 +588,18 @@ ZSB_DEV int lane_dynamic_header(Lane &L, uint8_t *T, const uint32_t *lut) {
         d.msg = M_CLENS;
         return EV_ERR;
     }
+    {   // entries of the reference's table for this code (root 7, src/inftrees.c:126-142): the z_stream surface reports it
+        uint32_t mn = 16, mx = 0;
+        for (uint32_t i = 0; i < 19; i++) {
+            const uint32_t l = T[H_CLL + i];
+            if (l) {
+                mn = l < mn ? l : mn;
+                mx = l > mx ? l : mx;
+            }
+        }
+        const uint32_t root = mx == 0 ? 1u : (7u < mx ? (7u > mn ? 7u : mn) : mx);
+        L.ndist = 0x80000000u | (1u << root);
+    }
     const uint8_t *C = T + H_CL;
     uint32_t have = 0, total = nlen + ndist;
     while (have < total) {

@@ -42,7 +42,8 @@ struct Call {
     uint32_t hdr_len;      // nonzero in the call that completed the zlib / gzip header: its length in bytes
     uint32_t hdr_kind;     // 1 zlib, 2 gzip (with hdr_len)
     uint32_t bit0;         // bit offset of the resume point inside the first carried byte
-    uint32_t pad[3];
+    uint32_t wprod;        // bytes of this call's output that enter the sliding window (see finish_call)
+    uint32_t pad[2];
 };
 
 struct State {
@@ -159,7 +160,12 @@ ZSB_DEV int run_serial(State &S, Lane &L, Run &R, uint8_t *T, const uint32_t *lu
                 return 0;
             }
             if (btype == 2) {
+                L.ndist = 0;
                 const int ev = lane::lane_dynamic_header(L, T, lut);
+                // inflateCodesUsed(): once the code-length code is accepted its table is what the reference holds
+                // (src/inflate.c:933-945), until the two block codes replace it; a rejected one leaves none
+                if (ev != EV_NONE && (L.ndist & 0x80000000u)) S.codes_used = L.ndist & 0xffffu;
+                else if (ev == EV_ERR && d.msg == M_CLENS) S.codes_used = 0;
                 if (ev != EV_NONE) {
                     R.stop = ev;
                     return 0;
@@ -413,10 +419,15 @@ ZSB_DEV void finish_call(State &S, const uint8_t *in, uint32_t in_len, uint32_t 
         S.check = check;
         c.adler = check;
     }
+    // The reference zeroes its per-call output count once it has read the check word of a zlib / gzip trailer
+    // (src/inflate.c:1196-1200: out -= left ... out = left), so what such a call produced before the trailer never
+    // reaches updatewindow() (:1255-1260): neither whave nor the window contents change.
+    bool window_skip = false;
     if (c.need_trailer && c.stop == EV_DONE) {
         uint32_t pos = c.trailer_pos, phase = S.phase;
         bool done = false;
         if (phase == PH_CHECK) {
+            if (in_len - pos >= 4) window_skip = true;
             if (in_len - pos < 4) {
                 c.stop = EV_STARVE; c.cpos = in_len; c.resume_byte = pos; c.data_type = 8 * (in_len - pos) + 64;
                 done = true;
@@ -455,10 +466,13 @@ ZSB_DEV void finish_call(State &S, const uint8_t *in, uint32_t in_len, uint32_t 
     }
     // history the reference would keep (src/inflate.c:1255-1260, 375-419)
     const uint32_t ph = S.phase;
-    if (S.wsize || (produced && ph < PH_BAD && (ph < PH_CHECK || !finish))) {
+    const uint32_t wprod = window_skip ? 0u : produced;
+    c.wprod = 0;
+    if (S.wsize || (wprod && ph < PH_BAD && (ph < PH_CHECK || !finish))) {
         S.wsize = 1u << S.wbits;
-        const uint64_t h = (uint64_t)S.whave + produced;
+        const uint64_t h = (uint64_t)S.whave + wprod;
         S.whave = h > S.wsize ? S.wsize : (uint32_t)h;
+        c.wprod = wprod;
     }
     c.whave = S.whave;
     S.call = c;

@@ -50,7 +50,8 @@ __global__ void __launch_bounds__(CHK_THREADS) k_zs_finish(zs::State *S, uint8_t
         s_cpos = c.cpos;
     }
     __syncthreads();
-    for (uint32_t i = tid; i < zs::HIST; i += CHK_THREADS) hist[i] = w[produced + i];
+    const uint32_t wprod = S->call.wprod;        // (written by thread 0 before the barrier above)
+    for (uint32_t i = tid; i < zs::HIST; i += CHK_THREADS) hist[i] = w[wprod + i];
     uint32_t rb = s_resume, n = s_cpos > s_resume ? s_cpos - s_resume : 0u;
     if (n > ZS_CARRY_LIMIT) n = ZS_CARRY_LIMIT;           // the host answers Z_MEM_ERROR (a gzip header that long)
     for (uint32_t i = tid; i < n; i += CHK_THREADS) carry[i] = in[rb + i];
@@ -111,7 +112,8 @@ __global__ void __launch_bounds__(CHK_THREADS) k_zsm_finish(const ZsJob *jobs, z
         calls[blockIdx.x] = c;
     }
     __syncthreads();
-    for (uint32_t i = tid; i < zs::HIST; i += CHK_THREADS) j.hist[i] = j.w[produced + i];
+    const uint32_t wprod = S->call.wprod;
+    for (uint32_t i = tid; i < zs::HIST; i += CHK_THREADS) j.hist[i] = j.w[wprod + i];
     uint32_t rb = s_resume, n = s_cpos > s_resume ? s_cpos - s_resume : 0u;
     if (n > ZS_CARRY_LIMIT) n = ZS_CARRY_LIMIT;           // the host answers Z_MEM_ERROR (a gzip header that long)
     for (uint32_t i = tid; i < n; i += CHK_THREADS) j.carry[i] = j.in[rb + i];
@@ -279,6 +281,12 @@ void zs_after_round(z_streamp strm, ZStream *z, const zsb::zs::Call &c, uint32_t
     uint32_t cpos = c.cpos;
     if (c.stop == EV_NEEDDICT) cpos = in_len < 6 ? in_len : 6;      // header + dictionary id were read
     auto byte_at = [&](uint32_t i) -> uint8_t { return i < old_carry ? z->carry_shadow[i] : strm->next_in[i - old_carry]; };
+    if (!z->header_seen && z->wrap && in_len >= 2 && !(((z->wrap & 2) && byte_at(0) == 0x1f && byte_at(1) == 0x8b))) {
+        // src/inflate.c:660-664: two bytes that are not the gzip magic are taken for a zlib header, right or wrong
+        z->header_seen = true;
+        z->kind = 1;
+        if (z->head) z->head->done = -1;
+    }
     if (c.hdr_len) {
         z->header_seen = true;
         z->kind = c.hdr_kind;
@@ -313,8 +321,6 @@ void zs_after_round(z_streamp strm, ZStream *z, const zsb::zs::Call &c, uint32_t
                     hd->hcrc = (int)((flg >> 1) & 1);
                     hd->done = 1;
                 }
-            } else {
-                z->head->done = -1;                                            // a zlib header: src/inflate.c:662-664
             }
         }
     }
