@@ -63,7 +63,7 @@ def ref_trace(data, wb, chunks, ocap, flush):
 def test_mark_codes_used_sync_point_traces():
     rnd = random.Random(13)
     pool = [(n, d, w) for n, d, w, p in cases.valid_streams()[1::5]] + [(n, d, -16) for n, d, m in cases.golden_fixtures()[:5]]
-    pool += [(n, d, w) for n, d, w, c in cases.damaged_streams(60)[:60:2]]
+    pool += [(n, d, w) for n, d, w, c in cases.damaged_streams(300)[:300]]
     pool += [(n, d, w) for n, d, w, c, _ in cases.probe_vectors()]
     for name, data, wb in pool:
         for flush in (0, 5, 6):

@@ -10,7 +10,7 @@ import subprocess
 
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 PKG = os.path.join(ROOT, "zlib-streams_b200")
-LIB = os.path.join(PKG, "libzsb.so")
+LIB = os.environ.get("ZSB_LIB") or os.path.join(PKG, "libzsb.so")      # ZSB_LIB: a variant build (experiments)
 EMUL_DIR = os.path.join(ROOT, "tests", "emul")
 
 API_SYMBOLS = ["zsb_create", "zsb_destroy", "zsb_create_error", "zsb_last_error", "zsb_num_devices",

@@ -110,6 +110,7 @@ struct Lane {
     uint32_t mode;       // fast_step: 0 = the next code is a literal/length code, 1 = a distance code
     uint32_t pl;         // fast_step: length of the match whose distance code comes next (mode 1)
     uint32_t ring_sa;    // shared-window address of `ring` (device only)
+    uint32_t pre;        // ZSB_V_PREFETCH: the input word at d.b.next, loaded one refill ahead
     seq_t *q0, *qend;    // k_big: the warp's sequence queue in shared memory (NULL in k_lane); L.seq runs inside it
     uint32_t qbase;      // k_big: output position of the queue's first sequence
 };
@@ -176,6 +177,11 @@ ZSB_DEV void fetch_word(const Lane &L, uint32_t off) {
 }
 ZSB_DEV void prime(Lane &L) {
     const BitIn &b = L.d.b;
+#if ZSB_V_PREFETCH
+    L.pre = 0;
+    if ((((uintptr_t)(b.p + b.next)) & 3) == 0 && b.next + 4 <= b.len) L.pre = __ldg((const uint32_t *)(b.p + b.next));
+    return;
+#endif
     ZSB_CP_WAIT(0);
     if ((((uintptr_t)(b.p + b.next)) & 3) != 0) return;       // only at the very end of a member
     fetch_word(L, b.next);
@@ -196,9 +202,23 @@ ZSB_DEV uint32_t sym_entry(uint32_t sym) {        // symbol -> entry without the
     return E_INVALID;
 }
 // number of lengths whose limit is at or below c15 (0..15) = code length - 1; 15 = no code
+#ifndef ZSB_V_SPLIT
+#define ZSB_V_SPLIT 0
+#endif
+#ifndef ZSB_V_PREFETCH
+#define ZSB_V_PREFETCH 0
+#endif
 ZSB_DEV uint32_t canon_len(const uint16_t *lim, uint32_t c15) {
+#if ZSB_V_SPLIT
+    // the three splitters of the first two levels are independent loads (their addresses do not depend on the
+    // code): two dependent shared-memory round trips instead of four
+    const uint32_t l7 = lim[7], l3 = lim[3], l11 = lim[11];
+    uint32_t k = c15 >= l7 ? 8u : 0u;
+    k += c15 >= (k ? l11 : l3) ? 4u : 0u;
+#else
     uint32_t k = c15 >= lim[7] ? 8u : 0u;
     k += c15 >= lim[k + 3] ? 4u : 0u;
+#endif
     k += c15 >= lim[k + 1] ? 2u : 0u;
     k += c15 >= lim[k] ? 1u : 0u;
     return k;
@@ -348,12 +368,22 @@ ZSB_DEV bool fast_step(Lane &L, const uint8_t *T, const uint32_t *lut) {
     BitIn &b = d.b;
     // ---- refill: 32 more bits when fewer than 32 are held; the word three ahead is requested ----
     const bool need = b.nbits < 32;
+#if ZSB_V_PREFETCH
+    // the word at b.next was requested at the previous refill; the loop's entry condition (8 more input bytes)
+    // makes the next word readable
+    const uint32_t rw = L.pre;
+    b.hold |= need ? (uint64_t)rw << b.nbits : 0ull;
+    b.nbits += need ? 32u : 0u;
+    b.next += need ? 4u : 0u;
+    if (need) L.pre = __ldg((const uint32_t *)(b.p + b.next));
+#else
     ZSB_CP_WAIT(2);
     const uint32_t rw = ring_load(L, b.next & 12u);
     fetch_word_if(L, need, b.next + 12);
     b.hold |= need ? (uint64_t)rw << b.nbits : 0ull;
     b.nbits += need ? 32u : 0u;
     b.next += need ? 4u : 0u;
+#endif
     // ---- the code at the head of the buffer, in the lane's current code (mask arithmetic, no branch) ----
     const uint32_t w = (uint32_t)b.hold;
     const uint32_t m = 0u - L.mode;                                // ~0 in distance mode

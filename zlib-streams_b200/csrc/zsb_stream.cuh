@@ -77,6 +77,8 @@ struct Run {               // lane 0's bookkeeping during one call
     uint32_t hdr_tin, hdr_bits;
     const uint32_t *big_lut;   // direct tables of the current block (lane::big_build), or NULL
     uint32_t sync_point;
+    uint64_t first_bit;        // bit position this call resumed at
+    bool resumed_partial;      // ... inside a symbol whose first codes the reference has consumed already (state->back > 0)
     uint32_t hdr_len, hdr_kind;
     uint32_t flush_mode;       // 0, FL_BLOCK (inflate(Z_BLOCK)) or FL_TREES (inflate(Z_TREES))
 };
@@ -253,12 +255,20 @@ ZSB_DEV int run_serial(State &S, Lane &L, Run &R, uint8_t *T, const uint32_t *lu
         case PH_SYM: {
             // plain literals and whole matches through the direct tables (the loop of k_big); it stops at a
             // symbol boundary, and whatever stopped it is decoded by the checked path below
-            if (R.big_lut) lane::big_run(L, T, lut, R.big_lut);
+            // (a symbol the previous call was cut in goes through the checked path: the reference finishes it on its slow
+            //  path, and what that leaves in state->back outlives the inflate_fast() run that follows)
+            if (R.big_lut && !(R.resumed_partial && bitpos(b) == R.first_bit)) lane::big_run(L, T, lut, R.big_lut);
             R.unit = bitpos(b);
+            // Would the reference decode this symbol inside inflate_fast() (src/inflate.c:1038-1044: at least 6 input
+            // bytes and 258 bytes of room at the symbol's start, never in Deflate64 mode)?  Its bit buffer holds less
+            // than a byte between symbols on both paths, so the input left is a function of the bit position.
+            // (a symbol cut by the end of the previous call's input is finished on the slow path: modes LENEXT / DIST / DISTEXT)
+            const bool fastsym = !S.d64 && b.len - (uint32_t)((R.unit + 7) >> 3) >= 6u && d.cap - d.pos >= 258u &&
+                                 !(R.resumed_partial && R.unit == R.first_bit);
             const int ev = lane::careful_symbol(d, T, lut);
             // the bits of this symbol's codes consumed so far: what the reference keeps in state->back
-            // (src/inflate.c:1046-1142); a symbol the direct-table loop took whole leaves no trace, as inflate_fast()
-            S.back = (int32_t)(bitpos(b) - R.unit);
+            // (src/inflate.c:1046-1142); inflate_fast() does not touch it, whatever it runs into
+            if (!fastsym) S.back = (int32_t)(bitpos(b) - R.unit);
             if (ev == EV_LIT) {
                 S.plit = d.mdist;
                 R.phase = PH_PENDLIT;
@@ -304,6 +314,8 @@ ZSB_DEV void stream_decode(State &S, const uint8_t *in, uint32_t in_len, uint32_
     L.seq = L.seq0 = seq; L.lw = 0; L.nl = 0; L.ring = ring; L.hist = S.whave; L.nlen = 0; L.ndist = 0;
     R.phase = S.phase; R.unit = 0; R.stop = EV_NONE; R.last0 = S.last; R.hdr_stop = false; R.hdr_tin = 0; R.hdr_bits = 0;
     if (active && R.phase != PH_HEAD) seek_bit(d.b, S.bit0);
+    R.first_bit = bitpos(d.b);
+    R.resumed_partial = S.phase == PH_SYM && S.back > 0;
     R.big_lut = big_lut;
     R.sync_point = 0;
     R.hdr_len = 0;
