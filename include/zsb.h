@@ -225,6 +225,36 @@ ZSB_API int zsb_gzip_header(const void *in, size_t len, zsb_gz_header *h);
  * ZSB_E_ARG. */
 ZSB_API int zsb_inflate_streams(size_t n, void **strms, int flush, int *rets);
 
+/* ---- batched deflate (compression) on the GPU ----
+ * The compress half of the reference's product: what src/wasm/deflate_stream_wasm.c:22-69 obtains from
+ * deflateInit / deflateInit2(level, Z_DEFLATED, -15 | 15 | 31, 8, Z_DEFAULT_STRATEGY) + deflate(Z_FINISH) +
+ * deflateEnd per stream, for n independent members in one call.  window_bits: -15 raw deflate, 15 zlib, 31 gzip
+ * (the three the reference's glue uses; the window is always 32 KiB); level: 0 = stored blocks, 1..9 or -1 = LZ77 +
+ * Huffman coding (one parameter set; the level only goes into the zlib / gzip header fields).  The output is a
+ * valid stream of the requested format — it decodes to the input with the reference's inflate() — but not the
+ * byte string zlib would produce (compressed streams are not unique).  ret: Z_STREAM_END (1), Z_BUF_ERROR (-5)
+ * when out_cap is too small (zsb_deflate_bound() is always enough), Z_STREAM_ERROR (-2) for parameters outside
+ * the above.  check = Adler-32 (zlib) / CRC-32 (gzip) of the input.  Host or device pointers, as
+ * zsb_inflate_batch; runs on the first device of the context. */
+typedef struct zsb_deflate_member {
+    const void *in;
+    size_t in_len;       /* < 2^32 */
+    void *out;
+    size_t out_cap;
+    int32_t window_bits;
+    int32_t level;
+} zsb_deflate_member;
+typedef struct zsb_deflate_result {
+    int32_t ret;
+    int32_t blocks;      /* 64 KiB input blocks the member was cut into (each compressed by one warp) */
+    uint64_t total_in;
+    uint64_t total_out;
+    uint32_t check;
+    uint32_t reserved;
+} zsb_deflate_result;
+ZSB_API int zsb_deflate_batch(zsb_ctx *ctx, size_t n, const zsb_deflate_member *members, zsb_deflate_result *results);
+ZSB_API size_t zsb_deflate_bound(size_t in_len, int window_bits);
+
 #define ZSB_E_ZIP   (-103)
 #define ZSB_E_ARG   (-100)
 #define ZSB_E_CUDA  (-101)

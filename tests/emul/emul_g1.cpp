@@ -29,6 +29,8 @@ static inline unsigned __ballot_sync(unsigned, bool p) { return p; }
 static inline int __ffs(unsigned x) { return __builtin_ffs((int)x); }
 static inline unsigned __match_any_sync(unsigned, uint32_t) { return 1u; }
 static inline int __popc(unsigned x) { return __builtin_popcount(x); }
+static inline int __clz(int x) { return x ? __builtin_clz((unsigned)x) : 32; }
+#define ZSB_SMEM_OR(p, v) (*(p) |= (v))
 #define ZSB_CP4(sdst, gsrc) (*(sdst) = *(const uint32_t *)(gsrc))
 #define ZSB_CP_COMMIT() ((void)0)
 #define ZSB_CP_WAIT(n) ((void)0)
@@ -270,4 +272,50 @@ extern "C" void emulzs_aux(void *hh, long *out3) {
     out3[0] = fresh ? -65536 : (long)z->S.call.mark;
     out3[1] = (long)z->S.call.codes_used;
     out3[2] = (long)z->S.call.sync_point;
+}
+
+// ---------------------------------------------------------------------------------------------------
+// The deflate (compression) device code (zsb_deflate.cuh) with a warp of one lane: blocks of 64 KiB, then the
+// wrapper exactly as k_dstitch writes it.  Returns the stream length, or -1 when out_cap is too small.
+// ---------------------------------------------------------------------------------------------------
+#include "../../zlib-streams_b200/csrc/zsb_deflate.cuh"
+extern "C" long emul_deflate(const uint8_t *in, size_t in_len, uint8_t *out, size_t out_cap, int wbits, int level) {
+    using namespace zsb;
+    std::vector<uint8_t> sm(df::D_BYTES + 64);
+    std::vector<uint32_t> tok(df::BLK + 64);
+    std::vector<uint8_t> inbuf(in_len + 16, 0);            // (word reads look up to 3 bytes past the end)
+    memcpy(inbuf.data(), in, in_len);
+    const uint32_t kind = wbits < 0 ? 0u : wbits > 15 ? 2u : 1u;
+    std::vector<uint8_t> o;
+    if (kind == 1) {
+        const uint32_t fl = level < 0 ? 2u : level < 2 ? 0u : level < 6 ? 1u : level == 6 ? 2u : 3u;
+        uint32_t h16 = (0x78u << 8) | (fl << 6);
+        h16 += 31 - h16 % 31;
+        o.push_back((uint8_t)(h16 >> 8));
+        o.push_back((uint8_t)h16);
+    } else if (kind == 2) {
+        const uint8_t g[10] = {0x1f, 0x8b, 8, 0, 0, 0, 0, 0, (uint8_t)(level == 9 ? 2 : level == 1 ? 4 : 0), 3};
+        o.insert(o.end(), g, g + 10);
+    }
+    const size_t nblk = in_len ? (in_len + df::BLK - 1) / df::BLK : 1;
+    std::vector<uint32_t> scratch((df::BLK + 128) / 4);
+    for (size_t b = 0; b < nblk; b++) {
+        const uint32_t start = (uint32_t)(b * df::BLK);
+        const uint32_t n = (uint32_t)(in_len - start < df::BLK ? in_len - start : df::BLK);
+        memset(scratch.data(), 0xEE, scratch.size() * 4);
+        const uint32_t nb = df::deflate_block<1>(sm.data(), inbuf.data(), in_len, start, n, b + 1 == nblk, level, tok.data(),
+                                                 (uint8_t *)scratch.data(), 0);
+        o.insert(o.end(), (uint8_t *)scratch.data(), (uint8_t *)scratch.data() + nb);
+    }
+    if (kind == 1) {
+        const uint32_t a = emul_adler(1, in, in_len);
+        for (int i = 3; i >= 0; i--) o.push_back((uint8_t)(a >> (8 * i)));
+    } else if (kind == 2) {
+        const uint32_t c = emul_crc(0, in, in_len);
+        for (int i = 0; i < 4; i++) o.push_back((uint8_t)(c >> (8 * i)));
+        for (int i = 0; i < 4; i++) o.push_back((uint8_t)((uint32_t)in_len >> (8 * i)));
+    }
+    if (o.size() > out_cap) return -1;
+    memcpy(out, o.data(), o.size());
+    return (long)o.size();
 }

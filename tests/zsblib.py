@@ -13,7 +13,7 @@ PKG = os.path.join(ROOT, "zlib-streams_b200")
 LIB = os.environ.get("ZSB_LIB") or os.path.join(PKG, "libzsb.so")      # ZSB_LIB: a variant build (experiments)
 EMUL_DIR = os.path.join(ROOT, "tests", "emul")
 
-API_SYMBOLS = ["zsb_create", "zsb_destroy", "zsb_create_error", "zsb_last_error", "zsb_num_devices",
+API_SYMBOLS = ["zsb_deflate_batch", "zsb_deflate_bound", "zsb_create", "zsb_destroy", "zsb_create_error", "zsb_last_error", "zsb_num_devices",
                "zsb_inflate_batch", "zsb_inflate_batch_device", "zsb_set_option", "zsb_get_option",
                "zsb_last_launches", "zsb_plan_shards", "zsb_host_alloc", "zsb_host_free", "zsb_message",
                "zsb_profile_read", "zsb_zip_scan", "zsb_zip_members", "zsb_zip_inflate", "zsb_gunzip_files", "zsb_plan_big", "zsb_inflate_streams", "zsb_gzip_header"]
@@ -40,6 +40,16 @@ class Result(ctypes.Structure):
 
     def __repr__(self):
         return "Result(ret=%d msg=%d in=%d out=%d check=%08x dt=%d)" % self.astuple()
+
+
+class DeflateMember(ctypes.Structure):
+    _fields_ = [("inp", ctypes.c_void_p), ("in_len", ctypes.c_size_t), ("out", ctypes.c_void_p),
+                ("out_cap", ctypes.c_size_t), ("window_bits", ctypes.c_int32), ("level", ctypes.c_int32)]
+
+
+class DeflateResult(ctypes.Structure):
+    _fields_ = [("ret", ctypes.c_int32), ("blocks", ctypes.c_int32), ("total_in", ctypes.c_uint64),
+                ("total_out", ctypes.c_uint64), ("check", ctypes.c_uint32), ("reserved", ctypes.c_uint32)]
 
 
 class ZipEntry(ctypes.Structure):
@@ -99,6 +109,9 @@ def load_product():
                                     ctypes.c_void_p, ctypes.c_void_p]
     lib.zsb_plan_big.restype = ctypes.c_size_t
     lib.zsb_plan_big.argtypes = [ctypes.c_size_t, ctypes.c_void_p, ctypes.c_void_p, ctypes.c_int]
+    lib.zsb_deflate_batch.argtypes = [ctypes.c_void_p, ctypes.c_size_t, ctypes.c_void_p, ctypes.c_void_p]
+    lib.zsb_deflate_bound.restype = ctypes.c_size_t
+    lib.zsb_deflate_bound.argtypes = [ctypes.c_size_t, ctypes.c_int]
     lib.zsb_profile_read.restype = ctypes.c_long
     lib.zsb_profile_read.argtypes = [ctypes.c_void_p, ctypes.c_int, ctypes.POINTER(ctypes.c_double),
                                      ctypes.POINTER(ctypes.c_double)]
@@ -166,6 +179,24 @@ class Zsb:
         if rc:
             raise RuntimeError("zsb_inflate_batch rc=%d: %s" % (rc, self.error()))
         return [(res[i], outs[i].raw[:min(res[i].total_out, out_caps[i])]) for i in range(n)]
+
+
+def deflate_batch(eng, plains, wbits, levels, caps=None):
+    """zsb_deflate_batch over host buffers -> [(DeflateResult, compressed bytes)]."""
+    n = len(plains)
+    ins = [ctypes.create_string_buffer(p, max(len(p), 1)) for p in plains]
+    caps = caps or [eng.lib.zsb_deflate_bound(len(p), w) for p, w in zip(plains, wbits)]
+    outs = [ctypes.create_string_buffer(max(c, 1)) for c in caps]
+    arr = (DeflateMember * n)()
+    for i in range(n):
+        arr[i].inp, arr[i].in_len = ctypes.addressof(ins[i]), len(plains[i])
+        arr[i].out, arr[i].out_cap = ctypes.addressof(outs[i]), caps[i]
+        arr[i].window_bits, arr[i].level = wbits[i], levels[i]
+    res = (DeflateResult * n)()
+    rc = eng.lib.zsb_deflate_batch(eng.ctx, n, arr, res)
+    if rc:
+        raise RuntimeError("zsb_deflate_batch rc=%d: %s" % (rc, eng.error()))
+    return [(res[i], outs[i].raw[:res[i].total_out]) for i in range(n)]
 
 
 class Emul:

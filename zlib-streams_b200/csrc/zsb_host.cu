@@ -621,6 +621,7 @@ static void free_device(zsb_dev &dv) {
     cudaFree(dv.d_in);
     cudaFree(dv.d_out);
     cudaFree(dv.d_desc);
+    cudaFree(dv.d_df);
     if (dv.h_desc) cudaFreeHost(dv.h_desc);
     for (cudaEvent_t e : dv.prof_ev) cudaEventDestroy(e);
     dv.prof_ev.clear();
@@ -1225,6 +1226,132 @@ extern "C" int zsb_inflate_batch(zsb_ctx *ctx, size_t n, const zsb_member *m, zs
 
 // the ZIP container walker (zsb_zip_scan / zsb_zip_members / zsb_zip_inflate)
 #include "zsb_zip.cuh"
+
+// ---- batched deflate (zsb_deflate_batch): blocks of 64 KiB, a warp each (zsb_deflate.cuh) ----------------------
+#include "zsb_deflate.cuh"
+
+extern "C" size_t zsb_deflate_bound(size_t in_len, int window_bits) {
+    const size_t blocks = in_len / df::BLK + 1;
+    return in_len + blocks * 16 + (window_bits < 0 ? 0 : window_bits > 15 ? 18 : 6) + 16;
+}
+
+extern "C" int zsb_deflate_batch(zsb_ctx *ctx, size_t n, const zsb_deflate_member *m, zsb_deflate_result *r) {
+    static_assert(sizeof(df::Member) == sizeof(zsb_deflate_member) && sizeof(DfResult) == sizeof(zsb_deflate_result), "ABI");
+    if (!ctx || (n && (!m || !r))) return ZSB_E_ARG;
+    if (n == 0) return 0;
+    if (n > 0x7fffffffull) return ZSB_E_ARG;
+    int cur = 0;
+    cudaGetDevice(&cur);
+    zsb_dev &dv = ctx->devs[0];
+    struct Restore { int cur; ~Restore() { cudaSetDevice(cur); } } restore{cur};
+    CK(ctx, cudaSetDevice(dv.device));
+    bool device_ptrs = false;
+    for (size_t i = 0; i < n; i++) {
+        const void *p = m[i].in ? m[i].in : m[i].out;
+        if (!p) continue;
+        cudaPointerAttributes at;
+        if (cudaPointerGetAttributes(&at, p) == cudaSuccess) device_ptrs = at.type == cudaMemoryTypeDevice || at.type == cudaMemoryTypeManaged;
+        else cudaGetLastError();
+        break;
+    }
+    auto valid = [](const zsb_deflate_member &x) {
+        return (x.window_bits == -15 || x.window_bits == 15 || x.window_bits == 31) && x.level >= -1 && x.level <= 9 &&
+               x.in_len <= 0xfffffff0ull && (x.in || !x.in_len) && (x.out || !x.out_cap);
+    };
+    // plan: members -> blocks, scratch offsets, staging offsets
+    std::vector<df::Member> hm(n);
+    std::vector<uint32_t> first(n + 1, 0);
+    std::vector<df::Block> hb;
+    std::vector<size_t> in_off(n, 0), out_off(n, 0);
+    size_t scratch = 0, in_total = 0, out_total = 0;
+    for (size_t i = 0; i < n; i++) {
+        memcpy(&hm[i], &m[i], sizeof(df::Member));
+        first[i] = (uint32_t)hb.size();
+        const bool ok = valid(m[i]);
+        if (!ok) {
+            hm[i].in_len = 0;
+            hm[i].out_cap = 0;
+            hm[i].window_bits = -15;
+            hm[i].level = 6;
+        }
+        in_off[i] = in_total;
+        out_off[i] = out_total;
+        in_total += (hm[i].in_len + 19) & ~(size_t)15;          // (3 bytes of slack behind every input: word reads)
+        out_total += (hm[i].out_cap + 15) & ~(size_t)15;
+        if (!ok) continue;
+        const uint64_t len = hm[i].in_len;
+        const uint64_t nblk = len ? (len + df::BLK - 1) / df::BLK : 1;
+        if (hb.size() + nblk > 0x7fffffffull) return ZSB_E_ARG;
+        for (uint64_t b = 0; b < nblk; b++) {
+            df::Block k;
+            k.member = (uint32_t)i;
+            k.start = (uint32_t)(b * df::BLK);
+            k.scratch_off = scratch;
+            k.last = b + 1 == nblk;
+            k.nbytes = 0;
+            const uint64_t nb = std::min<uint64_t>(df::BLK, len - b * df::BLK);
+            scratch += (nb + 64 + 15) & ~(size_t)15;
+            hb.push_back(k);
+        }
+    }
+    first[n] = (uint32_t)hb.size();
+    const size_t nb = hb.size();
+    static bool configured = false;
+    if (!configured) {
+        CK(ctx, cudaFuncSetAttribute(k_deflate, cudaFuncAttributeMaxDynamicSharedMemorySize, df::D_BYTES));
+        configured = true;
+    }
+    int occ = 0;
+    CK(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, k_deflate, 32, df::D_BYTES));
+    if (occ < 1) occ = 1;
+    const unsigned grid = (unsigned)std::max<size_t>(1, std::min<size_t>(nb, (size_t)dv.sm_count * occ));
+    // one device allocation, carved up
+    auto up = [](size_t v) { return (v + 255) & ~(size_t)255; };
+    const size_t o_mem = 0, o_blk = o_mem + up(n * sizeof(df::Member)), o_first = o_blk + up(nb * sizeof(df::Block)),
+                 o_res = o_first + up((n + 1) * 4), o_cnt = o_res + up(n * sizeof(DfResult)), o_tok = o_cnt + 256,
+                 o_scr = o_tok + up((size_t)grid * DF_TOK_WORDS * 4), o_in = o_scr + up(scratch + 64),
+                 o_out = o_in + (device_ptrs ? 0 : up(in_total + 64)), need = o_out + (device_ptrs ? 0 : up(out_total + 64));
+    int rc;
+    if ((rc = grow(ctx, dv.d_df, dv.d_df_cap, need))) return rc;
+    uint8_t *base = dv.d_df;
+    cudaStream_t st = dv.stream;
+    if (!device_ptrs) {
+        for (size_t i = 0; i < n; i++) {
+            if (hm[i].in_len) CK(ctx, cudaMemcpyAsync(base + o_in + in_off[i], hm[i].in, hm[i].in_len, cudaMemcpyHostToDevice, st));
+            hm[i].in = base + o_in + in_off[i];
+            hm[i].out = base + o_out + out_off[i];
+        }
+    }
+    CK(ctx, cudaMemcpyAsync(base + o_mem, hm.data(), n * sizeof(df::Member), cudaMemcpyHostToDevice, st));
+    if (nb) CK(ctx, cudaMemcpyAsync(base + o_blk, hb.data(), nb * sizeof(df::Block), cudaMemcpyHostToDevice, st));
+    CK(ctx, cudaMemcpyAsync(base + o_first, first.data(), (n + 1) * 4, cudaMemcpyHostToDevice, st));
+    CK(ctx, cudaMemsetAsync(base + o_cnt, 0, 256, st));
+    ctx->launches = 0;
+    if (nb) {
+        k_deflate<<<grid, 32, df::D_BYTES, st>>>((const df::Member *)(base + o_mem), (df::Block *)(base + o_blk), (uint32_t)nb,
+                                                 (uint32_t *)(base + o_cnt), (uint32_t *)(base + o_tok), base + o_scr);
+        ctx->launches++;
+        CK(ctx, cudaGetLastError());
+    }
+    k_dstitch<<<(unsigned)std::min<size_t>(n, (size_t)dv.sm_count * 8), CHK_THREADS, 0, st>>>(
+        (const df::Member *)(base + o_mem), (const df::Block *)(base + o_blk), (const uint32_t *)(base + o_first), (uint32_t)n,
+        (uint32_t *)(base + o_cnt) + 1, base + o_scr, (DfResult *)(base + o_res));
+    ctx->launches++;
+    CK(ctx, cudaGetLastError());
+    CK(ctx, cudaMemcpyAsync(r, base + o_res, n * sizeof(DfResult), cudaMemcpyDeviceToHost, st));
+    CK(ctx, cudaStreamSynchronize(st));
+    for (size_t i = 0; i < n; i++) {
+        if (!valid(m[i])) {
+            memset(&r[i], 0, sizeof r[i]);
+            r[i].ret = -2;
+            continue;
+        }
+        if (!device_ptrs && r[i].ret == 1 && r[i].total_out)
+            CK(ctx, cudaMemcpyAsync(m[i].out, base + o_out + out_off[i], r[i].total_out, cudaMemcpyDeviceToHost, st));
+    }
+    if (!device_ptrs) CK(ctx, cudaStreamSynchronize(st));
+    return 0;
+}
 
 // the z_stream surface (inflateInit2_ / inflate / inflateEnd): same translation unit, it shares the kernels above
 #include "zsb_zstream.cuh"

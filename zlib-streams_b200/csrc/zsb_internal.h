@@ -30,6 +30,8 @@ struct zsb_dev {
     // staging arenas for host-pointer batches
     uint8_t *d_in = nullptr, *d_out = nullptr, *d_desc = nullptr;
     size_t d_in_cap = 0, d_out_cap = 0, d_desc_cap = 0;
+    uint8_t *d_df = nullptr;           // zsb_deflate_batch: descriptors, token scratch, block scratch, staging
+    size_t d_df_cap = 0;
     uint8_t *h_desc = nullptr;
     size_t h_desc_cap = 0;
     bool configured[33] = {};
