@@ -297,13 +297,16 @@ def main():
     barrier()
     sampler.stop = True
     ms_per_step = max_over_ranks(ev0.elapsed_time(ev1)) / args.steps
-    lane_ms = lz_ms = None
+    lane_ms = lz_ms = check_ms = None
     if not args.lanes:
         a, b = ctypes.c_double(0), ctypes.c_double(0)
         pairs = lib.zsb_profile_read(eng.ctx, 0, ctypes.byref(a), ctypes.byref(b))
         eng.set_option("profile", 0)
         if pairs > 0:
             lane_ms, lz_ms = a.value / args.steps, b.value / args.steps
+        c = ctypes.c_double(0)
+        if lib.zsb_profile_read_check(eng.ctx, 0, ctypes.byref(c)) > 0:
+            check_ms = c.value / args.steps
     bad = batch.verify()
     if bad:
         raise SystemExit("bench.py: GPU results differ from the oracle: %s" % bad[:3])
@@ -321,7 +324,8 @@ def main():
            "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
                         "traffic": ncu_traffic(config), "peak_source": peak_src, "kernel": kernels,
                         "kernel_ms": ms_per_step,
-                        "kernel_ms_split": {"k_lane(+k_big)": lane_ms, "k_lz": lz_ms},
+                        "kernel_ms_split": {"k_lane(+k_big, concurrent streams)": lane_ms, "k_lz": lz_ms, "k_check": check_ms},
+                        "k_check_gbs": (sum_out / (check_ms * 1e-3) / 1e9) if check_ms else None,
                         "algorithmic_bytes_per_launch": sum_in + sum_out},
            "clocks": sampler.summary(), "gpu_launches": int(launches_per_step * args.steps),
            "path": "group" if args.lanes else "lane", "lanes_per_member": int(args.lanes),

@@ -122,6 +122,8 @@ ZSB_API long zsb_get_option(const zsb_ctx *ctx, const char *name);
  * stream.  zsb_profile_read() waits for them, returns the number of launch pairs recorded on device
  * `dev_index` since the last read and their summed durations in milliseconds. */
 ZSB_API long zsb_profile_read(zsb_ctx *ctx, int dev_index, double *lane_ms, double *lz_ms);
+/* ... and of the k_check launches (Adler-32 / CRC-32 + trailer checks). */
+ZSB_API long zsb_profile_read_check(zsb_ctx *ctx, int dev_index, double *check_ms);
 
 /* Number of kernels the last zsb_inflate_batch*() call launched (for accounting). */
 ZSB_API long zsb_last_launches(const zsb_ctx *ctx);

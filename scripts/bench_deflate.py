@@ -82,7 +82,14 @@ def main():
     ires = (zsblib.Result * n)()
     assert lib.zsb_inflate_batch(eng.ctx, n, mem, ires) == 0, eng.error()
     ir = np.frombuffer(ires, dtype=np.dtype([("ret", "<i4"), ("msg", "<i4"), ("tin", "<u8"), ("tout", "<u8"), ("chk", "<u4"), ("dt", "<i4")]))
-    assert (ir["ret"] == 1).all() and (ir["tout"] == 65536).all()
+    badm = np.nonzero((ir["ret"] != 1) | (ir["tout"] != 65536))[0]
+    if len(badm):
+        j = int(badm[0])
+        comp = t_out[j * cap:j * cap + int(r["tout"][j])].cpu().numpy().tobytes()
+        open(os.path.join(ROOT, "gpurun_out", "deflate_bad_member.bin"), "wb").write(comp)
+        open(os.path.join(ROOT, "gpurun_out", "deflate_bad_plain.bin"), "wb").write(plains[j % K])
+        raise SystemExit("round trip: %d of %d members fail to inflate; first %d: deflate %r inflate %r" % (
+            len(badm), n, j, r[j], ir[j]))
     assert bool((t_back == t_in).all()), "round trip differs"
     # ratio against zlib level 6 on the distinct plaintexts
     with ThreadPoolExecutor(os.cpu_count() or 1) as ex:

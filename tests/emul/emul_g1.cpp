@@ -319,3 +319,13 @@ extern "C" long emul_deflate(const uint8_t *in, size_t in_len, uint8_t *out, siz
     memcpy(out, o.data(), o.size());
     return (long)o.size();
 }
+
+// the code-length builder alone (property tests of the length limits)
+extern "C" void emul_build_lengths(const uint32_t *freq, uint32_t n, uint32_t maxbits, uint8_t *lens) {
+    using namespace zsb;
+    std::vector<uint8_t> sm(df::D_BYTES + 64);
+    uint32_t *f = (uint32_t *)(sm.data() + df::D_LFREQ);
+    for (uint32_t i = 0; i < n; i++) f[i] = freq[i];
+    df::build_lengths<1>(sm.data() + df::D_HASH, f, n, maxbits, sm.data() + df::D_HASH + df::B_LLEN, 0);
+    memcpy(lens, sm.data() + df::D_HASH + df::B_LLEN, n);
+}

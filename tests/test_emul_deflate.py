@@ -55,3 +55,49 @@ def test_ratio_against_zlib_level_6():
     # the matcher keeps 4 candidates per hash bucket where zlib level 6 walks chains of up to 128
     assert total <= 1.15 * ref, (total, ref)
     print("ratio vs zlib level 6: %.3f" % (total / ref))
+
+
+def test_length_limits_are_repaired_to_complete_codes():
+    """Skewed symbol statistics push the unlimited Huffman depths past 15 (literal/length, distance) and 7 (the
+    code-length code); every code set written must still be complete."""
+    rnd = random.Random(8)
+    fib = [1, 1]
+    while len(fib) < 40:
+        fib.append(fib[-1] + fib[-2])
+    plains = []
+    for k in range(12):
+        # byte values with Fibonacci-like counts: the deepest possible Huffman trees
+        parts = [bytes([(7 * i + k) % 256]) * min(fib[i + (k % 3)], 30000) for i in range(20 + k)]
+        rnd.shuffle(parts)
+        plains.append(b"".join(parts)[:65536])
+        plains.append(bytes(rnd.choice(b"abcdefgh" * (k + 1) + bytes(range(k, k + 40))) for _ in range(3000 + 997 * k)))
+    plains.append(open("gpurun_out/deflate_bad_plain.bin", "rb").read() if __import__("os").path.exists("gpurun_out/deflate_bad_plain.bin") else b"x")
+    for plain in plains:
+        comp = emul_deflate(plain, -15)
+        assert zlib.decompress(comp, -15) == plain
+        r, out = CHK.oneshot(comp, len(plain) + 8, -15)
+        assert r.ret == 1 and out == plain
+
+
+def test_code_lengths_are_complete_and_within_the_limit():
+    lib = zsblib.emul().lib
+    lib.emul_build_lengths.argtypes = [ctypes.c_void_p, ctypes.c_uint, ctypes.c_uint, ctypes.c_void_p]
+    rnd = random.Random(77)
+    repaired = 0
+    for trial in range(3000):
+        n, maxbits = rnd.choice([(19, 7), (30, 15), (286, 15), (19, 7)])
+        k = rnd.randrange(1, n + 1)
+        shape = rnd.randrange(4)
+        freq = [0] * n
+        for s in rnd.sample(range(n), k):
+            freq[s] = [rnd.randrange(1, 10), 1 << rnd.randrange(0, 24), int(1.7 ** rnd.randrange(0, 40)) + 1, rnd.randrange(1, 100000)][shape]
+        f = (ctypes.c_uint32 * n)(*freq)
+        lens = (ctypes.c_uint8 * n)()
+        lib.emul_build_lengths(f, n, maxbits, lens)
+        ls = list(lens)
+        coded = [l for l in ls if l]
+        assert all(l <= maxbits for l in coded) and len(coded) >= 2
+        assert all(ls[s] for s in range(n) if freq[s]), "a used symbol without a code"
+        assert sum(1 << (maxbits - l) for l in coded) == 1 << maxbits, (trial, n, maxbits, freq, ls)
+        repaired += max(coded) == maxbits
+    assert repaired > 100

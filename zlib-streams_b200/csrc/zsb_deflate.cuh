@@ -281,11 +281,20 @@ ZSB_DEV void build_lengths(uint8_t *scr, uint32_t *freq, uint32_t n, uint32_t ma
             nn++;
         }
         // depths of the internal nodes (reusing wt), root first; then the census of the leaves' lengths
+        // (a node below a clamped node is clamped too and counts as an overflow of its own, internal or leaf: the
+        //  repair below moves two of them per round)
         const uint32_t root = 2 * m - 2;
-        wt[root] = 0;
-        for (uint32_t i = root; i-- > m;) wt[i] = wt[par[i]] + 1;
-        for (uint32_t b = 0; b <= 15; b++) cnt[b] = 0;
         uint32_t overflow = 0;
+        wt[root] = 0;
+        for (uint32_t i = root; i-- > m;) {
+            uint32_t bits = wt[par[i]] + 1;
+            if (bits > maxbits) {
+                bits = maxbits;
+                overflow++;
+            }
+            wt[i] = bits;
+        }
+        for (uint32_t b = 0; b <= 15; b++) cnt[b] = 0;
         for (uint32_t i = 0; i < m; i++) {
             uint32_t bits = wt[par[i]] + 1;
             if (bits > maxbits) {

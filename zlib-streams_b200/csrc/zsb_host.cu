@@ -542,9 +542,21 @@ static int run_device(zsb_ctx *ctx, zsb_dev &dv, size_t n, const zsb_member *dm,
     }
     if (!(flags & ZSB_RAW_ONLY)) {
         unsigned grid = (unsigned)std::min<size_t>(n, (size_t)dv.sm_count * 8);
+        cudaEvent_t *ce = nullptr;
+        if (ctx->profile) {                           // k_check's own duration (zsb_profile_read_check)
+            if (dv.chk_used + 2 > dv.chk_ev.size()) {
+                const size_t old = dv.chk_ev.size();
+                dv.chk_ev.resize(old + 32);
+                for (size_t i = old; i < dv.chk_ev.size(); i++) CK(ctx, cudaEventCreate(&dv.chk_ev[i]));
+            }
+            ce = &dv.chk_ev[dv.chk_used];
+            dv.chk_used += 2;
+            CK(ctx, cudaEventRecord(ce[0], st));
+        }
         k_check<<<grid, CHK_THREADS, 0, st>>>(dm, dr, sc ? sc->aux : dv.aux, (uint32_t)n, (sc ? sc->counters : dv.counters) + 1);
         ctx->launches++;
         CK(ctx, cudaGetLastError());
+        if (ce) CK(ctx, cudaEventRecord(ce[1], st));
     }
     return 0;
 }
@@ -625,6 +637,8 @@ static void free_device(zsb_dev &dv) {
     if (dv.h_desc) cudaFreeHost(dv.h_desc);
     for (cudaEvent_t e : dv.prof_ev) cudaEventDestroy(e);
     dv.prof_ev.clear();
+    for (cudaEvent_t e : dv.chk_ev) cudaEventDestroy(e);
+    dv.chk_ev.clear();
 }
 
 extern "C" zsb_ctx *zsb_create(const int *devices, int ndev) {
@@ -740,6 +754,24 @@ extern "C" long zsb_profile_read(zsb_ctx *ctx, int dev_index, double *lane_ms, d
     if (lane_ms) *lane_ms = a;
     if (lz_ms) *lz_ms = b;
     return pairs;
+}
+
+// Sum of the event-timed durations (ms) of the k_check launches recorded since the last read (option "profile").
+extern "C" long zsb_profile_read_check(zsb_ctx *ctx, int dev_index, double *check_ms) {
+    if (!ctx || dev_index < 0 || dev_index >= (int)ctx->devs.size()) return ZSB_E_ARG;
+    zsb_dev &dv = ctx->devs[dev_index];
+    double a = 0;
+    long k = 0;
+    for (size_t i = 0; i + 2 <= dv.chk_used; i += 2) {
+        float t = 0;
+        CK(ctx, cudaEventSynchronize(dv.chk_ev[i + 1]));
+        CK(ctx, cudaEventElapsedTime(&t, dv.chk_ev[i], dv.chk_ev[i + 1]));
+        a += t;
+        k++;
+    }
+    dv.chk_used = 0;
+    if (check_ms) *check_ms = a;
+    return k;
 }
 
 extern "C" int zsb_inflate_batch_device(zsb_ctx *ctx, int dev_index, size_t n, const zsb_member *d_members,

@@ -39,6 +39,8 @@ struct zsb_dev {
     // "profile" option: CUDA events around every decode-kernel launch, on the launching stream
     std::vector<cudaEvent_t> prof_ev;  // 3 per lane-path slice: before k_lane, between, after k_lz
     size_t prof_used = 0;
+    std::vector<cudaEvent_t> chk_ev;   // 2 per k_check launch
+    size_t chk_used = 0;
 };
 
 struct zsb_ctx {
