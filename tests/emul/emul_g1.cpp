@@ -25,6 +25,8 @@ static inline bool __any_sync(unsigned, bool p) { return p; }
 static inline bool __all_sync(unsigned, bool p) { return p; }
 #define ZSB_FETCH_SLOT(counter) ((*(counter))++)
 static inline uint32_t __shfl_up_sync(unsigned, uint32_t v, int, int = 32) { return v; }
+static inline uint32_t __shfl_down_sync(unsigned, uint32_t v, int, int = 32) { return v; }
+static inline unsigned __reduce_or_sync(unsigned, unsigned v) { return v; }
 static inline unsigned __ballot_sync(unsigned, bool p) { return p; }
 static inline int __ffs(unsigned x) { return __builtin_ffs((int)x); }
 static inline unsigned __match_any_sync(unsigned, uint32_t) { return 1u; }

@@ -9,7 +9,7 @@
 // Z_SYNC_FLUSH emits), and k_dstitch concatenates the blocks behind the wrapper header.
 //
 //   k_deflate   per block: (1) LZ77 — the warp handles 32 consecutive positions at once: a 4-byte hash selects a
-//               bucket of the 4 most recent positions with that hash (shared memory, 2^12 buckets x 4 x u16),
+//               bucket of the 4 most recent positions with that hash (shared memory, 2^11 buckets x 4 x u16),
 //               every lane measures its candidates (plus distance 1, which catches runs inside a tile), then the
 //               warp walks the tile once to choose literals / matches greedily with one step of lazy evaluation
 //               and appends tokens; (2) code construction — symbol frequencies -> length-limited Huffman code
@@ -30,17 +30,17 @@ namespace df {
 using lane::Wp;
 
 constexpr uint32_t BLK = 65536;             // input bytes per block
-constexpr int HBITS = 12;                   // 4096 buckets of 4 ways
+constexpr int HBITS = 11;                   // 2048 buckets of 4 ways (16 KiB: twelve warps per SM)
 constexpr uint32_t WIN = 32768, MINM = 4, MAXM = 258, NICE = 128, LAZY = 32;
 constexpr uint32_t TOK_MATCH = 0x80000000u; // token: literal byte, or TOK_MATCH | (len - 3) << 15 | (dist - 1)
 
 // ---- per-warp shared memory (bytes) ----
-constexpr int D_HASH = 0;                   // u64[4096]: the matcher's buckets; afterwards the code builder's scratch
-constexpr int D_LFREQ = 32768;              // u32[288] literal/length symbol counts
+constexpr int D_HASH = 0;                   // u64[2048]: the matcher's buckets; afterwards the code builder's scratch
+constexpr int D_LFREQ = 16384;              // u32[288] literal/length symbol counts
 constexpr int D_DFREQ = D_LFREQ + 288 * 4;  // u32[32]
 constexpr int D_STAGE = D_DFREQ + 32 * 4;   // u32[64] emission stage
 constexpr int D_TILE = D_STAGE + 64 * 4;    // u32[32] tokens of the current tile
-constexpr int D_BYTES = D_TILE + 32 * 4;    // 34432
+constexpr int D_BYTES = D_TILE + 32 * 4;    // 18048
 // builder scratch inside D_HASH (the buckets are dead by then)
 constexpr int B_ORDER = 0;                  // u16[288] symbols by ascending count
 constexpr int B_W = 1024;                   // u32[576] node weights (leaves in order, then internal nodes)
@@ -171,19 +171,28 @@ ZSB_DEV uint32_t lz77_block(uint8_t *sm, const uint8_t *in, uint64_t in_len, uin
             const uint32_t most = n - p < MAXM ? n - p : MAXM;
             const unsigned long long b = buckets[h];
             if (most >= MINM) {
+                // the four candidates' first words are requested together (independent loads), then the survivors
+                // are measured
+                long long cand[4];
+                uint32_t cw[4];
+#pragma unroll
                 for (int w = 0; w < 4; w++) {
                     const uint32_t e = (uint32_t)(b >> (16 * w)) & 0xffffu;
-                    long long cand = (long long)((cur & ~0xffffu) | e);
-                    if (cand >= (long long)cur) cand -= 0x10000;
-                    const long long dist = (long long)cur - cand;
-                    if (cand < 0 || dist > (long long)WIN) continue;
-                    if (ld32u(in + cand) != v4) continue;
-                    const uint32_t l = match_len(in + cur, in + cand, most);
-                    if (l > blen || (l == blen && (uint32_t)dist < bdist)) {
+                    long long c = (long long)((cur & ~0xffffu) | e);
+                    if (c >= (long long)cur) c -= 0x10000;
+                    const bool okc = c >= 0 && (long long)cur - c <= (long long)WIN;
+                    cand[w] = okc ? c : -1;
+                    cw[w] = okc ? ld32u(in + c) : ~v4;
+                }
+#pragma unroll
+                for (int w = 0; w < 4; w++) {
+                    if (cand[w] < 0 || cw[w] != v4 || blen >= NICE) continue;
+                    const uint32_t dist = (uint32_t)((long long)cur - cand[w]);
+                    const uint32_t l = 4 + (most > 4 ? match_len(in + cur + 4, in + cand[w] + 4, most - 4) : 0u);
+                    if (l > blen || (l == blen && dist < bdist)) {
                         blen = l;
-                        bdist = (uint32_t)dist;
+                        bdist = dist;
                     }
-                    if (blen >= NICE) break;
                 }
                 if (cur >= 1 && blen < most && in[cur - 1] == (uint8_t)v4) {     // a run: its source may lie inside this tile
                     const uint32_t l = match_len(in + cur, in + cur - 1, most);
@@ -196,28 +205,38 @@ ZSB_DEV uint32_t lz77_block(uint8_t *sm, const uint8_t *in, uint64_t in_len, uin
             if (blen < MINM) blen = 0;
         }
         hash_insert<W>(buckets, canhash, h, cur, lane);
-        // one walk over the tile: greedy with one step of lazy evaluation
-        uint32_t j = skip, count = 0;
+        // The parse of the tile — greedy with one step of lazy evaluation — without a serial walk: every position knows
+        // where the parse would go next from it (a match's end, or the next byte), and the positions the parse visits
+        // from `skip` are found by pointer doubling (five rounds for 32 positions, one warp-wide OR each).
         const uint32_t lim = n - t0 < (uint32_t)W ? n - t0 : (uint32_t)W;
-        while (j < lim) {
-            const uint32_t L = Wp<W>::shfl(blen, (int)j), D = Wp<W>::shfl(bdist, (int)j);
-            const uint32_t L2 = j + 1 < lim ? Wp<W>::shfl(blen, (int)(j + 1)) : 0u;
-            const uint32_t lit = Wp<W>::shfl(v4 & 0xffu, (int)j);
-            const bool take = L >= MINM && !(L < LAZY && L2 > L);
-            if (lane == 0) tile[count] = take ? (TOK_MATCH | ((L - 3) << 15) | (D - 1)) : lit;
-            count++;
-            j += take ? L : 1u;
+        const uint32_t L2 = Wp<W>::shfl_down(blen, 1);
+        const bool take = blen >= MINM && !(blen < LAZY && (uint32_t)lane + 1 < lim && W > 1 && L2 > blen);
+        uint32_t jump = (uint32_t)lane + (take ? blen : 1u);           // next position of the parse, tile-relative
+        const uint32_t nxt = jump;
+        if (jump > (uint32_t)W) jump = W;
+        unsigned visited = skip < lim ? 1u << skip : 0u;
+#pragma unroll
+        for (int r = 1; r < W; r <<= 1) {
+            const bool mine = (visited >> lane) & 1u;
+            visited |= Wp<W>::reduce_or((mine && jump < (uint32_t)W) ? 1u << jump : 0u);
+            const uint32_t j2 = Wp<W>::shfl(jump, (int)(jump < (uint32_t)W ? jump : 0u));
+            jump = jump < (uint32_t)W ? j2 : (uint32_t)W;
         }
-        skip = j > (uint32_t)W ? j - W : 0u;
-        Wp<W>::sync();
-        for (uint32_t i = lane; i < count; i += W) {
-            const uint32_t t = tile[i];
-            tok[T + i] = t;
-            if (t & TOK_MATCH) {
+        visited &= lim >= 32 ? 0xffffffffu : (1u << lim) - 1u;
+        const bool on = (visited >> lane) & 1u;
+        const uint32_t count = (uint32_t)__popc(visited);
+        // where the parse leaves the tile: the end of the last visited position's step
+        const int lastv = visited ? 31 - __clz((int)visited) : -1;
+        const uint32_t endpos = lastv >= 0 ? Wp<W>::shfl(nxt, lastv) : skip;
+        skip = endpos > (uint32_t)W ? endpos - W : 0u;
+        if (on) {
+            const uint32_t t = take ? (TOK_MATCH | ((blen - 3) << 15) | (bdist - 1)) : (v4 & 0xffu);
+            tok[T + (uint32_t)__popc(visited & ((1u << lane) - 1u))] = t;
+            if (take) {
                 uint32_t sym, xb, xv;
-                len_symbol(((t >> 15) & 0xffu) + 3, sym, xb, xv);
+                len_symbol(blen, sym, xb, xv);
                 ZSB_SMEM_ADD(&lfreq[sym], 1u);
-                dist_symbol((t & 0x7fffu) + 1, sym, xb, xv);
+                dist_symbol(bdist, sym, xb, xv);
                 ZSB_SMEM_ADD(&dfreq[sym], 1u);
             } else {
                 ZSB_SMEM_ADD(&lfreq[t], 1u);

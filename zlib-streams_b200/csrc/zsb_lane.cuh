@@ -85,6 +85,8 @@ template <int W> struct Wp {
     static ZSB_DEV uint32_t shfl(uint32_t v, int src) { return __shfl_sync(0xffffffffu, v, src); }
     static ZSB_DEV uint32_t shfl_up(uint32_t v, int d) { return __shfl_up_sync(0xffffffffu, v, d); }
     static ZSB_DEV unsigned match(uint32_t v) { return __match_any_sync(0xffffffffu, v); }
+    static ZSB_DEV unsigned reduce_or(unsigned v) { return __reduce_or_sync(0xffffffffu, v); }
+    static ZSB_DEV uint32_t shfl_down(uint32_t v, int d) { return __shfl_down_sync(0xffffffffu, v, d); }
     static ZSB_DEV void sync() { __syncwarp(); }
 };
 template <> struct Wp<1> {
@@ -93,6 +95,8 @@ template <> struct Wp<1> {
     static ZSB_DEV uint32_t shfl(uint32_t v, int) { return v; }
     static ZSB_DEV uint32_t shfl_up(uint32_t v, int) { return v; }
     static ZSB_DEV unsigned match(uint32_t) { return 1u; }
+    static ZSB_DEV unsigned reduce_or(unsigned v) { return v; }
+    static ZSB_DEV uint32_t shfl_down(uint32_t v, int) { return v; }
     static ZSB_DEV void sync() {}
 };
 
