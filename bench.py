@@ -441,7 +441,7 @@ def main():
             barrier()
             if rank == 0:
                 allctx = zsblib.Zsb(devices=list(range(world)))
-                sub = np.arange(0, nn, max(1, nn // 65536), dtype=np.int64)[:65536]
+                sub = np.arange(min(nn, 65536), dtype=np.int64)      # whole tiles: neighbouring members have adjacent buffers
                 ob = batchlib.DeviceBatch(sw, dev, members=sub, exp=sexp).to_host(lib)
                 ob.host_step(allctx)
                 t0 = time.perf_counter()
