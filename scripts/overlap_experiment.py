@@ -2,9 +2,10 @@
 """Experiment: does k_lz's work fit into the issue slots k_lane leaves idle?
 
 The C2 batch is cut into K parts; part i is decoded by its own context (own scratch) on its own CUDA stream with
-k_lane in small CTAs (option small_ctas: 2-warp CTAs, six per SM), so that k_lz of one part runs beside k_lane of
-the next on the same SMs — the overlap a fused kernel with resolver warps would give, without the fusion.  Prints
-ms per step for K = 1 (one launch pair, full-size CTAs: the product's default), and K = 2, 4, 8."""
+k_lane in full-size CTAs (one per SM: k_lz's CTAs fit beside it, the next part's k_lane takes the SM when this
+part's leaves) or in small CTAs (option small_ctas: 2-warp CTAs, six per SM), so that k_lz of one part runs beside
+k_lane of the next on the same SMs — the overlap a fused kernel with resolver warps would give, without the
+fusion.  Prints ms per step for K = 1 (one launch pair, full-size CTAs: the product's default), and K = 2 .. 16."""
 import ctypes
 import json
 import os
@@ -26,14 +27,14 @@ def main():
     exp = batchlib.expected(w["distinct"])
     n = 1024 * 64
     out = {}
-    for K in (1, 2, 4, 8):
+    for K, small in ((1, 0), (2, 0), (4, 0), (8, 0), (16, 0), (2, 1), (4, 1), (8, 1), (16, 1)):
         engs = [zsblib.Zsb(devices=[0]) for _ in range(K)]
         streams = [torch.cuda.Stream(dev) for _ in range(K)]
         parts = []
         for i in range(K):
             members = np.arange(i, n, K, dtype=np.int64)          # every part has the same mix of members
             parts.append(batchlib.DeviceBatch(w, dev, members=members, exp=exp).to_device())
-            if K > 1:
+            if small:
                 engs[i].set_option("small_ctas", 1)
         def step():
             for i in range(K):
@@ -60,7 +61,7 @@ def main():
         ms = e0.elapsed_time(e1) / steps
         bad = [b for p in parts for b in p.verify()]
         assert not bad, bad[:3]
-        out["K=%d" % K] = {"ms_per_step": ms, "decompressed_gbs": n * 65536 / ms / 1e6, "members_verified": n}
+        out["K=%d%s" % (K, " small CTAs" if small else "")] = {"ms_per_step": ms, "decompressed_gbs": n * 65536 / ms / 1e6, "members_verified": n}
         del parts
         for e in engs:
             e.close()

@@ -11,8 +11,8 @@
 //   k_deflate   per block: (1) LZ77 — the warp handles 32 consecutive positions at once: a 4-byte hash selects a
 //               bucket of the 4 most recent positions with that hash (shared memory, 2^11 buckets x 4 x u16),
 //               every lane measures its candidates (plus distance 1, which catches runs inside a tile), then the
-//               warp walks the tile once to choose literals / matches greedily with one step of lazy evaluation
-//               and appends tokens; (2) code construction — symbol frequencies -> length-limited Huffman code
+//               parse of the tile — greedy with one step of lazy evaluation — is found by pointer doubling over
+//               the lanes' "next position" links (five shuffle rounds, no serial walk) and the tokens appended; (2) code construction — symbol frequencies -> length-limited Huffman code
 //               lengths (rank sort by the warp, two-queue merge, overflow repair), canonical codes, the run-length
 //               coded header of RFC 1951 3.2.7, and the choice between a dynamic, a fixed and stored blocks by
 //               exact size; (3) emission — 32 tokens per trip: bit lengths by a warp prefix sum, bits OR-ed into
@@ -143,7 +143,7 @@ ZSB_DEV void hash_insert(unsigned long long *buckets, bool canhash, uint32_t h, 
 template <int W>
 ZSB_DEV uint32_t lz77_block(uint8_t *sm, const uint8_t *in, uint64_t in_len, uint32_t start, uint32_t n, uint32_t *tok, int lane) {
     unsigned long long *buckets = (unsigned long long *)(sm + D_HASH);
-    uint32_t *lfreq = (uint32_t *)(sm + D_LFREQ), *dfreq = (uint32_t *)(sm + D_DFREQ), *tile = (uint32_t *)(sm + D_TILE);
+    uint32_t *lfreq = (uint32_t *)(sm + D_LFREQ), *dfreq = (uint32_t *)(sm + D_DFREQ);
     for (int i = lane; i < (1 << HBITS); i += W) buckets[i] = 0;
     for (int i = lane; i < 288 + 32; i += W) lfreq[i] = 0;             // (dfreq follows lfreq)
     Wp<W>::sync();

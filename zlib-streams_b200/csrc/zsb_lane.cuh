@@ -308,7 +308,7 @@ ZSB_DEV int careful_symbol(Dec &d, const uint8_t *T, const uint32_t *lut, bool h
 ZSB_DEV int accept_match(Lane &L) {
     Dec &d = L.d;
     if (d.pos >= d.cap) return EV_OUTFULL;
-    if (d.mdist > d.pos + L.hist) {
+    if ((uint64_t)d.mdist > (uint64_t)d.pos + L.hist) {        // 64-bit: pos + hist may pass 2^32 in a member near the 4 GiB limit
         d.msg = M_TOOFAR;
         return EV_ERR;
     }
@@ -408,7 +408,7 @@ ZSB_DEV bool fast_step(Lane &L, const uint8_t *T, const uint32_t *lut) {
     const uint32_t val = (lw & 0xffffu) + ((w >> nb) & ((1u << xb) - 1u));
     const uint32_t used = nb + xb;
     // ---- may this code be committed here? ----
-    const uint32_t okD = (hasx && !(lw >> 31) && val <= d.pos + L.hist && d.pos + L.pl <= d.cap) ? 1u : 0u;
+    const uint32_t okD = (hasx && !(lw >> 31) && (uint64_t)val <= (uint64_t)d.pos + L.hist && L.pl <= d.cap - d.pos) ? 1u : 0u;
     const uint32_t okL = (hasx || (k < 15 && islit && d.pos < d.cap)) ? 1u : 0u;
     if (!sel(m, okD, okL)) return false;
     // ---- commit ----
@@ -533,7 +533,7 @@ ZSB_DEV bool big_run(Lane &L, const uint8_t *T, const uint32_t *lut, const uint3
             if (!(f & 15u)) f = big_dd_entry(T, lut, d.d64, (uint32_t)b.hold);
             const uint32_t nb2 = f & 15u, xb2 = (f >> 4) & 31u;
             const uint32_t dist = (f >> 16) + ((uint32_t)(b.hold >> nb2) & ((1u << xb2) - 1u));
-            if (((f >> 9) & 3u) != BK_BASE || dist > d.pos + L.hist || mlen > d.cap - d.pos) {
+            if (((f >> 9) & 3u) != BK_BASE || (uint64_t)dist > (uint64_t)d.pos + L.hist || mlen > d.cap - d.pos) {
                 b.hold = h0;
                 b.nbits = n0;
                 b.next = x0;
