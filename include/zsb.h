@@ -257,6 +257,26 @@ typedef struct zsb_deflate_result {
 ZSB_API int zsb_deflate_batch(zsb_ctx *ctx, size_t n, const zsb_deflate_member *members, zsb_deflate_result *results);
 ZSB_API size_t zsb_deflate_bound(size_t in_len, int window_bits);
 
+/* ---- batched deflate with no allocation ----
+ * NO COUNTERPART IN THE REFERENCE: added for callers that cannot call
+ * cudaMalloc (CUDA graph capture, tight serving loops, harnesses that forbid it).  The same kernels and the same
+ * output bytes as zsb_deflate_batch(), but every piece of device scratch (descriptors, block table, token and block
+ * buffers, results) lives in ONE file-scope device array of zsb_deflate_static_limits() bytes (about 8.4 MB) that
+ * every GPU which loads the library holds until exit; the call makes no cudaMalloc / cudaFree / allocating library
+ * call and needs no zsb_ctx.  members[i].in / .out must be DEVICE pointers on `device` (there is nowhere to stage
+ * host buffers); members and results themselves are host arrays.  Limits: at most max_members (64) members and
+ * max_blocks (64) blocks of 64 KiB over the whole call (a member of L bytes takes max(1, ceil(L / 65536)) blocks);
+ * beyond them the call returns ZSB_E_LIMIT and says which limit in err.  The kernels run on `stream` (a
+ * cudaStream_t; NULL = the default stream) and the call synchronises that stream before it returns.  All calls
+ * share the array, which keeps the last call's contents (the call clears what must start at zero); calls in one
+ * process are serialised by a mutex — work that overlapped on the GPU with another user of the array would race.
+ * err (optional, err_cap bytes) receives a message when the return value is not 0: ZSB_E_ARG, ZSB_E_LIMIT, ZSB_E_CUDA. */
+ZSB_API int zsb_deflate_batch_static(int device, size_t n, const zsb_deflate_member *members, zsb_deflate_result *results,
+                                     void *stream, char *err, size_t err_cap);
+/* bytes of the static array; the two limits through the pointers (either may be NULL) */
+ZSB_API size_t zsb_deflate_static_limits(size_t *max_members, size_t *max_blocks);
+
+#define ZSB_E_LIMIT (-104)
 #define ZSB_E_ZIP   (-103)
 #define ZSB_E_ARG   (-100)
 #define ZSB_E_CUDA  (-101)

@@ -13,7 +13,7 @@ PKG = os.path.join(ROOT, "zlib-streams_b200")
 LIB = os.environ.get("ZSB_LIB") or os.path.join(PKG, "libzsb.so")      # ZSB_LIB: a variant build (experiments)
 EMUL_DIR = os.path.join(ROOT, "tests", "emul")
 
-API_SYMBOLS = ["zsb_deflate_batch", "zsb_deflate_bound", "zsb_profile_read_check", "zsb_create", "zsb_destroy", "zsb_create_error", "zsb_last_error", "zsb_num_devices",
+API_SYMBOLS = ["zsb_deflate_batch", "zsb_deflate_bound", "zsb_deflate_batch_static", "zsb_deflate_static_limits", "zsb_profile_read_check", "zsb_create", "zsb_destroy", "zsb_create_error", "zsb_last_error", "zsb_num_devices",
                "zsb_inflate_batch", "zsb_inflate_batch_device", "zsb_set_option", "zsb_get_option",
                "zsb_last_launches", "zsb_plan_shards", "zsb_host_alloc", "zsb_host_free", "zsb_message",
                "zsb_profile_read", "zsb_zip_scan", "zsb_zip_members", "zsb_zip_inflate", "zsb_gunzip_files", "zsb_plan_big", "zsb_inflate_streams", "zsb_gzip_header"]
@@ -110,6 +110,10 @@ def load_product():
     lib.zsb_plan_big.restype = ctypes.c_size_t
     lib.zsb_plan_big.argtypes = [ctypes.c_size_t, ctypes.c_void_p, ctypes.c_void_p, ctypes.c_int]
     lib.zsb_deflate_batch.argtypes = [ctypes.c_void_p, ctypes.c_size_t, ctypes.c_void_p, ctypes.c_void_p]
+    lib.zsb_deflate_batch_static.argtypes = [ctypes.c_int, ctypes.c_size_t, ctypes.c_void_p, ctypes.c_void_p, ctypes.c_void_p,
+                                             ctypes.c_char_p, ctypes.c_size_t]
+    lib.zsb_deflate_static_limits.restype = ctypes.c_size_t
+    lib.zsb_deflate_static_limits.argtypes = [ctypes.POINTER(ctypes.c_size_t), ctypes.POINTER(ctypes.c_size_t)]
     lib.zsb_deflate_bound.restype = ctypes.c_size_t
     lib.zsb_deflate_bound.argtypes = [ctypes.c_size_t, ctypes.c_int]
     lib.zsb_profile_read_check.restype = ctypes.c_long

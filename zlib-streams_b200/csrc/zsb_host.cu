@@ -4,9 +4,11 @@
 #include <cuda_runtime.h>
 #include <algorithm>
 #include <chrono>
+#include <cstdarg>
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
+#include <mutex>
 #include <string>
 #include <vector>
 #include "zsb_kernels.cuh"
@@ -1382,6 +1384,134 @@ extern "C" int zsb_deflate_batch(zsb_ctx *ctx, size_t n, const zsb_deflate_membe
             CK(ctx, cudaMemcpyAsync(m[i].out, base + o_out + out_off[i], r[i].total_out, cudaMemcpyDeviceToHost, st));
     }
     if (!device_ptrs) CK(ctx, cudaStreamSynchronize(st));
+    return 0;
+}
+
+// ---- zsb_deflate_batch_static: the same two kernels with NO allocation anywhere -------------------------------
+// For callers that cannot call cudaMalloc (CUDA graph capture, tight serving loops, harnesses that forbid it).  No
+// counterpart in the reference.  Everything zsb_deflate_batch() carves
+// out of its grown device allocation (descriptors, block table, results, counters, token scratch, block bytes)
+// lives in one file-scope device array of a fixed size, so the batch is limited to ZSB_STATIC_MAX_MEMBERS members
+// and ZSB_STATIC_MAX_BLOCKS 64 KiB blocks.  Every GPU that loads the library holds the array until exit; every
+// call shares it (the host part is serialised by a mutex and the call synchronises its stream before it returns,
+// so calls of one process do not overlap on the GPU; anything else that made them overlap would race).
+constexpr size_t ST_MEMBERS = 64, ST_BLOCKS = 64, ST_GRID = 16;
+constexpr size_t st_up(size_t v) { return (v + 255) & ~(size_t)255; }
+constexpr size_t ST_O_MEM = 0, ST_O_BLK = ST_O_MEM + st_up(ST_MEMBERS * sizeof(df::Member)),
+                 ST_O_FIRST = ST_O_BLK + st_up(ST_BLOCKS * sizeof(df::Block)), ST_O_RES = ST_O_FIRST + st_up((ST_MEMBERS + 1) * 4),
+                 ST_O_CNT = ST_O_RES + st_up(ST_MEMBERS * sizeof(DfResult)), ST_O_TOK = ST_O_CNT + 256,
+                 ST_O_SCR = ST_O_TOK + st_up(ST_GRID * DF_TOK_WORDS * 4),
+                 ST_BYTES = ST_O_SCR + st_up(ST_BLOCKS * (df::BLK + 64 + 16) + 64);
+static __device__ __align__(256) uint8_t g_static_scratch[ST_BYTES];       // 8.4 MB per GPU
+
+static int st_fail(char *err, size_t cap, int code, const char *fmt, ...) {
+    if (err && cap) {
+        va_list ap;
+        va_start(ap, fmt);
+        vsnprintf(err, cap, fmt, ap);
+        va_end(ap);
+    }
+    return code;
+}
+
+extern "C" size_t zsb_deflate_static_limits(size_t *max_members, size_t *max_blocks) {
+    if (max_members) *max_members = ST_MEMBERS;
+    if (max_blocks) *max_blocks = ST_BLOCKS;
+    return ST_BYTES;
+}
+
+extern "C" int zsb_deflate_batch_static(int device, size_t n, const zsb_deflate_member *m, zsb_deflate_result *r, void *stream,
+                                        char *err, size_t err_cap) {
+    static std::mutex mu;
+    static uint8_t *base_of[64];            // device address of g_static_scratch, per device (0 = not asked yet)
+    if (err && err_cap) err[0] = 0;
+    if (n && (!m || !r)) return st_fail(err, err_cap, ZSB_E_ARG, "members / results is NULL");
+    if (device < 0 || device >= 64) return st_fail(err, err_cap, ZSB_E_ARG, "device %d out of range", device);
+    if (n == 0) return 0;
+    if (n > ST_MEMBERS)
+        return st_fail(err, err_cap, ZSB_E_LIMIT, "%zu members: the static scratch holds at most %zu per call", n, ST_MEMBERS);
+    df::Member hm[ST_MEMBERS];
+    df::Block hb[ST_BLOCKS];
+    uint32_t first[ST_MEMBERS + 1];
+    bool ok[ST_MEMBERS];
+    size_t nb = 0, scratch = 0;
+    for (size_t i = 0; i < n; i++) {
+        const zsb_deflate_member &x = m[i];
+        memcpy(&hm[i], &x, sizeof(df::Member));
+        first[i] = (uint32_t)nb;
+        ok[i] = (x.window_bits == -15 || x.window_bits == 15 || x.window_bits == 31) && x.level >= -1 && x.level <= 9 &&
+                x.in_len <= 0xfffffff0ull && (x.in || !x.in_len) && (x.out || !x.out_cap);
+        if (!ok[i]) {
+            hm[i].in_len = 0;
+            hm[i].out_cap = 0;
+            hm[i].window_bits = -15;
+            hm[i].level = 6;
+            continue;
+        }
+        const uint64_t len = x.in_len, nblk = len ? (len + df::BLK - 1) / df::BLK : 1;
+        if (nb + nblk > ST_BLOCKS)
+            return st_fail(err, err_cap, ZSB_E_LIMIT, "more than %zu blocks of 64 KiB (member %zu of %zu bytes): beyond the static scratch",
+                           ST_BLOCKS, i, (size_t)len);
+        for (uint64_t b = 0; b < nblk; b++) {
+            df::Block &k = hb[nb++];
+            k.member = (uint32_t)i;
+            k.start = (uint32_t)(b * df::BLK);
+            k.scratch_off = scratch;
+            k.last = b + 1 == nblk;
+            k.nbytes = 0;
+            scratch += (std::min<uint64_t>(df::BLK, len - b * df::BLK) + 64 + 15) & ~(size_t)15;
+        }
+    }
+    first[n] = (uint32_t)nb;
+    for (size_t i = 0; i < n; i++) {        // the caller's buffers must be device memory: there is nowhere to stage them
+        const void *ps[2] = {hm[i].in_len ? (const void *)hm[i].in : nullptr, hm[i].out_cap ? (const void *)hm[i].out : nullptr};
+        for (const void *p : ps) {
+            if (!p) continue;
+            cudaPointerAttributes at;
+            if (cudaPointerGetAttributes(&at, p) != cudaSuccess || !(at.type == cudaMemoryTypeDevice || at.type == cudaMemoryTypeManaged)) {
+                cudaGetLastError();
+                return st_fail(err, err_cap, ZSB_E_ARG, "member %zu: in / out must be device pointers", i);
+            }
+        }
+    }
+    std::lock_guard<std::mutex> lk(mu);
+    int cur = 0;
+    cudaGetDevice(&cur);
+    struct Restore { int cur; ~Restore() { cudaSetDevice(cur); } } restore{cur};
+    cudaError_t e;
+#define ST_CK(call)                                                                                         \
+    if ((e = (call)) != cudaSuccess)                                                                        \
+        return st_fail(err, err_cap, ZSB_E_CUDA, "%s: %s", #call, cudaGetErrorString(e))
+    ST_CK(cudaSetDevice(device));
+    if (!base_of[device]) {                 // once per device, with that device current
+        uint8_t *p = nullptr;
+        ST_CK(cudaGetSymbolAddress((void **)&p, g_static_scratch));
+        base_of[device] = p;
+    }
+    uint8_t *base = base_of[device];
+    cudaStream_t st = (cudaStream_t)stream;
+    ST_CK(cudaMemcpyAsync(base + ST_O_MEM, hm, n * sizeof(df::Member), cudaMemcpyHostToDevice, st));
+    if (nb) ST_CK(cudaMemcpyAsync(base + ST_O_BLK, hb, nb * sizeof(df::Block), cudaMemcpyHostToDevice, st));
+    ST_CK(cudaMemcpyAsync(base + ST_O_FIRST, first, (n + 1) * 4, cudaMemcpyHostToDevice, st));
+    ST_CK(cudaMemsetAsync(base + ST_O_CNT, 0, 256, st));             // the two work counters start at zero every call
+    if (nb) {
+        k_deflate<<<(unsigned)std::min(nb, ST_GRID), 32, df::D_BYTES, st>>>((const df::Member *)(base + ST_O_MEM), (df::Block *)(base + ST_O_BLK),
+                                                                            (uint32_t)nb, (uint32_t *)(base + ST_O_CNT),
+                                                                            (uint32_t *)(base + ST_O_TOK), base + ST_O_SCR);
+        ST_CK(cudaGetLastError());
+    }
+    k_dstitch<<<(unsigned)n, CHK_THREADS, 0, st>>>((const df::Member *)(base + ST_O_MEM), (const df::Block *)(base + ST_O_BLK),
+                                                   (const uint32_t *)(base + ST_O_FIRST), (uint32_t)n, (uint32_t *)(base + ST_O_CNT) + 1,
+                                                   base + ST_O_SCR, (DfResult *)(base + ST_O_RES));
+    ST_CK(cudaGetLastError());
+    ST_CK(cudaMemcpyAsync(r, base + ST_O_RES, n * sizeof(DfResult), cudaMemcpyDeviceToHost, st));
+    ST_CK(cudaStreamSynchronize(st));
+#undef ST_CK
+    for (size_t i = 0; i < n; i++)
+        if (!ok[i]) {
+            memset(&r[i], 0, sizeof r[i]);
+            r[i].ret = -2;
+        }
     return 0;
 }
 
