@@ -5,7 +5,9 @@ The C2 batch is cut into K parts; part i is decoded by its own context (own scra
 k_lane in full-size CTAs (one per SM: k_lz's CTAs fit beside it, the next part's k_lane takes the SM when this
 part's leaves) or in small CTAs (option small_ctas: 2-warp CTAs, six per SM), so that k_lz of one part runs beside
 k_lane of the next on the same SMs — the overlap a fused kernel with resolver warps would give, without the
-fusion.  Prints ms per step for K = 1 (one launch pair, full-size CTAs: the product's default), and K = 2 .. 16."""
+fusion.  CAVEAT (found afterwards): the timed steps are queued back to back, so with K > 1 a step also overlaps the
+NEXT step; inside one zsb_inflate_batch_device() call the same parts give no gain (profiles/r02_bench_overlap_parts8.json:
+30.8 ms).  Prints ms per step for K = 1 (one launch pair, full-size CTAs: the product's default), and K = 2 .. 16."""
 import ctypes
 import json
 import os
