@@ -7,6 +7,8 @@
 #include <cstdint>
 #include <cstring>
 #include <cstdlib>
+#include <cstdio>
+#include <vector>
 #define __device__
 #define __host__
 #define __forceinline__ inline
@@ -109,6 +111,84 @@ extern "C" int emul_decode_lane(const uint8_t *in, size_t in_len, uint8_t *out, 
     free(seq);
     aux4[0] = a.kind; aux4[1] = a.trailer_pos; aux4[2] = a.need_trailer; aux4[3] = a.init_check;
     return rc;
+}
+
+// the segmented path of large members (zsb_seg.cuh) with a warp of one lane: find the block starts near multiples of
+// segb compressed bytes, decode the segments, chain them, resolve; info[0] = starts found, info[1] = 1 when the chain
+// held (0: the caller sees the serial fallback's result, as on the device), info[2] = segments, info[3] = live ones
+#include "../../zlib-streams_b200/csrc/zsb_seg.cuh"
+extern "C" int emul_decode_seg(const uint8_t *in, size_t in_len, uint8_t *out, size_t out_cap, int wbits, uint32_t segb,
+                               uint32_t seg_q, zsb_result *res, uint32_t *aux4, uint32_t *info) {
+    using namespace zsb;
+    alignas(16) static uint32_t fixLL[lane::BIG_LUT_BYTES / 4];
+    static uint8_t fixed[lane::SLOT];
+    static uint32_t lut[LUT_WORDS];
+    static bool init = false;
+    alignas(16) static uint8_t scr[lane::WSCR];
+    if (!init) {
+        init_lut(lut, 0, 1);
+        alignas(16) uint8_t T0[lane::SLOT];
+        for (int i = 0; i < 288; i++) T0[lane::H_LENS + i] = i < 144 ? 8 : i < 256 ? 9 : i < 280 ? 7 : 8;
+        for (int i = 0; i < 32; i++) T0[lane::H_LENS + 288 + i] = 5;
+        lane::build_tables<1>(T0, scr, 288, 32, false, 0);
+        memcpy(fixed, T0, sizeof fixed);
+        lane::big_build<1>(fixLL, fixed, lut, 0u, 0);
+        init = true;
+    }
+    alignas(16) uint8_t T[lane::SLOT];
+    memset(T, 0xA5, sizeof T);
+    zsb_member m;
+    m.in = in; m.in_len = in_len; m.out = out; m.out_cap = out_cap; m.window_bits = wbits; m.flags = 0;
+    const uint32_t nseg = (uint32_t)((in_len + segb - 1) / segb);
+    std::vector<lane::Seg> segs(nseg ? nseg : 1);
+    std::vector<uint64_t> seq_off(segs.size());
+    std::vector<lane::seq_t> arena((size_t)segs.size() * seg_q + 64);
+    alignas(16) static uint8_t fsm[seg::F_BYTES];
+    uint32_t found = 0;
+    for (uint32_t k = 0; k < segs.size(); k++) {
+        lane::Seg &g = segs[k];
+        memset(&g, 0, sizeof g);
+        g.member = 0; g.k = k; g.first = 0; g.nseg = (uint32_t)segs.size();
+        g.start_bit = 0; g.target = lane::SEG_NONE; g.ev = lane::EV_ABSENT;
+        seq_off[k] = (uint64_t)k * seg_q;
+        if (k) g.start_bit = lane::SEG_NONE;
+        if (k && wbits != -16 && (uint64_t)k * segb >= seg::first_start(false))
+            g.start_bit = seg::find_sync_fixed<1>(true, in, (uint32_t)in_len, 8ull * k * segb, 8ull * k * segb + 16ull * segb, fixLL);
+        if (k && g.start_bit != lane::SEG_NONE) found++;
+        else if (k && (uint64_t)k * segb >= seg::first_start(wbits == -16)) {
+            g.start_bit = seg::find_start<1>(in, (uint32_t)in_len, wbits == -16, 8ull * k * segb, 8ull * (k + 1) * segb, fsm, lut, 0);
+            if (g.start_bit != lane::SEG_NONE) found++;
+        }
+    }
+    seg::plan_member(segs.data(), segb, (uint32_t)in_len, wbits == -16);
+    Aux a;
+    memset(&a, 0, sizeof a);
+    uint32_t counter = 0;
+    lane::Batch B;
+    B.segs = segs.data(); B.seg_q = seg_q;
+    B.members = &m; B.results = res; B.aux = &a; B.order = nullptr; B.seq_off = seq_off.data(); B.seq_base = arena.data();
+    B.hist = nullptr; B.n = (uint32_t)segs.size(); B.counter = &counter; B.fixed_tab = fixed;
+    uint32_t ring[lane::RING_WORDS] = {0, 0, 0, 0};
+    lane::warp_lanes<1, false, true>(B, T, scr, ring, lut, 0);
+    const bool ok = seg::chain_member(B, 0);
+    info[0] = found; info[1] = ok; info[2] = (uint32_t)segs.size(); info[3] = 0;
+    if (getenv("ZSB_EMUL_TRACE"))
+        for (uint32_t k = 0; k < segs.size(); k++)
+            if (segs[k].start_bit != lane::SEG_NONE)
+                fprintf(stderr, "seg %u start %llu target %llu ev %d end %llu pos %u nseq %u base %u live %u\n", k,
+                        (unsigned long long)segs[k].start_bit, (unsigned long long)segs[k].target, segs[k].ev,
+                        8ull * segs[k].next - segs[k].nbits, segs[k].pos, segs[k].nseq, segs[k].base, segs[k].live);
+    if (ok) {
+        for (uint32_t k = 0; k < segs.size(); k++)
+            if (segs[k].live) {
+                info[3]++;
+                if (segs[k].nseq) lz::resolve_range<1>(out, in, arena.data() + seq_off[k], segs[k].nseq, 0, segs[k].base);
+            }
+        aux4[0] = a.kind; aux4[1] = a.trailer_pos; aux4[2] = a.need_trailer; aux4[3] = a.init_check;
+        return res->ret;
+    }
+    uint32_t nseq = 0;
+    return emul_decode_lane(in, in_len, out, out_cap, wbits, res, aux4, (uint64_t)out_cap + 8 * in_len + 64, &nseq);
 }
 
 // second half of the pipeline: what k_check does once the checksum of the output is known

@@ -1,0 +1,71 @@
+"""GPU tier: large members decoded in segments (zlib-streams_b200/csrc/zsb_seg.cuh) — block starts found inside a member,
+the stretches between them decoded by a lane each, chained, resolved — against the oracle, record for record and byte
+for byte: valid, damaged and truncated members, all three wrappers and Deflate64, members whose chain cannot hold
+(fixed / stored blocks only, short capacity) and therefore take the serial fallback, with small segments (many
+boundaries per member) and with the default geometry."""
+import random
+import zlib
+
+import pytest
+
+import gen
+import orclib
+import zsblib
+
+pytestmark = pytest.mark.gpu
+CHK = orclib.ref() or orclib.orc()
+
+
+def members():
+    import d64enc
+    rnd = random.Random(21)
+    soup = b"".join(gen.word_soup(65536, 140 + i) for i in range(12))
+    out = []
+    for wb in (-15, 15, 31):
+        out.append((gen.deflate(soup, 6, wb), wb, len(soup) + 16))
+    out.append((gen.deflate(soup, 1, -15), -15, len(soup) + 16))
+    out.append((gen.deflate(soup, 9, 31), 31, len(soup)))                      # exact capacity
+    out.append((gen.deflate(soup, 6, 15), 15, len(soup) - 1))                  # one byte short: serial verdict
+    mixed = gen.mixed_plain(900000, 5)
+    out.append((gen.deflate(mixed, 6, 15), 15, len(mixed) + 16))
+    out.append((gen.deflate(soup[:400000], 6, -15, zlib.Z_FIXED), -15, 400016))
+    rb = rnd.randbytes(300000)
+    out.append((gen.deflate(rb, 0, 15), 15, 300016))
+    plain = soup[:200000] + soup[:65536] + bytes(90000) + soup[300000:350000] * 3
+    out.append((d64enc.compress(plain, True, 3000, ("dynamic", "dynamic", "fixed", "stored")), -16, len(plain) + 16))
+    base = list(out[:4]) + [out[6], out[9]]
+    for comp, wb, cap in base:                                                # damage and truncation
+        for k in range(6):
+            bad = bytearray(comp)
+            at = rnd.randrange(len(bad))
+            bad[at] ^= 1 << rnd.randrange(8)
+            out.append((bytes(bad), wb, cap + 64))
+        for cut in (len(comp) // 3, len(comp) - 6, len(comp) - 1):
+            out.append((comp[:cut], wb, cap + 64))
+        out.append((comp + b"\0" * 3000 + comp[:2000], wb, cap + 64))
+    return out
+
+
+@pytest.mark.parametrize("seg_bytes,seg_min", [(8192, 32768), (32768, 131072), (2048, 16384)])
+def test_segmented_members_match_the_oracle(seg_bytes, seg_min):
+    import torch
+    import batchlib
+    eng = zsblib.Zsb(devices=[0])
+    try:
+        eng.set_option("seg_bytes", seg_bytes)
+        eng.set_option("seg_min", seg_min)
+        small = [(gen.deflate(gen.word_soup(3000 + 100 * i, i), 6, -15), -15, 3000 + 100 * i + 8) for i in range(40)]
+        distinct = [(c, wb, bytes(cap)) for c, wb, cap in members() + small]
+        w = {"distinct": distinct, "tiles": 3, "desc": "large members in segments"}
+        dev = torch.device("cuda", 0)
+        batch = batchlib.DeviceBatch(w, dev).to_device()
+        stream = torch.cuda.Stream(dev)
+        for segment in (1, 0, 1):
+            eng.set_option("segment", segment)
+            batch.clear_outputs()
+            batch.step(eng, stream)
+            stream.synchronize()
+            bad = batch.verify()
+            assert not bad, (segment, bad[:3])
+    finally:
+        eng.close()

@@ -246,6 +246,27 @@ class Emul:
         return r, out
 
 
+    def oneshot_seg(self, data, out_cap, wbits, segb, seg_q=None):
+        """The segmented path (zsb_seg.cuh) on the host: -> (Result, output, info) with info = (starts found, chain held,
+        segments, live segments)."""
+        import zlib
+        buf_in = ctypes.create_string_buffer(data, max((len(data) + 3) & ~3, 4))
+        buf = ctypes.create_string_buffer(max(out_cap, 1))
+        r = Result()
+        aux = (ctypes.c_uint32 * 4)()
+        info = (ctypes.c_uint32 * 4)()
+        self.lib.emul_decode_seg.argtypes = [ctypes.c_char_p, ctypes.c_size_t, ctypes.c_void_p, ctypes.c_size_t, ctypes.c_int,
+                                             ctypes.c_uint32, ctypes.c_uint32, ctypes.POINTER(Result), ctypes.c_void_p, ctypes.c_void_p]
+        rc = self.lib.emul_decode_seg(buf_in, len(data), buf if out_cap else None, out_cap, wbits, segb,
+                                      seg_q if seg_q is not None else max(segb * 3 // 4, 64), ctypes.byref(r), aux, info)
+        assert rc != -1000
+        out = buf.raw[:min(r.total_out, out_cap)]
+        if aux[0]:
+            chk = (zlib.adler32(out) if aux[0] == 1 else zlib.crc32(out)) & 0xffffffff
+            self.lib.emul_finish(buf_in, len(data), ctypes.byref(r), aux, chk)
+        return r, out, tuple(info)
+
+
 _emul = None
 
 

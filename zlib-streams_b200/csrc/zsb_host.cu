@@ -12,6 +12,7 @@
 #include <string>
 #include <vector>
 #include "zsb_kernels.cuh"
+#include "zsb_seg.cuh"
 #include "zsb_internal.h"
 
 using namespace zsb;
@@ -440,6 +441,141 @@ static int launch_lane(zsb_ctx *ctx, zsb_dev &dv, const zsb_member *dm, zsb_resu
     return 0;
 }
 
+
+// ---- large members in segments (zsb_seg.cuh) ----------------------------------------------------------------------
+static inline uint32_t seg_q_of(const zsb_ctx *ctx) { return (uint32_t)(ctx->seg_bytes / 4 * 3); }   // sequences of arena per segment
+
+static int seg_configure(zsb_ctx *ctx, zsb_dev &dv) {
+    if (dv.seg_configured) return 0;
+    CK(ctx, cudaFuncSetAttribute(k_lane_seg, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)lane::SMEM));
+    CK(ctx, cudaFuncSetAttribute(k_lane_seg, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared));
+    CK(ctx, cudaFuncSetAttribute(k_seg_find, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)FIND_SMEM));
+    CK(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&dv.find_occ, k_seg_find, FIND_WARPS * 32, FIND_SMEM));
+    if (dv.find_occ < 1) dv.find_occ = 1;
+    dv.seg_configured = true;
+    return 0;
+}
+
+// The members `segm` (indices into dm / hm) through find -> k_lane_seg -> chain -> k_seg_lz -> fallback, in waves that
+// fit the sequence arena (dv.d_seq, already allocated by the caller).  Everything is queued on st.
+static int run_segmented(zsb_ctx *ctx, zsb_dev &dv, const zsb_member *dm, zsb_result *dr, const zsb_member *hm,
+                         const std::vector<uint32_t> &segm, cudaStream_t st) {
+    int rc;
+    if ((rc = lane_configure(ctx, dv)) || (rc = seg_configure(ctx, dv))) return rc;
+    const uint32_t segb = (uint32_t)ctx->seg_bytes, seg_q = seg_q_of(ctx);
+    const size_t nm = segm.size();
+    const uint64_t arena_seqs = dv.d_seq_cap / sizeof(lane::seq_t);
+    // waves: whole members, first-fit in order; slots and arena offsets restart in every wave
+    std::vector<seg::MemberPlan> plan(nm);
+    std::vector<size_t> wave_m, wave_slot;          // first member / first slot of each wave (+ end)
+    size_t nsegs = 0;
+    uint64_t run = 0;
+    uint32_t wslot = 0;
+    wave_m.push_back(0);
+    wave_slot.push_back(0);
+    for (size_t i = 0; i < nm; i++) {
+        const zsb_member &x = hm[segm[i]];
+        const uint32_t nseg = (uint32_t)((x.in_len + segb - 1) / segb);
+        const uint64_t want = (uint64_t)nseg * seg_q;
+        if (want > arena_seqs) {
+            snprintf(ctx->err, sizeof ctx->err, "sequence arena too small for a member of %zu bytes in segments", (size_t)x.in_len);
+            return ZSB_E_NOMEM;
+        }
+        if (run + want > arena_seqs) {
+            wave_m.push_back(i);
+            wave_slot.push_back(nsegs);
+            run = 0;
+            wslot = 0;
+        }
+        plan[i].idx = segm[i]; plan[i].first = wslot; plan[i].nseg = nseg; plan[i].pad = 0; plan[i].seq_off = run;
+        run += want;
+        wslot += nseg;
+        nsegs += nseg;
+    }
+    wave_m.push_back(nm);
+    wave_slot.push_back(nsegs);
+    if (nsegs > 0x7fffffffull) return ZSB_E_ARG;
+    // device buffers: plan | fail order | counters | per-slot sequence offsets | segment records
+    auto up = [](size_t v) { return (v + 255) & ~(size_t)255; };
+    const size_t o_plan = 0, o_fail = o_plan + up(nm * sizeof(seg::MemberPlan)), o_cnt = o_fail + up(nm * 4),
+                 o_off = o_cnt + up((wave_m.size() * 4 + 4) * 4), o_seg = o_off + up(nsegs * 8), total = o_seg + up(nsegs * sizeof(lane::Seg));
+    if ((rc = grow(ctx, dv.d_segbuf, dv.d_segbuf_cap, total))) return rc;
+    uint8_t *base = dv.d_segbuf;
+    seg::MemberPlan *dplan = (seg::MemberPlan *)(base + o_plan);
+    uint32_t *dfail = (uint32_t *)(base + o_fail), *dcnt = (uint32_t *)(base + o_cnt);
+    uint64_t *doff = (uint64_t *)(base + o_off);
+    lane::Seg *dsegs = (lane::Seg *)(base + o_seg);
+    CK(ctx, cudaMemcpyAsync(dplan, plan.data(), nm * sizeof(seg::MemberPlan), cudaMemcpyHostToDevice, st));
+    CK(ctx, cudaMemsetAsync(dcnt, 0, (wave_m.size() * 4 + 4) * 4, st));
+    static const bool trace = getenv("ZSB_TRACE") != nullptr;
+    if (trace) fprintf(stderr, "zsb trace segments: %zu members, %zu segments of %u bytes, %zu wave(s)\n", nm, nsegs, segb, wave_m.size() - 1);
+    for (size_t w = 0; w + 1 < wave_m.size(); w++) {
+        const size_t m0 = wave_m[w], mc = wave_m[w + 1] - m0, s0 = wave_slot[w], sn = wave_slot[w + 1] - s0;
+        uint32_t *cnt = dcnt + 4 * w;               // [0] find, [1] lanes, [2] resolve, [3] fallback
+        k_seg_init<<<(unsigned)((mc + 127) / 128), 128, 0, st>>>(dplan + m0, (uint32_t)mc, dsegs + s0, doff + s0, seg_q);
+        ctx->launches++;
+        CK(ctx, cudaGetLastError());
+        k_seg_sync<<<(unsigned)((sn + SYNC_THREADS - 1) / SYNC_THREADS), SYNC_THREADS, 0, st>>>(dm, dsegs + s0, (uint32_t)sn, segb, dv.fixed_lane);
+        ctx->launches++;
+        CK(ctx, cudaGetLastError());
+        k_seg_find<<<(unsigned)std::min<size_t>((sn + FIND_WARPS - 1) / FIND_WARPS, (size_t)dv.sm_count * dv.find_occ), FIND_WARPS * 32, FIND_SMEM, st>>>(
+            dm, dsegs + s0, (uint32_t)sn, segb, cnt);
+        ctx->launches++;
+        CK(ctx, cudaGetLastError());
+        k_seg_plan<<<(unsigned)((mc + 127) / 128), 128, 0, st>>>(dm, dplan + m0, (uint32_t)mc, dsegs + s0, segb);
+        ctx->launches++;
+        CK(ctx, cudaGetLastError());
+        lane::Batch B;
+        B.segs = dsegs + s0;
+        B.seg_q = seg_q;
+        B.members = dm;
+        B.results = dr;
+        B.aux = dv.aux;
+        B.order = nullptr;
+        B.seq_off = doff + s0;
+        B.seq_base = (lane::seq_t *)dv.d_seq;
+        B.hist = nullptr;
+        B.n = (uint32_t)sn;
+        B.counter = cnt + 1;
+        B.fixed_tab = dv.fixed_lane;
+        const size_t per_sm = (sn + dv.sm_count - 1) / dv.sm_count;
+        const size_t warps = std::min<size_t>(lane::WARPS, std::max<size_t>(1, (per_sm + 31) / 32)), per_cta = warps * 32;
+        k_lane_seg<<<(unsigned)std::max<size_t>(1, std::min((sn + per_cta - 1) / per_cta, (size_t)dv.sm_count)), (unsigned)per_cta,
+                     lane::smem_for(warps), st>>>(B);
+        ctx->launches++;
+        CK(ctx, cudaGetLastError());
+        k_seg_chain<<<(unsigned)((mc + 127) / 128), 128, 0, st>>>(B, dplan + m0, (uint32_t)mc, dfail + m0);
+        ctx->launches++;
+        CK(ctx, cudaGetLastError());
+        if (mc <= (size_t)dv.sm_count * 4)          // few members: a CTA each (their length decides); many: a warp each (throughput)
+            k_seg_lz_cta<<<(unsigned)mc, SEGLZ_THREADS, 0, st>>>(B, dplan + m0, (uint32_t)mc, doff + s0, cnt + 2);
+        else
+            k_seg_lz<<<(unsigned)std::max<size_t>(1, std::min((mc + SEGLZ_WARPS - 1) / SEGLZ_WARPS, (size_t)dv.sm_count * 8)), SEGLZ_THREADS, 0, st>>>(
+                B, dplan + m0, (uint32_t)mc, doff + s0, cnt + 2);
+        ctx->launches++;
+        CK(ctx, cudaGetLastError());
+        // the members whose chain did not hold: serially, a warp each (slots of the others are empty)
+        lane::Batch F;
+        F.members = dm;
+        F.results = dr;
+        F.aux = dv.aux;
+        F.order = dfail + m0;
+        F.seq_off = doff + s0;                      // (read by no one: k_big keeps its sequences in shared memory)
+        F.seq_base = (lane::seq_t *)dv.d_seq;
+        F.hist = nullptr;
+        F.n = (uint32_t)mc;
+        F.counter = cnt + 3;
+        F.fixed_tab = dv.fixed_lane;
+        const size_t bper_sm = (mc + dv.sm_count - 1) / dv.sm_count;
+        const size_t bwarps = std::min<size_t>(BIG_WARPS, std::max<size_t>(1, bper_sm));
+        k_big<<<(unsigned)std::max<size_t>(1, std::min((mc + bwarps - 1) / bwarps, (size_t)dv.sm_count * dv.big_occ)), (unsigned)(bwarps * 32),
+                LUT_BYTES + bwarps * BIG_PER_WARP, st>>>(F);
+        ctx->launches++;
+        CK(ctx, cudaGetLastError());
+    }
+    return 0;
+}
+
 static int pipe_stream_limit();
 
 // dm/dr: device arrays; hm: host copy of the descriptors; horder: host slot order (NULL = identity)
@@ -465,26 +601,42 @@ static int run_device(zsb_ctx *ctx, zsb_dev &dv, size_t n, const zsb_member *dm,
     uint32_t *counters = sc ? sc->counters : dv.counters;
     size_t nparts = 1;
     std::vector<size_t> part_start;
+    size_t ns = n;                         // slots of the lane / group paths (n less the segmented members)
+    std::vector<uint32_t> segm;            // members decoded in segments
+    uint64_t seg_want = 0;                 // sequences of arena the segmented part would like
     if (!planned) {
         if (!horder) {
             own.resize(n);
             for (size_t i = 0; i < n; i++) own[i] = (uint32_t)i;
             if (ctx->path == 0)          // largest first: lanes finish together, and the split needs it
                 sort_largest_first(own.data(), n, [&](uint32_t a) { return (uint64_t)hm[a].in_len + hm[a].out_cap; });
+            // members large enough to be decoded in segments (zsb_seg.cuh) leave the slot order
+            if (!sc && ctx->path == 0 && ctx->segment && ctx->split_big != 2) {
+                size_t keep = 0;
+                for (size_t i = 0; i < n; i++) {
+                    const zsb_member &x = hm[own[i]];
+                    // (a member that does not shrink is stored blocks or as good as: the serial path copies those at memory speed)
+                    if (x.in_len >= ctx->seg_min && x.in_len <= 0xfffffff0ull && !(x.flags & ZSB_M_STORED) &&
+                        (uint64_t)x.in_len * 16 < (uint64_t)x.out_cap * 15)
+                        segm.push_back(own[i]);
+                    else own[keep++] = own[i];
+                }
+                ns = keep;
+            }
             horder = own.data();
         }
-        if (ctx->path == 0 && ctx->split_big) nbig = ctx->split_big == 2 ? n : split_big(hm, horder, n, dv.sm_count);
+        if (ctx->path == 0 && ctx->split_big) nbig = ctx->split_big == 2 ? ns : split_big(hm, horder, ns, dv.sm_count);
         // Overlapped parts (option "overlap_parts" > 1, an experiment kept for measurement): the lane path's members
         // are dealt out to K parts, each with its own k_lane + k_lz pair on a stream of its own.  Measured on C2 inside
         // one call: 30.8 ms with 8 parts against 30.7 ms with one, and C5 475 ms against 362 ms — the 25.6 ms of
         // scripts/overlap_experiment.py came from consecutive STEPS overlapping each other, not from the parts of a step.
-        if (!sc && ctx->path != 2 && ctx->overlap_parts > 1 && n - nbig >= 2 * PART_MIN) {
-            nparts = (size_t)std::min<long>(std::min<long>(ctx->overlap_parts, pipe_stream_limit()), (long)((n - nbig) / PART_MIN));
+        if (!sc && ctx->path != 2 && ctx->overlap_parts > 1 && ns - nbig >= 2 * PART_MIN) {
+            nparts = (size_t)std::min<long>(std::min<long>(ctx->overlap_parts, pipe_stream_limit()), (long)((ns - nbig) / PART_MIN));
             if (nparts < 2) nparts = 1;
         }
         if (nparts > 1) {                        // part p = slots p, p + K, ... of the (largest first) order, made contiguous
-            if (own.empty()) own.assign(horder, horder + n);
-            const size_t m = n - nbig;
+            if (own.empty()) own.assign(horder, horder + ns);
+            const size_t m = ns - nbig;
             std::vector<uint32_t> tmp(m);
             size_t j = 0;
             part_start.assign(nparts + 1, 0);
@@ -496,15 +648,20 @@ static int run_device(zsb_ctx *ctx, zsb_dev &dv, size_t n, const zsb_member *dm,
             memcpy(own.data() + nbig, tmp.data(), m * sizeof(uint32_t));
             horder = own.data();
         }
-        CK(ctx, cudaMemcpyAsync(dorder, horder, n * sizeof(uint32_t), cudaMemcpyHostToDevice, st));
+        if (ns) CK(ctx, cudaMemcpyAsync(dorder, horder, ns * sizeof(uint32_t), cudaMemcpyHostToDevice, st));
         CK(ctx, cudaMemsetAsync(counters, 0, 8 * nparts * sizeof(uint32_t), st));
         if (ctx->path != 2) {
             off_own.resize(n);
-            uint64_t need = plan_parts(hm, horder, n, nbig, (sc ? sc->seq_bytes : arena_bytes(ctx, dv)) / sizeof(lane::seq_t),
+            if (!segm.empty()) {               // the segmented part shares the arena: as much as it can use, within the budget
+                for (uint32_t i : segm) seg_want += ((hm[i].in_len + ctx->seg_bytes - 1) / ctx->seg_bytes) * (uint64_t)seg_q_of(ctx);
+                seg_want = std::min<uint64_t>(seg_want, arena_bytes(ctx, dv) / sizeof(lane::seq_t));
+            }
+            uint64_t need = plan_parts(hm, horder, ns, nbig, (sc ? sc->seq_bytes : arena_bytes(ctx, dv)) / sizeof(lane::seq_t),
                                        off_own.data(), cuts_big_own, cuts_own, big_seqs);
             if (!sc && cuts_own.size() > 2 && !ctx->seq_arena_bytes)      // sliced: is more memory free by now?
-                need = plan_parts(hm, horder, n, nbig, arena_bytes(ctx, dv, true) / sizeof(lane::seq_t), off_own.data(),
+                need = plan_parts(hm, horder, ns, nbig, arena_bytes(ctx, dv, true) / sizeof(lane::seq_t), off_own.data(),
                                   cuts_big_own, cuts_own, big_seqs);
+            need = std::max(need, seg_want);
             if (!sc) {
                 // the arena: when the device cannot give it (another process took the memory since the last query),
                 // decode in more slices of half the size rather than fail
@@ -521,19 +678,24 @@ static int run_device(zsb_ctx *ctx, zsb_dev &dv, size_t n, const zsb_member *dm,
                     }
                     cudaGetLastError();
                     uint64_t largest = 0;
-                    for (size_t s = nbig; s < n; s++) largest = std::max(largest, seq_bound(hm[horder[s]]));
+                    for (size_t s = nbig; s < ns; s++) largest = std::max(largest, seq_bound(hm[horder[s]]));
+                    if (seg_want > largest && need == seg_want) {      // the segmented part asked for it: it can do with less
+                        seg_want /= 2;
+                        need = std::max(plan_parts(hm, horder, ns, nbig, arena, off_own.data(), cuts_big_own, cuts_own, big_seqs), seg_want);
+                        continue;
+                    }
                     if (arena <= largest || ctx->seq_arena_bytes) {
                         snprintf(ctx->err, sizeof ctx->err, "out of device memory for %zu bytes of sequence scratch", want);
                         return ZSB_E_CUDA;
                     }
                     arena = std::max(largest, std::min(arena, need) / 2);
                     dv.arena_auto = (size_t)arena * sizeof(lane::seq_t);
-                    need = plan_parts(hm, horder, n, nbig, arena, off_own.data(), cuts_big_own, cuts_own, big_seqs);
+                    need = std::max(plan_parts(hm, horder, ns, nbig, arena, off_own.data(), cuts_big_own, cuts_own, big_seqs), seg_want);
                 }
             }
             if (cuts_own.size() > 2) nparts = 1;       // sliced by the arena: the slices run one after the other
             // (a pageable source is staged by the runtime before cudaMemcpyAsync returns, so off_own may go)
-            CK(ctx, cudaMemcpyAsync(dseqoff, off_own.data(), n * sizeof(uint64_t), cudaMemcpyHostToDevice, st));
+            if (ns) CK(ctx, cudaMemcpyAsync(dseqoff, off_own.data(), ns * sizeof(uint64_t), cudaMemcpyHostToDevice, st));
         }
     }
     {
@@ -551,7 +713,7 @@ static int run_device(zsb_ctx *ctx, zsb_dev &dv, size_t n, const zsb_member *dm,
         P.small_ctas = sc && sc->small_ctas;
         lane::seq_t *seq0 = (lane::seq_t *)(sc ? sc->seq : dv.d_seq);
         // the large members, a warp each, on the group stream beside the rest on the caller's (fork / join by events)
-        const bool fork = nbig && nbig < n;
+        const bool fork = nbig && nbig < ns;
         if (nbig) {
             P.dorder = dorder; P.dseqoff = dseqoff; P.cuts = cuts_big; P.seq_base = seq0;
             P.counters = counters + 4; P.big = true; P.timed = false;
@@ -563,7 +725,7 @@ static int run_device(zsb_ctx *ctx, zsb_dev &dv, size_t n, const zsb_member *dm,
             if ((rc = launch_lane(ctx, dv, dm, dr, P))) return rc;
             if (fork) CK(ctx, cudaEventRecord(dv.ev_join, dv.group_stream));
         }
-        if (nbig < n && nparts > 1) {
+        if (nbig < ns && nparts > 1) {
             while (dv.pipe_streams.size() < nparts + 1) {
                 cudaStream_t ns;
                 CK(ctx, cudaStreamCreateWithFlags(&ns, cudaStreamNonBlocking));
@@ -607,12 +769,13 @@ static int run_device(zsb_ctx *ctx, zsb_dev &dv, size_t n, const zsb_member *dm,
                 CK(ctx, cudaEventRecord(pe[1], st));
                 CK(ctx, cudaEventRecord(pe[2], st));
             }
-        } else if (nbig < n) {
+        } else if (nbig < ns) {
             P.dorder = dorder + nbig; P.dseqoff = dseqoff + nbig; P.cuts = cuts; P.seq_base = seq0;
             P.counters = counters; P.big = false; P.timed = true; P.st = st;
             if ((rc = launch_lane(ctx, dv, dm, dr, P))) return rc;
         }
         if (fork) CK(ctx, cudaStreamWaitEvent(st, dv.ev_join, 0));
+        if (!segm.empty() && (rc = run_segmented(ctx, dv, dm, dr, hm, segm, st))) return rc;
     }
     if (!(flags & ZSB_RAW_ONLY)) {
         unsigned grid = (unsigned)std::min<size_t>(n, (size_t)dv.sm_count * 8);
@@ -710,6 +873,7 @@ static void free_device(zsb_dev &dv) {
     cudaFree(dv.d_out);
     cudaFree(dv.d_desc);
     cudaFree(dv.d_df);
+    cudaFree(dv.d_segbuf);
     if (dv.h_desc) cudaFreeHost(dv.h_desc);
     for (cudaEvent_t e : dv.prof_ev) cudaEventDestroy(e);
     dv.prof_ev.clear();
@@ -791,6 +955,20 @@ extern "C" int zsb_set_option(zsb_ctx *ctx, const char *name, long value) {
         ctx->path = (int)value;
         return 0;
     }
+    if (!strcmp(name, "segment")) {               // 1 (default): members of seg_min compressed bytes or more are decoded in segments
+        ctx->segment = value != 0;
+        return 0;
+    }
+    if (!strcmp(name, "seg_bytes")) {             // compressed bytes between the block starts looked for
+        if (value < 256 || value > (1 << 24)) return ZSB_E_ARG;
+        ctx->seg_bytes = (size_t)value;
+        return 0;
+    }
+    if (!strcmp(name, "seg_min")) {               // smallest member (compressed bytes) that is segmented
+        if (value < 64) return ZSB_E_ARG;
+        ctx->seg_min = (size_t)value;
+        return 0;
+    }
     if (!strcmp(name, "overlap_parts")) {         // device-resident batches: parts decoded side by side (1 = off)
         if (value < 1 || value > 16) return ZSB_E_ARG;
         ctx->overlap_parts = (int)value;
@@ -810,6 +988,9 @@ extern "C" long zsb_get_option(const zsb_ctx *ctx, const char *name) {
     if (!strcmp(name, "path")) return ctx->path;
     if (!strcmp(name, "chunks")) return ctx->chunks;
     if (!strcmp(name, "overlap_parts")) return ctx->overlap_parts;
+    if (!strcmp(name, "segment")) return ctx->segment;
+    if (!strcmp(name, "seg_bytes")) return (long)ctx->seg_bytes;
+    if (!strcmp(name, "seg_min")) return (long)ctx->seg_min;
     if (!strcmp(name, "seq_arena_bytes")) return (long)ctx->seq_arena_bytes;
     if (!strcmp(name, "sm_count")) return ctx->devs.empty() ? 0 : ctx->devs[0].sm_count;
     return ZSB_E_ARG;

@@ -33,6 +33,10 @@ struct zsb_dev {
     size_t d_in_cap = 0, d_out_cap = 0, d_desc_cap = 0;
     uint8_t *d_df = nullptr;           // zsb_deflate_batch: descriptors, token scratch, block scratch, staging
     size_t d_df_cap = 0;
+    uint8_t *d_segbuf = nullptr;       // segmented members: plans, segment records, per-slot sequence offsets
+    size_t d_segbuf_cap = 0;
+    bool seg_configured = false;
+    int find_occ = 0;
     uint8_t *h_desc = nullptr;
     size_t h_desc_cap = 0;
     bool configured[33] = {};
@@ -56,6 +60,8 @@ struct zsb_ctx {
     bool force_small_ctas = false;
     int split_big = 1;                 // path 0: 1 = members far larger than the rest get a warp each (k_big,
                                        // split_big()), 0 = never, 2 = every member (tests)
+    int segment = 1;                   // members of seg_min compressed bytes or more are decoded in segments (zsb_seg.cuh)
+    size_t seg_bytes = 32768, seg_min = 131072;
     int profile = 0;                   // 1: record per-kernel events (zsb_profile_read)
     char err[256] = "";
 };

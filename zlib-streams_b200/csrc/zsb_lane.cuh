@@ -108,6 +108,7 @@ struct Lane {
                          // through cp.async, so a refill never waits on a load scoreboard
     seq_t *seq;          // where this member's next sequence goes
     seq_t *seq0;         // start of its sequence array
+    seq_t *seq_lim;      // k_lane_seg: end of the arena range the segment may fill
     uint32_t lw, nl;     // literals waiting for their sequence
     uint32_t hist;       // valid bytes of history before out[0] (0 for one-shot members)
     uint32_t nlen, ndist;
@@ -593,7 +594,10 @@ ZSB_DEV bool build_clen8(uint8_t *T, bool d64) {
     return true;
 }
 
-ZSB_DEV int lane_dynamic_header(Lane &L, uint8_t *T, const uint32_t *lut) {
+// EARLY (the block-start search of zsb_seg.cuh, which tries positions that are mostly no headers): give up as soon as
+// the lengths read so far over-subscribe the literal/length or the distance code — sets build_tables would refuse.
+template <bool EARLY>
+ZSB_DEV int lane_dynamic_header_t(Lane &L, uint8_t *T, const uint32_t *lut) {
     Dec &d = L.d;
     BitIn &b = d.b;
     uint8_t *lens = T + H_LENS;
@@ -636,6 +640,7 @@ ZSB_DEV int lane_dynamic_header(Lane &L, uint8_t *T, const uint32_t *lut) {
     }
     const uint8_t *C = T + H_CL;
     uint32_t have = 0, total = nlen + ndist;
+    uint32_t kl = 0, kd = 0;                      // EARLY: sums of 2^(15 - length) over the two codes
     while (have < total) {
         if (b.nbits < 32) bi_fill(b);
         uint32_t e = C[(uint32_t)b.hold & 127u];
@@ -643,6 +648,11 @@ ZSB_DEV int lane_dynamic_header(Lane &L, uint8_t *T, const uint32_t *lut) {
         if (nb > b.nbits) return EV_STARVE;
         if (sym < 16) {
             bi_drop(b, nb);
+            if (EARLY && sym) {
+                uint32_t &k = have < nlen ? kl : kd;
+                k += 32768u >> sym;
+                if (k > 32768u) return EV_ERR;
+            }
             lens[have++] = (uint8_t)sym;
             continue;
         }
@@ -664,7 +674,14 @@ ZSB_DEV int lane_dynamic_header(Lane &L, uint8_t *T, const uint32_t *lut) {
             d.msg = M_REPEAT;
             return EV_ERR;
         }
-        while (rep--) lens[have++] = (uint8_t)val;
+        while (rep--) {
+            if (EARLY && val) {
+                uint32_t &k = have < nlen ? kl : kd;
+                k += 32768u >> val;
+            }
+            lens[have++] = (uint8_t)val;
+        }
+        if (EARLY && (kl > 32768u || kd > 32768u)) return EV_ERR;
     }
     if (lens[256] == 0) {
         d.msg = M_NOEOB;
@@ -674,6 +691,7 @@ ZSB_DEV int lane_dynamic_header(Lane &L, uint8_t *T, const uint32_t *lut) {
     L.ndist = ndist;
     return EV_NONE;
 }
+ZSB_DEV int lane_dynamic_header(Lane &L, uint8_t *T, const uint32_t *lut) { return lane_dynamic_header_t<false>(L, T, lut); }
 
 // ------------------------------------------------------------------------------------------------
 // Table construction by the whole warp for ONE member (reference src/inftrees.c:33-321 decides what
@@ -849,7 +867,26 @@ ZSB_DEV int build_tables(uint8_t *T, uint8_t *scr, uint32_t nlen, uint32_t ndist
 // ------------------------------------------------------------------------------------------------
 enum : int { LS_FETCH = 0, LS_BLOCK = 1, LS_SYM = 2, LS_TAIL = 3, LS_IDLE = 4, LS_BUILD = 5, LS_FIXED = 6 };
 
+// A SEGMENT of a large member (zsb_seg.cuh): the blocks between two block starts that k_seg_find found near
+// multiples of `segb` compressed bytes.  k_lane_seg decodes a segment like a member of its own (one lane, its own
+// range of the sequence arena); k_seg_chain then checks that every segment ended exactly where the next one began.
+constexpr uint64_t SEG_NONE = ~0ull;
+enum : int { EV_SEGEND = 11, EV_SEGFULL = 12, EV_ABSENT = 13 };
+struct Seg {
+    uint32_t member, k, first, nseg;    // member index; ordinal; slot of the member's segment 0; its segment count
+    uint64_t start_bit;                 // bit position of the block header it starts at (k = 0: 0); SEG_NONE: no start found
+    uint64_t target;                    // where it has to stop: the next found start (SEG_NONE: the member's end)
+    int32_t ev, msg;                    // how it ended (EV_*), message id
+    uint32_t pos, next, nbits, extent, at_type, last;   // Dec / BitIn at the end (pos = bytes the segment produced)
+    uint32_t nseq;                      // sequences written
+    uint32_t kind, adler0, hdr_tin, hdr_bits, hdr_stop;  // k = 0: the wrapper (Mem)
+    uint32_t base;                      // k_seg_chain: output position of the segment's first byte
+    uint32_t live;                      // k_seg_chain: 1 = part of the verified chain (resolve it)
+};
+
 struct Batch {
+    Seg *segs = nullptr;         // k_lane_seg: slots are segments (order is not used); NULL everywhere else
+    uint32_t seg_q = 0;          // sequences of arena per segment
     const zsb_member *members;
     zsb_result *results;
     Aux *aux;
@@ -864,13 +901,21 @@ struct Batch {
 
 ZSB_DEV void finish(Lane &L, int ev, const Batch &B) {
     flush_literals(L);
+    if (B.segs) {                      // a segment: the state goes to its record, k_seg_chain writes the member's result
+        Seg &g = B.segs[L.mm.idx];
+        g.ev = ev; g.msg = L.d.msg; g.pos = L.d.pos; g.next = L.d.b.next; g.nbits = L.d.b.nbits; g.extent = L.d.extent;
+        g.at_type = L.d.at_type; g.last = L.d.last; g.nseq = (uint32_t)(L.seq - L.seq0);
+        g.kind = L.mm.kind; g.adler0 = L.mm.adler0; g.hdr_tin = L.mm.hdr_tin; g.hdr_bits = L.mm.hdr_bits; g.hdr_stop = L.mm.hdr_stop;
+        return;
+    }
     write_result(L.d, L.mm, ev, B.results + L.mm.idx, B.aux + L.mm.idx);
     B.aux[L.mm.idx].nseq = L.q0 ? 0u : (uint32_t)(L.seq - L.seq0);      // k_big resolves its own sequences
 }
 
 // descriptor + wrapper header of a new member; returns the lane's next state
 ZSB_DEV int start_member(Lane &L, uint32_t slot, const Batch &B) {
-    const uint32_t idx = B.order[slot];
+    const uint32_t idx = B.segs ? B.segs[slot].member : B.order[slot];
+    if (idx == 0xffffffffu) return LS_FETCH;        // an empty slot (the fallback list of the segmented members)
     const zsb_member m = B.members[idx];
     Dec &d = L.d;
     Mem &mm = L.mm;
@@ -888,6 +933,36 @@ ZSB_DEV int start_member(Lane &L, uint32_t slot, const Batch &B) {
     L.lw = 0; L.nl = 0; L.mode = 0; L.pl = 0;
     L.hist = B.hist ? B.hist[idx] : 0u;
     int ev = EV_NONE;
+    if (B.segs) {
+        Seg &g = B.segs[slot];
+        mm.idx = slot;
+        // it stops at the next start that was found, and may write sequences up to that segment's range
+        uint32_t j = g.k + 1;
+        while (j < g.nseg && B.segs[g.first + j].start_bit == SEG_NONE) j++;
+        g.target = j < g.nseg ? B.segs[g.first + j].start_bit : SEG_NONE;
+        L.seq_lim = L.seq0 + (size_t)(j - g.k) * B.seg_q;
+        if (!g.k && g.start_bit == SEG_NONE) {       // the member is not decoded in segments after all (seg::plan_member)
+            g.ev = EV_SEGFULL;
+            g.nseq = 0;
+            return LS_FETCH;
+        }
+        if (g.k) {
+            if (g.start_bit == SEG_NONE) {
+                g.ev = EV_ABSENT;
+                g.nseq = 0;
+                return LS_FETCH;
+            }
+            // a block header in the middle of the member: no wrapper, unknown output position (at least a window's
+            // worth, k_seg_chain checks), no capacity of its own
+            bi_seek(d.b, (uint32_t)(g.start_bit >> 3));
+            bi_need(d.b, 8);
+            bi_drop(d.b, (uint32_t)(g.start_bit & 7u));
+            d.cap = 0xfffffff0u;
+            d.at_type = 1;
+            L.hist = 65536u;
+            return LS_BLOCK;
+        }
+    }
     if (m.flags & ZSB_M_STORED) {          // copied (and checked) by k_check; nothing to decode
         Aux a;
         a.kind = 0; a.trailer_pos = 0; a.need_trailer = 0; a.init_check = 0; a.nseq = 0;
@@ -928,6 +1003,16 @@ ZSB_DEV int lane_block(Lane &L, uint8_t *T, const uint32_t *lut, const Batch &B)
         if (d.last) {
             finish(L, EV_DONE, B);
             return LS_FETCH;
+        }
+        if (B.segs) {                              // a segment ends at the first block boundary at or behind its target
+            if (bi_bitpos(b) >= B.segs[L.mm.idx].target) {
+                finish(L, EV_SEGEND, B);
+                return LS_FETCH;
+            }
+            if (L.seq + 16 > L.seq_lim) {
+                finish(L, EV_SEGFULL, B);
+                return LS_FETCH;
+            }
         }
         if (!bi_need(b, 3)) {
             finish(L, EV_STARVE, B);
@@ -991,7 +1076,7 @@ ZSB_DEV int lane_block(Lane &L, uint8_t *T, const uint32_t *lut, const Batch &B)
 
 // BIG: one member per warp (lane 0 decodes with the direct tables at `big_lut`, big_run); the other lanes
 // only help to build tables.
-template <int W, bool BIG = false>
+template <int W, bool BIG = false, bool SEG = false>
 __device__ __forceinline__ void warp_lanes(const Batch &B, uint8_t *slots, uint8_t *scr, uint32_t *rings, const uint32_t *lut, int lane,
                                            uint32_t *big_lut = nullptr, seq_t *big_q = nullptr) {
     Lane L;
@@ -1001,7 +1086,7 @@ __device__ __forceinline__ void warp_lanes(const Batch &B, uint8_t *slots, uint8
     L.ring = rings + lane * (RING_STRIDE == 1 ? RING_WORDS : 1);
     L.d.pos = 0; L.d.cap = 0; L.d.b.p = nullptr; L.d.b.len = 0; L.d.b.next = 0; L.d.b.nbits = 0; L.d.b.hold = 0;
     L.d.d64 = 0; L.d.msg = 0; L.nl = 0; L.lw = 0; L.seq = L.seq0 = nullptr; L.nlen = 0; L.ndist = 0;
-    L.mm.idx = 0; L.mode = 0; L.pl = 0; L.hist = 0;
+    L.mm.idx = 0; L.mode = 0; L.pl = 0; L.hist = 0; L.seq_lim = nullptr;
 #if defined(__CUDA_ARCH__)
     L.ring_sa = (uint32_t)__cvta_generic_to_shared(L.ring);
 #else
@@ -1013,6 +1098,10 @@ __device__ __forceinline__ void warp_lanes(const Batch &B, uint8_t *slots, uint8
     const unsigned lt = (1u << lane) - 1u;
 
     for (;;) {
+        if (SEG && st == LS_SYM && L.seq + 16 > L.seq_lim) {           // the segment's arena range is full: the member falls back
+            finish(L, EV_SEGFULL, B);
+            st = LS_FETCH;
+        }
         // ---------------- service: until every lane is decoding symbols or out of work ----------------
         for (;;) {
             if (BIG) big_flush<W>(L, big_q, lane);       // before a new member is fetched, a block is read, the tail goes on
@@ -1067,6 +1156,11 @@ __device__ __forceinline__ void warp_lanes(const Batch &B, uint8_t *slots, uint8
             if (st == LS_SYM && L.d.b.next + 8 > L.d.b.len) st = LS_TAIL;
             while (st == LS_TAIL) {             // the last bytes of a member: every step checked
                 if (BIG && L.seq + 8 > L.qend) break;  // k_big: the queue is emptied at the top of the service loop
+                if (SEG && L.seq + 16 > L.seq_lim) {
+                    finish(L, EV_SEGFULL, B);
+                    st = LS_FETCH;
+                    break;
+                }
                 if (L.mode) L.d.mlen = L.pl;          // the loop stopped between a length and its distance
                 int e2 = careful_symbol(L.d, T, lut, L.mode != 0);
                 L.mode = 0;
@@ -1105,7 +1199,7 @@ __device__ __forceinline__ void warp_lanes(const Batch &B, uint8_t *slots, uint8
                 if (st == LS_SYM) {
                     if (L.d.b.next + 8 > L.d.b.len || !fast_step(L, T, lut)) st = LS_TAIL;
                 }
-                if (Wp<W>::any(st != LS_SYM && st != LS_IDLE)) break;
+                if (Wp<W>::any((st != LS_SYM && st != LS_IDLE) || (SEG && st == LS_SYM && L.seq + 16 > L.seq_lim))) break;
             }
         }
     }
