@@ -121,6 +121,7 @@ extern "C" int emul_decode_seg(const uint8_t *in, size_t in_len, uint8_t *out, s
                                uint32_t seg_q, zsb_result *res, uint32_t *aux4, uint32_t *info) {
     using namespace zsb;
     alignas(16) static uint32_t fixLL[lane::BIG_LUT_BYTES / 4];
+    static uint16_t ktab[seg::KTAB_ENTRIES];
     static uint8_t fixed[lane::SLOT];
     static uint32_t lut[LUT_WORDS];
     static bool init = false;
@@ -133,6 +134,7 @@ extern "C" int emul_decode_seg(const uint8_t *in, size_t in_len, uint8_t *out, s
         lane::build_tables<1>(T0, scr, 288, 32, false, 0);
         memcpy(fixed, T0, sizeof fixed);
         lane::big_build<1>(fixLL, fixed, lut, 0u, 0);
+        for (uint32_t i = 0; i < (uint32_t)seg::KTAB_ENTRIES; i++) ktab[i] = seg::ktab_entry(i);
         init = true;
     }
     alignas(16) uint8_t T[lane::SLOT];
@@ -156,7 +158,7 @@ extern "C" int emul_decode_seg(const uint8_t *in, size_t in_len, uint8_t *out, s
             g.start_bit = seg::find_sync_fixed<1>(true, in, (uint32_t)in_len, 8ull * k * segb, 8ull * k * segb + 16ull * segb, fixLL);
         if (k && g.start_bit != lane::SEG_NONE) found++;
         else if (k && (uint64_t)k * segb >= seg::first_start(wbits == -16)) {
-            g.start_bit = seg::find_start<1>(in, (uint32_t)in_len, wbits == -16, 8ull * k * segb, 8ull * (k + 1) * segb, fsm, lut, 0);
+            g.start_bit = seg::find_start<1>(in, (uint32_t)in_len, wbits == -16, 8ull * k * segb, 8ull * (k + 1) * segb, fsm, ktab, lut, 0);
             if (g.start_bit != lane::SEG_NONE) found++;
         }
     }

@@ -45,13 +45,15 @@ ZSB_DEV uint32_t first_start(bool d64) { return d64 ? 81920u : 40960u; }
 // ---- the finder's per-warp shared memory (bytes) ----
 constexpr int F_STAGE_WORDS = 256;                    // input words staged per chunk (+ F_STAGE_PAD read-ahead)
 constexpr int F_STAGE_PAD = 4;
-constexpr int F_VSLOTS = 8;                           // headers validated side by side
+constexpr int F_VSLOTS = 4;                           // headers validated side by side
 constexpr int F_STAGE = 0;                            // u32[260]
-constexpr int F_Q1 = (F_STAGE_WORDS + F_STAGE_PAD) * 4;   // u32[64]: positions that passed the 13-bit test (within the chunk)
-constexpr int F_Q2 = F_Q1 + 64 * 4;                   // u32[48]: positions whose code-length code is complete (relative to `from`)
-constexpr int F_SLOTS = F_Q2 + 48 * 4;                // F_VSLOTS table slots of 480 bytes (16-byte aligned: 1488)
+constexpr int F_Q1_CAP = 1024 + 64;                   // u16: positions (within the chunk) that passed the 13-bit test
+constexpr int F_Q1 = (F_STAGE_WORDS + F_STAGE_PAD) * 4;
+constexpr int F_Q2 = F_Q1 + F_Q1_CAP * 2;             // u32[48]: positions whose code-length code is complete (relative to `from`)
+constexpr int F_SLOTS = F_Q2 + 48 * 4;                // F_VSLOTS table slots of 480 bytes (16-byte aligned: 3408)
 constexpr int F_SCR = F_SLOTS + F_VSLOTS * 480;       // the warp's build scratch
-constexpr int F_BYTES = F_SCR + lane::WSCR;           // 6,320
+constexpr int F_BYTES = F_SCR + lane::WSCR;           // 8,240
+constexpr int KTAB_ENTRIES = 4096;                    // u16 per 4 code-length-code lengths (12 bits): their sum of 2^(7-l)
 
 // Could a dynamic block start here?  Stage 1, the first 13 bits: BFINAL = 0, BTYPE = 2, HLIT and HDIST in range.
 ZSB_DEV bool maybe_header(uint32_t a, bool d64) {
@@ -73,6 +75,28 @@ ZSB_DEV bool complete_clen(uint32_t a, uint32_t b, uint32_t c) {
     return kraft == 128u;
 }
 ZSB_DEV uint32_t fsr32(uint32_t lo, uint32_t hi, uint32_t sh) { return sh ? (lo >> sh) | (hi << (32 - sh)) : lo; }
+ZSB_DEV uint16_t ktab_entry(uint32_t idx) {
+    uint32_t s = 0;
+    for (int f = 0; f < 4; f++) s += (128u >> ((idx >> (3 * f)) & 7u)) & 127u;
+    return (uint16_t)s;
+}
+// complete_clen() through the table: five lookups instead of nineteen shifts and adds
+ZSB_DEV bool complete_clen_tab(uint32_t a, uint32_t b, uint32_t c, const uint16_t *K) {
+    const uint32_t ncode = ((a >> 13) & 15u) + 4u;
+    uint64_t v = (((((uint64_t)b << 32) | a) >> 17) & ((1ull << 45) - 1ull)) | ((uint64_t)(((b >> 30) | (c << 2)) & 0xfffu) << 45);
+    v &= (1ull << (3u * ncode)) - 1ull;
+    const uint32_t sum = (uint32_t)K[(uint32_t)v & 4095u] + K[(uint32_t)(v >> 12) & 4095u] + K[(uint32_t)(v >> 24) & 4095u] +
+                         K[(uint32_t)(v >> 36) & 4095u] + K[(uint32_t)(v >> 48) & 4095u];
+    return sum == 128u;
+}
+// the 13-bit test (maybe_header) on the 32 positions of one word at once: bit p of the result = position p passes
+ZSB_DEV uint32_t header_mask(uint32_t w0, uint32_t w1, bool d64) {
+    const uint64_t x = ((uint64_t)w1 << 32) | w0, nx = ~x;
+    uint64_t M = nx & (nx >> 1) & (x >> 2);                              // BFINAL = 0, BTYPE = 2
+    M &= ~((x >> 4) & (x >> 5) & (x >> 6) & (x >> 7));                   // HLIT <= 29
+    if (!d64) M &= ~((x >> 9) & (x >> 10) & (x >> 11) & (x >> 12));      // HDIST <= 29
+    return (uint32_t)M;
+}
 
 // The first accepted start in [from, to) bits of the member's input, or SEG_NONE.  All lanes call; sm = F_BYTES of the
 // warp's shared memory.  The input is staged a chunk at a time (coalesced), positions go through two queues so that
@@ -84,7 +108,10 @@ struct Finder {
     uint32_t len;
     bool d64;
     uint64_t from;
-    uint32_t *stage, *q1, *q2;
+    uint32_t *stage, *q2;
+    uint16_t *q1;
+    const uint16_t *ktab;
+    uint32_t h1;                 // head of q1
     uint8_t *slots, *scr;
     const uint32_t *lut;
     int lane;
@@ -137,21 +164,20 @@ struct Finder {
         bool ok = false;
         uint32_t r = 0;
         if ((uint32_t)lane < take) {
-            r = q1[lane];
+            r = q1[h1 + lane];
             const uint32_t wi = r >> 5, sh = r & 31u;
             const uint32_t s0 = stage[wi], s1 = stage[wi + 1], s2 = stage[wi + 2], s3 = stage[wi + 3];
-            ok = complete_clen(fsr32(s0, s1, sh), fsr32(s1, s2, sh), fsr32(s2, s3, sh));
+            ok = complete_clen_tab(fsr32(s0, s1, sh), fsr32(s1, s2, sh), fsr32(s2, s3, sh), ktab);
         }
-        uint32_t keep = 0;
-        if ((uint32_t)lane + take < n1) keep = q1[lane + take];
-        Wp<W>::sync();
-        if ((uint32_t)lane + take < n1) q1[lane] = keep;
+        h1 += take;
         n1 -= take;
         const unsigned m = Wp<W>::ballot(ok);
-        if (ok) q2[n2 + (uint32_t)__popc(m & lt)] = (uint32_t)(Ac + r - A_from);
-        n2 += (uint32_t)__popc(m);
-        Wp<W>::sync();
-        while (n2 >= (uint32_t)F_VSLOTS && found == SEG_NONE) validate();
+        if (m) {
+            if (ok) q2[n2 + (uint32_t)__popc(m & lt)] = (uint32_t)(Ac + r - A_from);
+            n2 += (uint32_t)__popc(m);
+            Wp<W>::sync();
+            while (n2 >= (uint32_t)F_VSLOTS && found == SEG_NONE) validate();
+        }
     }
 
     ZSB_DEV uint64_t run(uint64_t to) {
@@ -171,26 +197,39 @@ struct Finder {
                 stage[i] = w0 + i < full_words ? __ldg(abase + w0 + i) : 0u;
             Wp<W>::sync();
             const uint64_t Aend = Ac + 32ull * F_STAGE_WORDS < A_to ? Ac + 32ull * F_STAGE_WORDS : A_to;
-            // stage 1: W positions per trip (chunk-relative position r; with W = 32 a trip is one staged word, shifted by the lane)
+            // stage 1: a word (32 positions) per lane and trip; the positions that pass go to q1 in order
             const uint32_t r_lo = A_from > Ac ? (uint32_t)(A_from - Ac) : 0u, r_hi = (uint32_t)(Aend - Ac);
-            uint32_t wnext = stage[0];
-            for (uint32_t r0 = 0; r0 < r_hi && found == SEG_NONE; r0 += W) {
-                const uint32_t r = r0 + (uint32_t)lane;
-                uint32_t a;
-                if (W == 32) {
-                    const uint32_t wcur = wnext;
-                    wnext = stage[(r0 >> 5) + 1];
-                    a = fsr32(wcur, wnext, (uint32_t)lane);
-                } else {
-                    a = fsr32(stage[r >> 5], stage[(r >> 5) + 1], r & 31u);
+            h1 = 0;
+            for (uint32_t j0 = 0; 32u * j0 < r_hi && found == SEG_NONE; j0 += W) {
+                const uint32_t j = j0 + (uint32_t)lane;
+                uint32_t m32 = 0;
+                if (32u * j < r_hi) {
+                    m32 = header_mask(stage[j], stage[j + 1], d64);
+                    if (32u * j < r_lo) m32 &= r_lo - 32u * j >= 32u ? 0u : ~0u << (r_lo - 32u * j);
+                    if (r_hi - 32u * j < 32u) m32 &= (1u << (r_hi - 32u * j)) - 1u;
                 }
-                const bool ok = maybe_header(a, d64) && r >= r_lo && r < r_hi;
-                const unsigned m = Wp<W>::ballot(ok);
-                if (m) {
-                    if (ok) q1[n1 + (uint32_t)__popc(m & lt)] = r;
-                    n1 += (uint32_t)__popc(m);
+                uint32_t incl = (uint32_t)__popc(m32);
+#pragma unroll
+                for (int o = 1; o < W; o <<= 1) {
+                    const uint32_t v = Wp<W>::shfl_up(incl, o);
+                    if (lane >= o) incl += v;
+                }
+                const uint32_t total = Wp<W>::shfl(incl, W - 1);
+                if (total) {
+                    uint32_t at = h1 + n1 + incl - (uint32_t)__popc(m32);
+                    while (m32) {
+                        q1[at++] = (uint16_t)(32u * j + (uint32_t)__ffs(m32) - 1u);
+                        m32 &= m32 - 1u;
+                    }
+                    n1 += total;
                     Wp<W>::sync();
-                    if (n1 >= (uint32_t)W) kraft(Ac, A_from);
+                    while (n1 >= (uint32_t)W && found == SEG_NONE) kraft(Ac, A_from);
+                    // the remainder (< W entries) back to the front of the queue
+                    const uint16_t keep = (uint32_t)lane < n1 ? q1[h1 + lane] : (uint16_t)0;
+                    Wp<W>::sync();
+                    if ((uint32_t)lane < n1) q1[lane] = keep;
+                    h1 = 0;
+                    Wp<W>::sync();
                 }
             }
             while (n1 && found == SEG_NONE) kraft(Ac, A_from);     // (q1 refers to this chunk)
@@ -202,10 +241,12 @@ struct Finder {
 };
 
 template <int W>
-ZSB_DEV uint64_t find_start(const uint8_t *in, uint32_t len, bool d64, uint64_t from, uint64_t to, uint8_t *sm, const uint32_t *lut, int lane) {
+ZSB_DEV uint64_t find_start(const uint8_t *in, uint32_t len, bool d64, uint64_t from, uint64_t to, uint8_t *sm, const uint16_t *ktab,
+                            const uint32_t *lut, int lane) {
     Finder<W> f;
     f.in = in; f.len = len; f.d64 = d64; f.from = from;
-    f.stage = (uint32_t *)(sm + F_STAGE); f.q1 = (uint32_t *)(sm + F_Q1); f.q2 = (uint32_t *)(sm + F_Q2);
+    f.stage = (uint32_t *)(sm + F_STAGE); f.q1 = (uint16_t *)(sm + F_Q1); f.q2 = (uint32_t *)(sm + F_Q2);
+    f.ktab = ktab; f.h1 = 0;
     f.slots = sm + F_SLOTS; f.scr = sm + F_SCR; f.lut = lut; f.lane = lane;
     f.lt = W == 32 ? ((1u << lane) - 1u) : 0u;
     return f.run(to);
@@ -398,15 +439,17 @@ __global__ void k_seg_init(const seg::MemberPlan *__restrict__ plan, uint32_t nm
 }
 
 constexpr int FIND_WARPS = 16;
-constexpr size_t FIND_SMEM = LUT_BYTES + FIND_WARPS * (size_t)seg::F_BYTES;
+constexpr size_t FIND_SMEM = LUT_BYTES + seg::KTAB_ENTRIES * 2 + FIND_WARPS * (size_t)seg::F_BYTES;
 __global__ void __launch_bounds__(FIND_WARPS * 32) k_seg_find(const zsb_member *__restrict__ members, lane::Seg *segs, uint32_t nsegs,
                                                               uint32_t segb, uint32_t *counter) {
     extern __shared__ __align__(16) uint8_t smem[];
     uint32_t *lut = (uint32_t *)smem;
     init_lut(lut, threadIdx.x, blockDim.x);
+    uint16_t *ktab = (uint16_t *)(smem + LUT_BYTES);
+    for (uint32_t i = threadIdx.x; i < (uint32_t)seg::KTAB_ENTRIES; i += blockDim.x) ktab[i] = seg::ktab_entry(i);
     __syncthreads();
     const int ln = threadIdx.x & 31, warp = threadIdx.x >> 5;
-    uint8_t *sm = smem + LUT_BYTES + (size_t)warp * seg::F_BYTES;
+    uint8_t *sm = smem + LUT_BYTES + seg::KTAB_ENTRIES * 2 + (size_t)warp * seg::F_BYTES;
     for (;;) {
         uint32_t slot = 0;
         if (ln == 0) slot = atomicAdd(counter, 1u);
@@ -418,7 +461,7 @@ __global__ void __launch_bounds__(FIND_WARPS * 32) k_seg_find(const zsb_member *
         const uint64_t from = 8ull * k * segb;
         if ((uint64_t)k * segb < seg::first_start(m.window_bits == -16)) continue;        // (stays SEG_NONE)
         const uint64_t found = seg::find_start<32>((const uint8_t *)m.in, (uint32_t)m.in_len, m.window_bits == -16, from,
-                                                   from + 8ull * segb, sm, lut, ln);
+                                                   from + 8ull * segb, sm, ktab, lut, ln);
         if (ln == 0) segs[slot].start_bit = found;
         __syncwarp();
     }
