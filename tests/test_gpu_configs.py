@@ -1,7 +1,8 @@
 """BASELINE.json configs C2, C3, C4, C5 at their full member counts on the GPU: every member's
 result record and output bytes are compared with the oracle's for its distinct member (tests/batchlib.py).
 The default engine path is used: lane path, members handed out largest first, members far larger than the
-rest of their batch decoded by the large-member path; C4 also runs without that split."""
+rest of their batch decoded by the large-member path, members of 128 KiB compressed or more in segments; C4 also
+runs without the split and without the segments."""
 import os
 
 import pytest
@@ -61,9 +62,13 @@ def test_c4_wrapped_mixed_sizes_with_checksums():
 def test_c4_large_members_get_their_own_path():
     w = workloads.c4(distinct=512, tiles=2)
     r = _run(w, split=True)
-    assert r["gpu_launches_per_step"] >= 4   # the large-member kernels beside k_lane + k_lz, then k_check
-    r = _run(w, split=False)
+    assert r["gpu_launches_per_step"] >= 11  # the segment kernels (zsb_seg.cuh) and k_big beside k_lane + k_lz, then k_check
+    r = _run(w, split=True, options=(("segment", 0),))
+    assert r["gpu_launches_per_step"] == 4   # k_big beside k_lane + k_lz, then k_check
+    r = _run(w, split=False, options=(("segment", 0),))
     assert r["gpu_launches_per_step"] == 3
+    r = _run(w, split=False)
+    assert r["gpu_launches_per_step"] >= 10
 
 
 def test_c5_zip_like_mix():

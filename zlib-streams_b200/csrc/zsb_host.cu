@@ -459,12 +459,11 @@ static int seg_configure(zsb_ctx *ctx, zsb_dev &dv) {
 // The members `segm` (indices into dm / hm) through find -> k_lane_seg -> chain -> k_seg_lz -> fallback, in waves that
 // fit the sequence arena (dv.d_seq, already allocated by the caller).  Everything is queued on st.
 static int run_segmented(zsb_ctx *ctx, zsb_dev &dv, const zsb_member *dm, zsb_result *dr, const zsb_member *hm,
-                         const std::vector<uint32_t> &segm, cudaStream_t st) {
+                         const std::vector<uint32_t> &segm, cudaStream_t st, lane::seq_t *arena, uint64_t arena_seqs) {
     int rc;
     if ((rc = lane_configure(ctx, dv)) || (rc = seg_configure(ctx, dv))) return rc;
     const uint32_t segb = (uint32_t)ctx->seg_bytes, seg_q = seg_q_of(ctx);
     const size_t nm = segm.size();
-    const uint64_t arena_seqs = dv.d_seq_cap / sizeof(lane::seq_t);
     // waves: whole members, first-fit in order; slots and arena offsets restart in every wave
     std::vector<seg::MemberPlan> plan(nm);
     std::vector<size_t> wave_m, wave_slot;          // first member / first slot of each wave (+ end)
@@ -533,7 +532,7 @@ static int run_segmented(zsb_ctx *ctx, zsb_dev &dv, const zsb_member *dm, zsb_re
         B.aux = dv.aux;
         B.order = nullptr;
         B.seq_off = doff + s0;
-        B.seq_base = (lane::seq_t *)dv.d_seq;
+        B.seq_base = arena;
         B.hist = nullptr;
         B.n = (uint32_t)sn;
         B.counter = cnt + 1;
@@ -561,7 +560,7 @@ static int run_segmented(zsb_ctx *ctx, zsb_dev &dv, const zsb_member *dm, zsb_re
         F.aux = dv.aux;
         F.order = dfail + m0;
         F.seq_off = doff + s0;                      // (read by no one: k_big keeps its sequences in shared memory)
-        F.seq_base = (lane::seq_t *)dv.d_seq;
+        F.seq_base = arena;
         F.hist = nullptr;
         F.n = (uint32_t)mc;
         F.counter = cnt + 3;
@@ -603,7 +602,8 @@ static int run_device(zsb_ctx *ctx, zsb_dev &dv, size_t n, const zsb_member *dm,
     std::vector<size_t> part_start;
     size_t ns = n;                         // slots of the lane / group paths (n less the segmented members)
     std::vector<uint32_t> segm;            // members decoded in segments
-    uint64_t seg_want = 0;                 // sequences of arena the segmented part would like
+    uint64_t seg_want = 0, seg_least = 0;  // sequences of arena the segmented part would like / needs for its largest member
+    uint64_t normal_need = 0;              // sequences the lane path's part uses (the segmented part's range starts behind them)
     if (!planned) {
         if (!horder) {
             own.resize(n);
@@ -653,15 +653,19 @@ static int run_device(zsb_ctx *ctx, zsb_dev &dv, size_t n, const zsb_member *dm,
         if (ctx->path != 2) {
             off_own.resize(n);
             if (!segm.empty()) {               // the segmented part shares the arena: as much as it can use, within the budget
-                for (uint32_t i : segm) seg_want += ((hm[i].in_len + ctx->seg_bytes - 1) / ctx->seg_bytes) * (uint64_t)seg_q_of(ctx);
-                seg_want = std::min<uint64_t>(seg_want, arena_bytes(ctx, dv) / sizeof(lane::seq_t));
+                for (uint32_t i : segm) {
+                    const uint64_t one = ((hm[i].in_len + ctx->seg_bytes - 1) / ctx->seg_bytes) * (uint64_t)seg_q_of(ctx);
+                    seg_want += one;
+                    seg_least = std::max(seg_least, one);
+                }
+                seg_want = std::max(seg_least, std::min<uint64_t>(seg_want, arena_bytes(ctx, dv) / sizeof(lane::seq_t) / 2));
             }
             uint64_t need = plan_parts(hm, horder, ns, nbig, (sc ? sc->seq_bytes : arena_bytes(ctx, dv)) / sizeof(lane::seq_t),
                                        off_own.data(), cuts_big_own, cuts_own, big_seqs);
             if (!sc && cuts_own.size() > 2 && !ctx->seq_arena_bytes)      // sliced: is more memory free by now?
                 need = plan_parts(hm, horder, ns, nbig, arena_bytes(ctx, dv, true) / sizeof(lane::seq_t), off_own.data(),
                                   cuts_big_own, cuts_own, big_seqs);
-            need = std::max(need, seg_want);
+            need += seg_want;
             if (!sc) {
                 // the arena: when the device cannot give it (another process took the memory since the last query),
                 // decode in more slices of half the size rather than fail
@@ -679,9 +683,9 @@ static int run_device(zsb_ctx *ctx, zsb_dev &dv, size_t n, const zsb_member *dm,
                     cudaGetLastError();
                     uint64_t largest = 0;
                     for (size_t s = nbig; s < ns; s++) largest = std::max(largest, seq_bound(hm[horder[s]]));
-                    if (seg_want > largest && need == seg_want) {      // the segmented part asked for it: it can do with less
-                        seg_want /= 2;
-                        need = std::max(plan_parts(hm, horder, ns, nbig, arena, off_own.data(), cuts_big_own, cuts_own, big_seqs), seg_want);
+                    if (seg_want > seg_least) {                        // the segmented part can do with less (more waves)
+                        seg_want = std::max(seg_least, seg_want / 2);
+                        need = plan_parts(hm, horder, ns, nbig, arena, off_own.data(), cuts_big_own, cuts_own, big_seqs) + seg_want;
                         continue;
                     }
                     if (arena <= largest || ctx->seq_arena_bytes) {
@@ -690,9 +694,10 @@ static int run_device(zsb_ctx *ctx, zsb_dev &dv, size_t n, const zsb_member *dm,
                     }
                     arena = std::max(largest, std::min(arena, need) / 2);
                     dv.arena_auto = (size_t)arena * sizeof(lane::seq_t);
-                    need = std::max(plan_parts(hm, horder, ns, nbig, arena, off_own.data(), cuts_big_own, cuts_own, big_seqs), seg_want);
+                    need = plan_parts(hm, horder, ns, nbig, arena, off_own.data(), cuts_big_own, cuts_own, big_seqs) + seg_want;
                 }
             }
+            normal_need = need - seg_want;
             if (cuts_own.size() > 2) nparts = 1;       // sliced by the arena: the slices run one after the other
             // (a pageable source is staged by the runtime before cudaMemcpyAsync returns, so off_own may go)
             if (ns) CK(ctx, cudaMemcpyAsync(dseqoff, off_own.data(), ns * sizeof(uint64_t), cudaMemcpyHostToDevice, st));
@@ -708,6 +713,18 @@ static int run_device(zsb_ctx *ctx, zsb_dev &dv, size_t n, const zsb_member *dm,
     if (ctx->path == 2) {
         if ((rc = run_group(ctx, dv, n, dm, dr, dorder, st, sc, ctx->lanes))) return rc;
     } else {
+        // the segmented members on a stream of their own, beside the lane path's part (their range of the arena is behind it)
+        if (!segm.empty()) {
+            if (!dv.seg_stream) {
+                CK(ctx, cudaStreamCreateWithFlags(&dv.seg_stream, cudaStreamNonBlocking));
+                CK(ctx, cudaEventCreateWithFlags(&dv.seg_fork, cudaEventDisableTiming));
+                CK(ctx, cudaEventCreateWithFlags(&dv.seg_join, cudaEventDisableTiming));
+            }
+            CK(ctx, cudaEventRecord(dv.seg_fork, st));
+            CK(ctx, cudaStreamWaitEvent(dv.seg_stream, dv.seg_fork, 0));
+            if ((rc = run_segmented(ctx, dv, dm, dr, hm, segm, dv.seg_stream, (lane::seq_t *)dv.d_seq + normal_need, seg_want))) return rc;
+            CK(ctx, cudaEventRecord(dv.seg_join, dv.seg_stream));
+        }
         LanePart P;
         P.aux = sc ? sc->aux : dv.aux;
         P.small_ctas = sc && sc->small_ctas;
@@ -775,7 +792,7 @@ static int run_device(zsb_ctx *ctx, zsb_dev &dv, size_t n, const zsb_member *dm,
             if ((rc = launch_lane(ctx, dv, dm, dr, P))) return rc;
         }
         if (fork) CK(ctx, cudaStreamWaitEvent(st, dv.ev_join, 0));
-        if (!segm.empty() && (rc = run_segmented(ctx, dv, dm, dr, hm, segm, st))) return rc;
+        if (!segm.empty()) CK(ctx, cudaStreamWaitEvent(st, dv.seg_join, 0));
     }
     if (!(flags & ZSB_RAW_ONLY)) {
         unsigned grid = (unsigned)std::min<size_t>(n, (size_t)dv.sm_count * 8);
@@ -855,6 +872,9 @@ static void free_device(zsb_dev &dv) {
     if (dv.copy_stream) cudaStreamDestroy(dv.copy_stream);
     if (dv.back_stream) cudaStreamDestroy(dv.back_stream);
     if (dv.group_stream) cudaStreamDestroy(dv.group_stream);
+    if (dv.seg_stream) cudaStreamDestroy(dv.seg_stream);
+    if (dv.seg_fork) cudaEventDestroy(dv.seg_fork);
+    if (dv.seg_join) cudaEventDestroy(dv.seg_join);
     if (dv.ev_fork) cudaEventDestroy(dv.ev_fork);
     if (dv.ev_join) cudaEventDestroy(dv.ev_join);
     for (size_t i = 1; i < dv.pipe_streams.size(); i++) cudaStreamDestroy(dv.pipe_streams[i]);   // [0] is dv.stream

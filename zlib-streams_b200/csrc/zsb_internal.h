@@ -36,6 +36,8 @@ struct zsb_dev {
     uint8_t *d_segbuf = nullptr;       // segmented members: plans, segment records, per-slot sequence offsets
     size_t d_segbuf_cap = 0;
     bool seg_configured = false;
+    cudaStream_t seg_stream = nullptr;  // the segmented members run beside the lane path's part
+    cudaEvent_t seg_fork = nullptr, seg_join = nullptr;
     int find_occ = 0;
     uint8_t *h_desc = nullptr;
     size_t h_desc_cap = 0;
