@@ -368,30 +368,3 @@ def test_one_context_over_all_gpus_of_the_box():
     finally:
         e.close()
 
-
-def test_overlapped_parts_of_a_device_batch(eng):
-    """A device-resident batch of several thousand members is dealt out to parts whose k_lane / k_lz pairs run side
-    by side on streams of their own (option "overlap_parts"; off by default, no gain was measured): every record and
-    byte as the oracle's with 8, 3 and 1 parts, valid and damaged members mixed."""
-    import torch
-    import batchlib
-    select(eng, 0)
-    distinct = [(d, wb, bytes(len(p) + 16)) for _, d, wb, p in cases.valid_streams()]
-    distinct += [(d, wb, bytes(c)) for _, d, wb, c in cases.damaged_streams(150)]
-    tiles = -(-9000 // len(distinct))
-    w = {"distinct": distinct, "tiles": tiles, "desc": "valid + damaged streams"}
-    dev = torch.device("cuda", 0)
-    batch = batchlib.DeviceBatch(w, dev).to_device()
-    assert batch.n >= 9000
-    stream = torch.cuda.Stream(dev)
-    assert eng.get_option("overlap_parts") == 1
-    try:
-        for parts in (8, 3, 1):
-            eng.set_option("overlap_parts", parts)
-            batch.clear_outputs()
-            batch.step(eng, stream)
-            stream.synchronize()
-            bad = batch.verify()
-            assert not bad, (parts, bad[:3])
-    finally:
-        eng.set_option("overlap_parts", 1)

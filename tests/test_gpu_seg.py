@@ -69,3 +69,29 @@ def test_segmented_members_match_the_oracle(seg_bytes, seg_min):
             assert not bad, (segment, bad[:3])
     finally:
         eng.close()
+
+
+def test_device_batch_of_every_test_stream():
+    """All valid and damaged test streams (tests/cases.py) as one device-resident batch of several thousand members,
+    with the default geometry, with tiny segments, and with segments off."""
+    import torch
+    import batchlib
+    import cases
+    distinct = [(d, wb, bytes(len(p) + 16)) for _, d, wb, p in cases.valid_streams()]
+    distinct += [(d, wb, bytes(c)) for _, d, wb, c in cases.damaged_streams(150)]
+    w = {"distinct": distinct, "tiles": -(-9000 // len(distinct)), "desc": "valid + damaged streams"}
+    dev = torch.device("cuda", 0)
+    batch = batchlib.DeviceBatch(w, dev).to_device()
+    stream = torch.cuda.Stream(dev)
+    eng = zsblib.Zsb(devices=[0])
+    try:
+        for opts in ((), (("seg_bytes", 4096), ("seg_min", 16384)), (("segment", 0),)):
+            for k, v in opts:
+                eng.set_option(k, v)
+            batch.clear_outputs()
+            batch.step(eng, stream)
+            stream.synchronize()
+            bad = batch.verify()
+            assert not bad, (opts, bad[:3])
+    finally:
+        eng.close()

@@ -19,7 +19,6 @@ using namespace zsb;
 
 static thread_local char g_create_err[256] = "";
 constexpr int MAX_CHUNKS_DEV = 64;
-constexpr size_t PART_MIN = 2048;       // fewest members of an overlapped part (run_device)
 constexpr int BASE_PIPE_STREAMS = 6;    // decode streams that, with the two copy streams, fit the default 8 hardware queues      // sets of work counters per device (option "chunks" <= 64)
 
 #define CK(ctx, call)                                                                              \
@@ -598,8 +597,6 @@ static int run_device(zsb_ctx *ctx, zsb_dev &dv, size_t n, const zsb_member *dm,
     size_t nbig = planned ? sc->nbig : 0;
     uint64_t big_seqs = planned ? sc->big_seqs : 0;
     uint32_t *counters = sc ? sc->counters : dv.counters;
-    size_t nparts = 1;
-    std::vector<size_t> part_start;
     size_t ns = n;                         // slots of the lane / group paths (n less the segmented members)
     std::vector<uint32_t> segm;            // members decoded in segments
     uint64_t seg_want = 0, seg_least = 0;  // sequences of arena the segmented part would like / needs for its largest member
@@ -626,30 +623,8 @@ static int run_device(zsb_ctx *ctx, zsb_dev &dv, size_t n, const zsb_member *dm,
             horder = own.data();
         }
         if (ctx->path == 0 && ctx->split_big) nbig = ctx->split_big == 2 ? ns : split_big(hm, horder, ns, dv.sm_count);
-        // Overlapped parts (option "overlap_parts" > 1, an experiment kept for measurement): the lane path's members
-        // are dealt out to K parts, each with its own k_lane + k_lz pair on a stream of its own.  Measured on C2 inside
-        // one call: 30.8 ms with 8 parts against 30.7 ms with one, and C5 475 ms against 362 ms — the 25.6 ms of
-        // scripts/overlap_experiment.py came from consecutive STEPS overlapping each other, not from the parts of a step.
-        if (!sc && ctx->path != 2 && ctx->overlap_parts > 1 && ns - nbig >= 2 * PART_MIN) {
-            nparts = (size_t)std::min<long>(std::min<long>(ctx->overlap_parts, pipe_stream_limit()), (long)((ns - nbig) / PART_MIN));
-            if (nparts < 2) nparts = 1;
-        }
-        if (nparts > 1) {                        // part p = slots p, p + K, ... of the (largest first) order, made contiguous
-            if (own.empty()) own.assign(horder, horder + ns);
-            const size_t m = ns - nbig;
-            std::vector<uint32_t> tmp(m);
-            size_t j = 0;
-            part_start.assign(nparts + 1, 0);
-            for (size_t q = 0; q < nparts; q++) {
-                part_start[q] = j;
-                for (size_t t = q; t < m; t += nparts) tmp[j++] = own[nbig + t];
-            }
-            part_start[nparts] = m;
-            memcpy(own.data() + nbig, tmp.data(), m * sizeof(uint32_t));
-            horder = own.data();
-        }
         if (ns) CK(ctx, cudaMemcpyAsync(dorder, horder, ns * sizeof(uint32_t), cudaMemcpyHostToDevice, st));
-        CK(ctx, cudaMemsetAsync(counters, 0, 8 * nparts * sizeof(uint32_t), st));
+        CK(ctx, cudaMemsetAsync(counters, 0, 8 * sizeof(uint32_t), st));
         if (ctx->path != 2) {
             off_own.resize(n);
             if (!segm.empty()) {               // the segmented part shares the arena: as much as it can use, within the budget
@@ -698,7 +673,6 @@ static int run_device(zsb_ctx *ctx, zsb_dev &dv, size_t n, const zsb_member *dm,
                 }
             }
             normal_need = need - seg_want;
-            if (cuts_own.size() > 2) nparts = 1;       // sliced by the arena: the slices run one after the other
             // (a pageable source is staged by the runtime before cudaMemcpyAsync returns, so off_own may go)
             if (ns) CK(ctx, cudaMemcpyAsync(dseqoff, off_own.data(), ns * sizeof(uint64_t), cudaMemcpyHostToDevice, st));
         }
@@ -742,51 +716,7 @@ static int run_device(zsb_ctx *ctx, zsb_dev &dv, size_t n, const zsb_member *dm,
             if ((rc = launch_lane(ctx, dv, dm, dr, P))) return rc;
             if (fork) CK(ctx, cudaEventRecord(dv.ev_join, dv.group_stream));
         }
-        if (nbig < ns && nparts > 1) {
-            while (dv.pipe_streams.size() < nparts + 1) {
-                cudaStream_t ns;
-                CK(ctx, cudaStreamCreateWithFlags(&ns, cudaStreamNonBlocking));
-                dv.pipe_streams.push_back(ns);
-            }
-            while (dv.part_ev.size() < nparts) {
-                cudaEvent_t e;
-                CK(ctx, cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
-                dv.part_ev.push_back(e);
-            }
-            cudaEvent_t *pe = nullptr;
-            if (ctx->profile) {                        // the parts overlap: one interval for all of them (reported as k_lane's)
-                if (dv.prof_used + 3 > dv.prof_ev.size()) {
-                    const size_t old = dv.prof_ev.size();
-                    dv.prof_ev.resize(old + 96);
-                    for (size_t i = old; i < dv.prof_ev.size(); i++) CK(ctx, cudaEventCreate(&dv.prof_ev[i]));
-                }
-                pe = &dv.prof_ev[dv.prof_used];
-                dv.prof_used += 3;
-                CK(ctx, cudaEventRecord(pe[0], st));
-            }
-            CK(ctx, cudaEventRecord(dv.part_ev[0], st));
-            std::vector<size_t> pc(2);
-            size_t used = 0;                           // streams other than the caller's
-            for (size_t q = 0; q < nparts; q++) {
-                cudaStream_t sq = st;
-                if (q) {
-                    while (dv.pipe_streams[used] == st) used++;
-                    sq = dv.pipe_streams[used++];
-                    CK(ctx, cudaStreamWaitEvent(sq, dv.part_ev[0], 0));
-                }
-                pc[0] = 0;
-                pc[1] = part_start[q + 1] - part_start[q];
-                P.dorder = dorder + nbig + part_start[q]; P.dseqoff = dseqoff + nbig + part_start[q]; P.cuts = &pc;
-                P.seq_base = seq0; P.counters = counters + 8 * q; P.big = false; P.timed = false; P.st = sq;
-                if ((rc = launch_lane(ctx, dv, dm, dr, P))) return rc;
-                if (q) CK(ctx, cudaEventRecord(dv.part_ev[q], sq));
-            }
-            for (size_t q = 1; q < nparts; q++) CK(ctx, cudaStreamWaitEvent(st, dv.part_ev[q], 0));
-            if (pe) {
-                CK(ctx, cudaEventRecord(pe[1], st));
-                CK(ctx, cudaEventRecord(pe[2], st));
-            }
-        } else if (nbig < ns) {
+        if (nbig < ns) {
             P.dorder = dorder + nbig; P.dseqoff = dseqoff + nbig; P.cuts = cuts; P.seq_base = seq0;
             P.counters = counters; P.big = false; P.timed = true; P.st = st;
             if ((rc = launch_lane(ctx, dv, dm, dr, P))) return rc;
@@ -881,8 +811,6 @@ static void free_device(zsb_dev &dv) {
     dv.pipe_streams.clear();
     for (cudaEvent_t e : dv.pipe_ev) cudaEventDestroy(e);
     dv.pipe_ev.clear();
-    for (cudaEvent_t e : dv.part_ev) cudaEventDestroy(e);
-    dv.part_ev.clear();
     cudaFree(dv.fixed);
     cudaFree(dv.fixed_lane);
     cudaFree(dv.d_seq);
@@ -989,11 +917,6 @@ extern "C" int zsb_set_option(zsb_ctx *ctx, const char *name, long value) {
         ctx->seg_min = (size_t)value;
         return 0;
     }
-    if (!strcmp(name, "overlap_parts")) {         // device-resident batches: parts decoded side by side (1 = off)
-        if (value < 1 || value > 16) return ZSB_E_ARG;
-        ctx->overlap_parts = (int)value;
-        return 0;
-    }
     if (!strcmp(name, "seq_arena_bytes")) {       // 0 = choose from the device's free memory
         if (value != 0 && value < 4096) return ZSB_E_ARG;
         ctx->seq_arena_bytes = (size_t)value;
@@ -1007,7 +930,6 @@ extern "C" long zsb_get_option(const zsb_ctx *ctx, const char *name) {
     if (!strcmp(name, "slab_bytes")) return (long)ctx->slab_bytes;
     if (!strcmp(name, "path")) return ctx->path;
     if (!strcmp(name, "chunks")) return ctx->chunks;
-    if (!strcmp(name, "overlap_parts")) return ctx->overlap_parts;
     if (!strcmp(name, "segment")) return ctx->segment;
     if (!strcmp(name, "seg_bytes")) return (long)ctx->seg_bytes;
     if (!strcmp(name, "seg_min")) return (long)ctx->seg_min;

@@ -15,7 +15,6 @@ struct zsb_dev {
     cudaEvent_t ev_fork = nullptr, ev_join = nullptr;
     std::vector<cudaStream_t> pipe_streams;   // decode streams of the chunks of a pipelined host batch
     std::vector<cudaEvent_t> pipe_ev;  // per chunk of a host batch: inputs arrived, decoded
-    std::vector<cudaEvent_t> part_ev;  // overlapped parts of a device-resident batch: [0] fork, [q] part q done
     uint16_t *fixed = nullptr;         // prebuilt fixed-code tables (one member slot, group path)
     uint8_t *fixed_lane = nullptr;     // the same in the lane path's slot format
     uint8_t *d_seq = nullptr;          // LZ sequence arena of the lane path
@@ -57,7 +56,6 @@ struct zsb_ctx {
     size_t seq_arena_bytes = 0;        // most sequence scratch one slice of a batch may use; 0 = from free memory (arena_bytes)
     size_t slab_bytes = 256u << 20;
     int chunks = 0;                    // host batches: pipeline depth (0 = choose from the batch)
-    int overlap_parts = 1;             // device-resident batches: parts whose k_lane / k_lz pairs run side by side (1 = off, the default: no gain measured)
     long launches = 0;
     bool force_small_ctas = false;
     int split_big = 1;                 // path 0: 1 = members far larger than the rest get a warp each (k_big,

@@ -160,6 +160,8 @@ ZSB_DEV uint32_t resolve_range(uint8_t *out, const uint8_t *in, const seq_t *seq
 }
 
 // all sequences of one member
+// (A variant with S = 2 / 4 consecutive sequences per lane and trip — one prefix sum and frontier vote for S times the
+// sequences — was measured and dropped: k_lz on C2 13.6 / 24.3 ms against 9.5 ms, 64 / 104 registers against 40.)
 template <int W>
 ZSB_DEV void resolve_member(uint8_t *out, const uint8_t *in, const seq_t *seq, uint32_t nseq, int lane) {
     resolve_range<W>(out, in, seq, nseq, lane, 0u);
