@@ -146,6 +146,7 @@ extern "C" int emul_decode_seg(const uint8_t *in, size_t in_len, uint8_t *out, s
     std::vector<uint64_t> seq_off(segs.size());
     std::vector<lane::seq_t> arena((size_t)segs.size() * seg_q + 64);
     alignas(16) static uint8_t fsm[seg::F_BYTES];
+    alignas(16) static uint8_t ringbuf[lz::RING_BYTES];
     uint32_t found = 0;
     for (uint32_t k = 0; k < segs.size(); k++) {
         lane::Seg &g = segs[k];
@@ -184,7 +185,9 @@ extern "C" int emul_decode_seg(const uint8_t *in, size_t in_len, uint8_t *out, s
         for (uint32_t k = 0; k < segs.size(); k++)
             if (segs[k].live) {
                 info[3]++;
-                if (segs[k].nseq) lz::resolve_range<1>(out, in, arena.data() + seq_off[k], segs[k].nseq, 0, segs[k].base);
+                if (!segs[k].nseq) continue;
+                if (wbits != -16) lz::resolve_range_ring<1>(out, in, arena.data() + seq_off[k], segs[k].nseq, 0, segs[k].base, ringbuf);
+                else lz::resolve_range<1>(out, in, arena.data() + seq_off[k], segs[k].nseq, 0, segs[k].base);
             }
         aux4[0] = a.kind; aux4[1] = a.trailer_pos; aux4[2] = a.need_trailer; aux4[3] = a.init_check;
         return res->ret;

@@ -63,6 +63,7 @@ def test_segmented_members_match_the_oracle(seg_bytes, seg_min):
         for segment in (1, 0, 1):
             eng.set_option("segment", segment)
             batch.clear_outputs()
+            torch.cuda.synchronize()                  # (the clears run on torch's current stream, the step on `stream`)
             batch.step(eng, stream)
             stream.synchronize()
             bad = batch.verify()
@@ -89,6 +90,7 @@ def test_device_batch_of_every_test_stream():
             for k, v in opts:
                 eng.set_option(k, v)
             batch.clear_outputs()
+            torch.cuda.synchronize()                  # (the clears run on torch's current stream, the step on `stream`)
             batch.step(eng, stream)
             stream.synchronize()
             bad = batch.verify()

@@ -449,6 +449,7 @@ static int seg_configure(zsb_ctx *ctx, zsb_dev &dv) {
     CK(ctx, cudaFuncSetAttribute(k_lane_seg, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)lane::SMEM));
     CK(ctx, cudaFuncSetAttribute(k_lane_seg, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared));
     CK(ctx, cudaFuncSetAttribute(k_seg_find, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)FIND_SMEM));
+    CK(ctx, cudaFuncSetAttribute(k_seg_lz_ring, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)lz::RING_BYTES));
     CK(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&dv.find_occ, k_seg_find, FIND_WARPS * 32, FIND_SMEM));
     if (dv.find_occ < 1) dv.find_occ = 1;
     dv.seg_configured = true;
@@ -496,7 +497,7 @@ static int run_segmented(zsb_ctx *ctx, zsb_dev &dv, const zsb_member *dm, zsb_re
     // device buffers: plan | fail order | counters | per-slot sequence offsets | segment records
     auto up = [](size_t v) { return (v + 255) & ~(size_t)255; };
     const size_t o_plan = 0, o_fail = o_plan + up(nm * sizeof(seg::MemberPlan)), o_cnt = o_fail + up(nm * 4),
-                 o_off = o_cnt + up((wave_m.size() * 4 + 4) * 4), o_seg = o_off + up(nsegs * 8), total = o_seg + up(nsegs * sizeof(lane::Seg));
+                 o_off = o_cnt + up((wave_m.size() * 8 + 8) * 4), o_seg = o_off + up(nsegs * 8), total = o_seg + up(nsegs * sizeof(lane::Seg));
     if ((rc = grow(ctx, dv.d_segbuf, dv.d_segbuf_cap, total))) return rc;
     uint8_t *base = dv.d_segbuf;
     seg::MemberPlan *dplan = (seg::MemberPlan *)(base + o_plan);
@@ -504,12 +505,12 @@ static int run_segmented(zsb_ctx *ctx, zsb_dev &dv, const zsb_member *dm, zsb_re
     uint64_t *doff = (uint64_t *)(base + o_off);
     lane::Seg *dsegs = (lane::Seg *)(base + o_seg);
     CK(ctx, cudaMemcpyAsync(dplan, plan.data(), nm * sizeof(seg::MemberPlan), cudaMemcpyHostToDevice, st));
-    CK(ctx, cudaMemsetAsync(dcnt, 0, (wave_m.size() * 4 + 4) * 4, st));
+    CK(ctx, cudaMemsetAsync(dcnt, 0, (wave_m.size() * 8 + 8) * 4, st));
     static const bool trace = getenv("ZSB_TRACE") != nullptr;
     if (trace) fprintf(stderr, "zsb trace segments: %zu members, %zu segments of %u bytes, %zu wave(s)\n", nm, nsegs, segb, wave_m.size() - 1);
     for (size_t w = 0; w + 1 < wave_m.size(); w++) {
         const size_t m0 = wave_m[w], mc = wave_m[w + 1] - m0, s0 = wave_slot[w], sn = wave_slot[w + 1] - s0;
-        uint32_t *cnt = dcnt + 4 * w;               // [0] find, [1] lanes, [2] resolve, [3] fallback
+        uint32_t *cnt = dcnt + 8 * w;               // [0] find, [1] lanes, [2] resolve (ring), [3] fallback, [4] resolve (Deflate64)
         k_seg_init<<<(unsigned)((mc + 127) / 128), 128, 0, st>>>(dplan + m0, (uint32_t)mc, dsegs + s0, doff + s0, seg_q);
         ctx->launches++;
         CK(ctx, cudaGetLastError());
@@ -545,13 +546,44 @@ static int run_segmented(zsb_ctx *ctx, zsb_dev &dv, const zsb_member *dm, zsb_re
         k_seg_chain<<<(unsigned)((mc + 127) / 128), 128, 0, st>>>(B, dplan + m0, (uint32_t)mc, dfail + m0);
         ctx->launches++;
         CK(ctx, cudaGetLastError());
-        if (mc <= (size_t)dv.sm_count * 4)          // few members: a CTA each (their length decides); many: a warp each (throughput)
-            k_seg_lz_cta<<<(unsigned)mc, SEGLZ_THREADS, 0, st>>>(B, dplan + m0, (uint32_t)mc, doff + s0, cnt + 2);
-        else
-            k_seg_lz<<<(unsigned)std::max<size_t>(1, std::min((mc + SEGLZ_WARPS - 1) / SEGLZ_WARPS, (size_t)dv.sm_count * 8)), SEGLZ_THREADS, 0, st>>>(
-                B, dplan + m0, (uint32_t)mc, doff + s0, cnt + 2);
+        // Resolve: the ring kernel (fast for one member, 3 per SM) takes the first ring_k members — the wave's largest
+        // — and the global-memory kernel the rest beside it on a second stream; ring_k balances the two under the
+        // measured paces (ring: 200 MB/s per member; global: 125 MB/s per member, ~700 GB/s for the whole GPU).
+        size_t ring_k = 0;
+        {
+            const double slots = 3.0 * dv.sm_count, r = 200e6, g = 125e6, gall = 700e9;
+            double all = 0, head = 0, best = 1e300;
+            for (size_t i = m0; i < m0 + mc; i++) all += (double)hm[segm[i]].out_cap;
+            for (size_t k = 0; k <= mc; k++) {
+                // k members to the ring kernel (the order is largest first)
+                const double first = k ? (double)hm[segm[m0]].out_cap / r : 0.0;
+                const double t_ring = std::max(first, head / (slots * r));
+                const double next = k < mc ? (double)hm[segm[m0 + k]].out_cap / g : 0.0;
+                const double t_glob = std::max(next, (all - head) / gall);
+                const double t = std::max(t_ring, t_glob);
+                if (t < best) { best = t; ring_k = k; }
+                if (k < mc) head += (double)hm[segm[m0 + k]].out_cap;
+                if (t_ring > best) break;
+            }
+        }
+        if (!dv.seg_stream2) {
+            CK(ctx, cudaStreamCreateWithFlags(&dv.seg_stream2, cudaStreamNonBlocking));
+            CK(ctx, cudaEventCreateWithFlags(&dv.seg_fork2, cudaEventDisableTiming));
+            CK(ctx, cudaEventCreateWithFlags(&dv.seg_join2, cudaEventDisableTiming));
+        }
+        CK(ctx, cudaEventRecord(dv.seg_fork2, st));
+        CK(ctx, cudaStreamWaitEvent(dv.seg_stream2, dv.seg_fork2, 0));
+        k_seg_lz<<<(unsigned)std::max<size_t>(1, std::min((mc + SEGLZ_WARPS - 1) / SEGLZ_WARPS, (size_t)dv.sm_count * 8)), SEGLZ_THREADS, 0, dv.seg_stream2>>>(
+            B, dplan + m0, (uint32_t)mc, doff + s0, cnt + 4, (uint32_t)ring_k);
         ctx->launches++;
         CK(ctx, cudaGetLastError());
+        CK(ctx, cudaEventRecord(dv.seg_join2, dv.seg_stream2));
+        if (ring_k) {
+            k_seg_lz_ring<<<(unsigned)std::min(ring_k, (size_t)dv.sm_count * 3), 32, lz::RING_BYTES, st>>>(B, dplan + m0, (uint32_t)ring_k, doff + s0, cnt + 2);
+            ctx->launches++;
+            CK(ctx, cudaGetLastError());
+        }
+        CK(ctx, cudaStreamWaitEvent(st, dv.seg_join2, 0));
         // the members whose chain did not hold: serially, a warp each (slots of the others are empty)
         lane::Batch F;
         F.members = dm;
@@ -633,7 +665,7 @@ static int run_device(zsb_ctx *ctx, zsb_dev &dv, size_t n, const zsb_member *dm,
                     seg_want += one;
                     seg_least = std::max(seg_least, one);
                 }
-                seg_want = std::max(seg_least, std::min<uint64_t>(seg_want, arena_bytes(ctx, dv) / sizeof(lane::seq_t) / 2));
+                seg_want = std::max(seg_least, std::min<uint64_t>(seg_want, arena_bytes(ctx, dv) / sizeof(lane::seq_t)));
             }
             uint64_t need = plan_parts(hm, horder, ns, nbig, (sc ? sc->seq_bytes : arena_bytes(ctx, dv)) / sizeof(lane::seq_t),
                                        off_own.data(), cuts_big_own, cuts_own, big_seqs);
@@ -803,6 +835,9 @@ static void free_device(zsb_dev &dv) {
     if (dv.back_stream) cudaStreamDestroy(dv.back_stream);
     if (dv.group_stream) cudaStreamDestroy(dv.group_stream);
     if (dv.seg_stream) cudaStreamDestroy(dv.seg_stream);
+    if (dv.seg_stream2) cudaStreamDestroy(dv.seg_stream2);
+    if (dv.seg_fork2) cudaEventDestroy(dv.seg_fork2);
+    if (dv.seg_join2) cudaEventDestroy(dv.seg_join2);
     if (dv.seg_fork) cudaEventDestroy(dv.seg_fork);
     if (dv.seg_join) cudaEventDestroy(dv.seg_join);
     if (dv.ev_fork) cudaEventDestroy(dv.ev_fork);

@@ -37,6 +37,8 @@ struct zsb_dev {
     bool seg_configured = false;
     cudaStream_t seg_stream = nullptr;  // the segmented members run beside the lane path's part
     cudaEvent_t seg_fork = nullptr, seg_join = nullptr;
+    cudaStream_t seg_stream2 = nullptr; // the global-memory resolver beside the ring resolver
+    cudaEvent_t seg_fork2 = nullptr, seg_join2 = nullptr;
     int find_occ = 0;
     uint8_t *h_desc = nullptr;
     size_t h_desc_cap = 0;

@@ -523,120 +523,13 @@ __global__ void k_seg_chain(lane::Batch B, const seg::MemberPlan *__restrict__ p
     fail_order[i] = ok ? 0xffffffffu : plan[i].idx;
 }
 
-// The verified segments' sequences -> bytes, one CTA per member.  A ROUND is SEGLZ_WARPS trips of 32 sequences, a warp
-// each: the warps scan their byte counts, exchange the totals (positions), store their literals and copy every match
-// whose source lies before the round at once; a match that reaches into the round waits until the warps before it
-// have published that those bytes are final (done[w] = the position up to which warp w's trip is final; the rule of
-// lz::resolve_range with the frontier shared through shared memory).  Rounds are separated by a barrier.
 constexpr int SEGLZ_WARPS = 8, SEGLZ_THREADS = SEGLZ_WARPS * 32;
-__device__ __forceinline__ uint32_t resolve_range_cta(uint8_t *out, const uint8_t *in, const lane::seq_t *seq, uint32_t nseq, uint32_t base,
-                                                      volatile uint32_t *done, uint32_t *tot) {
-    const int ln = threadIdx.x & 31, w = threadIdx.x >> 5;
-    for (uint32_t c = 0; c < nseq; c += 32 * SEGLZ_WARPS) {
-        const uint32_t i = c + (uint32_t)w * 32u + (uint32_t)ln;
-        lane::seq_t q;
-        q.lo = 0;
-        q.hi = 0;
-        if (i < nseq) q = seq[i];
-        const uint32_t nlit = (q.lo >> lane::Q_NLIT_SHIFT) & 3u;
-        const bool is_match = (q.lo & lane::Q_MATCH) != 0, is_raw = (q.lo & lane::Q_RAW) != 0;
-        uint32_t mlen = 0;
-        if (is_match) mlen = (q.hi >> 16) + ((q.lo & lane::Q_ABSLEN) ? 0u : 3u);
-        if (is_raw) mlen = q.lo & 0xffffu;
-        const uint32_t dist = (q.hi & 0xffffu) + 1u;
-        const uint32_t nbytes = nlit + mlen;
-        uint32_t incl = nbytes;
-#pragma unroll
-        for (int o = 1; o < 32; o <<= 1) {
-            const uint32_t v = __shfl_up_sync(0xffffffffu, incl, o);
-            if (ln >= o) incl += v;
-        }
-        if (ln == 31) tot[w] = incl;
-        if (ln == 0) done[w] = 0u;
-        __syncthreads();
-        uint32_t before = 0, all = 0;
-        {
-            const uint32_t t = ln < SEGLZ_WARPS ? tot[ln] : 0u;
-            uint32_t sc = t;
-#pragma unroll
-            for (int o = 1; o < SEGLZ_WARPS; o <<= 1) {
-                const uint32_t v = __shfl_up_sync(0xffffffffu, sc, o);
-                if (ln >= o) sc += v;
-            }
-            before = __shfl_sync(0xffffffffu, sc - t, w);
-            all = __shfl_sync(0xffffffffu, sc, SEGLZ_WARPS - 1);
-        }
-        const uint32_t mypos = base + before + incl - nbytes;
-        if (nlit > 0) out[mypos] = (uint8_t)q.lo;
-        if (nlit > 1) out[mypos + 1] = (uint8_t)(q.lo >> 8);
-        if (nlit > 2) out[mypos + 2] = (uint8_t)(q.lo >> 16);
-        const uint32_t mp = mypos + nlit;
-        const bool solo = is_match && mlen <= lz::SHORT && dist >= mlen;
-        bool pending = mlen != 0;
-        const uint64_t need = is_raw ? 0ull : (uint64_t)mp + (dist < mlen ? dist : mlen);
-        __syncwarp();
-        for (;;) {
-            const unsigned pm = __ballot_sync(0xffffffffu, pending);
-            const uint32_t own = pm ? __shfl_sync(0xffffffffu, mp, __ffs(pm) - 1) : 0xffffffffu;
-            if (ln == 0) {
-                __threadfence_block();
-                done[w] = own;
-            }
-            if (!pm) break;
-            uint32_t F = own;
-            const uint32_t dv = ln < w ? done[ln] : 0xffffffffu;
-            __threadfence_block();
-            const unsigned inc = __ballot_sync(0xffffffffu, dv != 0xffffffffu);
-            if (inc) {
-                const uint32_t f2 = __shfl_sync(0xffffffffu, dv, __ffs(inc) - 1);
-                F = f2 < F ? f2 : F;
-            }
-            const bool ready = pending && need <= (uint64_t)F + dist;
-            if (ready && solo) lz::lane_copy16(out + mp, out + mp - dist, mlen);
-            unsigned cm = __ballot_sync(0xffffffffu, ready && !solo);
-            while (cm) {
-                const int src = __ffs(cm) - 1;
-                cm &= cm - 1;
-                const uint32_t p = __shfl_sync(0xffffffffu, mp, src), n = __shfl_sync(0xffffffffu, mlen, src);
-                const uint32_t hi = __shfl_sync(0xffffffffu, q.hi, src);
-                const bool raw = __shfl_sync(0xffffffffu, (uint32_t)is_raw, src) != 0;
-                if (raw) lz::coop_copy<32>(out + p, in + hi, n, n, ln);
-                else lz::coop_copy<32>(out + p, out + p - ((hi & 0xffffu) + 1u), (hi & 0xffffu) + 1u, n, ln);
-            }
-            if (ready) pending = false;
-            __syncwarp();
-        }
-        __syncthreads();                                  // the round's bytes are final
-        base += all;
-    }
-    return base;
-}
-
-__global__ void __launch_bounds__(SEGLZ_THREADS) k_seg_lz_cta(lane::Batch B, const seg::MemberPlan *__restrict__ plan, uint32_t nm,
-                                                              const uint64_t *__restrict__ seq_off, uint32_t *counter) {
-    __shared__ uint32_t s_i;
-    __shared__ volatile uint32_t done[SEGLZ_WARPS];
-    __shared__ uint32_t tot[SEGLZ_WARPS];
-    for (;;) {
-        if (threadIdx.x == 0) s_i = atomicAdd(counter, 1u);
-        __syncthreads();
-        const uint32_t i = s_i;
-        __syncthreads();
-        if (i >= nm) break;
-        const seg::MemberPlan p = plan[i];
-        const zsb_member m = B.members[p.idx];
-        for (uint32_t k = 0; k < p.nseg; k++) {
-            const lane::Seg &g = B.segs[p.first + k];
-            if (!g.live || !g.nseq) continue;
-            resolve_range_cta((uint8_t *)m.out, (const uint8_t *)m.in, B.seq_base + seq_off[p.first + k], g.nseq, g.base, done, tot);
-        }
-    }
-}
-
-// the same, a warp per member: the better choice when there are members enough to fill the GPU with warps (the CTA
-// version resolves one member 1.3x faster, but does a third of the work per SM: C3 23 ms here, 64 ms there)
+// The verified segments' sequences -> bytes, a warp per member, segment after segment, on global memory (Deflate64
+// members; the others go through k_seg_lz_ring below).  (A CTA per member — 8 warps taking 32 sequences each per
+// round, a frontier in shared memory for matches that reach into the round — resolved one member 1.3x faster but did
+// a third of the work per SM, C3 64 ms against 23 ms: measured and dropped.)
 __global__ void __launch_bounds__(SEGLZ_THREADS) k_seg_lz(lane::Batch B, const seg::MemberPlan *__restrict__ plan, uint32_t nm,
-                                                          const uint64_t *__restrict__ seq_off, uint32_t *counter) {
+                                                          const uint64_t *__restrict__ seq_off, uint32_t *counter, uint32_t ring_k) {
     const int ln = threadIdx.x & 31;
     for (;;) {
         uint32_t i = 0;
@@ -645,10 +538,36 @@ __global__ void __launch_bounds__(SEGLZ_THREADS) k_seg_lz(lane::Batch B, const s
         if (i >= nm) break;
         const seg::MemberPlan p = plan[i];
         const zsb_member m = B.members[p.idx];
+        if (i < ring_k && m.window_bits != -16) continue;      // (k_seg_lz_ring resolves those)
         for (uint32_t k = 0; k < p.nseg; k++) {
             const lane::Seg &g = B.segs[p.first + k];
             if (!g.live || !g.nseq) continue;
             lz::resolve_range<32>((uint8_t *)m.out, (const uint8_t *)m.in, B.seq_base + seq_off[p.first + k], g.nseq, ln, g.base);
+            __syncwarp();
+        }
+    }
+}
+
+// the same with the member's recent output in a shared-memory ring (lz::resolve_range_ring): one warp per CTA, 64 KiB
+// each, three members per SM at a time: 1.6x faster for ONE member (200 against 125 MB/s), an eighth of the
+// throughput for many — so it takes the first `nm` (largest) members of a wave, k_seg_lz the rest beside it
+// (the host balances the two, run_segmented).  Not for Deflate64 members (k_seg_lz takes those too).
+__global__ void __launch_bounds__(32) k_seg_lz_ring(lane::Batch B, const seg::MemberPlan *__restrict__ plan, uint32_t nm,
+                                                    const uint64_t *__restrict__ seq_off, uint32_t *counter) {
+    extern __shared__ __align__(16) uint8_t ring[];
+    const int ln = threadIdx.x;
+    for (;;) {
+        uint32_t i = 0;
+        if (ln == 0) i = atomicAdd(counter, 1u);
+        i = __shfl_sync(0xffffffffu, i, 0);
+        if (i >= nm) break;
+        const seg::MemberPlan p = plan[i];
+        const zsb_member m = B.members[p.idx];
+        if (m.window_bits == -16) continue;                    // (k_seg_lz resolves those)
+        for (uint32_t k = 0; k < p.nseg; k++) {
+            const lane::Seg &g = B.segs[p.first + k];
+            if (!g.live || !g.nseq) continue;
+            lz::resolve_range_ring<32>((uint8_t *)m.out, (const uint8_t *)m.in, B.seq_base + seq_off[p.first + k], g.nseq, ln, g.base, ring);
             __syncwarp();
         }
     }
