@@ -297,7 +297,7 @@ def main():
     barrier()
     sampler.stop = True
     ms_per_step = max_over_ranks(ev0.elapsed_time(ev1)) / args.steps
-    lane_ms = lz_ms = check_ms = None
+    lane_ms = lz_ms = check_ms = seg_ms = None
     if not args.lanes:
         a, b = ctypes.c_double(0), ctypes.c_double(0)
         pairs = lib.zsb_profile_read(eng.ctx, 0, ctypes.byref(a), ctypes.byref(b))
@@ -307,6 +307,9 @@ def main():
         c = ctypes.c_double(0)
         if lib.zsb_profile_read_check(eng.ctx, 0, ctypes.byref(c)) > 0:
             check_ms = c.value / args.steps
+        c = ctypes.c_double(0)
+        if lib.zsb_profile_read_seg(eng.ctx, 0, ctypes.byref(c)) > 0:
+            seg_ms = c.value / args.steps
     bad = batch.verify()
     if bad:
         raise SystemExit("bench.py: GPU results differ from the oracle: %s" % bad[:3])
@@ -316,7 +319,8 @@ def main():
     peak, peak_src = peaks()
     # the roofline is the whole decode step's: k_lane writes no output byte, k_lz (and k_big / k_check) finish the job
     kernels = ("k_inflate<%d>" % eng.get_option("lanes_per_member")) if args.lanes else \
-        ("k_lane+k_lz" if batch.raw_only and config in ("C2", "C5") else "k_lane+k_lz+k_big" + ("" if batch.raw_only else "+k_check"))
+        ("k_lane+k_lz" if batch.raw_only and config in ("C2", "C5") else
+         "k_seg_*+k_lane_seg+k_lane+k_lz+k_big" + ("" if batch.raw_only else "+k_check"))
     achieved = (sum_in + sum_out) / (ms_per_step * 1e-3) / 1e9
     out = {"metric": METRIC, "value": value, "unit": "GB/s", "n_gpus": world, "steps": args.steps,
            "warmup": args.warmup, "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "weak",
@@ -324,7 +328,8 @@ def main():
            "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
                         "traffic": ncu_traffic(config), "peak_source": peak_src, "kernel": kernels,
                         "kernel_ms": ms_per_step,
-                        "kernel_ms_split": {"k_lane(+k_big, concurrent streams)": lane_ms, "k_lz": lz_ms, "k_check": check_ms},
+                        "kernel_ms_split": {"k_lane(+k_big, concurrent streams)": lane_ms, "k_lz": lz_ms, "k_check": check_ms,
+                                            "segmented members (k_seg_* + k_lane_seg, own stream beside k_lane)": seg_ms},
                         "k_check_gbs": (sum_out / (check_ms * 1e-3) / 1e9) if check_ms else None,
                         "algorithmic_bytes_per_launch": sum_in + sum_out},
            "clocks": sampler.summary(), "gpu_launches": int(launches_per_step * args.steps),

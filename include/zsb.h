@@ -114,7 +114,9 @@ ZSB_API int zsb_inflate_batch_device(zsb_ctx *ctx, int dev_index, size_t n, cons
  * sequence scratch the lane path may hold at once (larger batches are decoded in slices; 0, the default = half
  * of the device's free memory, at least 32 GiB); "split_big" 1 (default) members far larger than the rest of
  * their batch are decoded a warp each (zsb_plan_big), 0 never; "chunks" pipeline depth of host-buffer batches
- * (0 = choose). */
+ * (0 = choose); "segment" 1 (default): members of "seg_min" (131072) compressed bytes or more, unless they do not
+ * shrink, are decoded in parallel from block starts found near every multiple of "seg_bytes" (32768) of their input
+ * and verified to fit together (device-resident batches), 0 never. */
 ZSB_API int zsb_set_option(zsb_ctx *ctx, const char *name, long value);
 ZSB_API long zsb_get_option(const zsb_ctx *ctx, const char *name);
 
@@ -124,6 +126,8 @@ ZSB_API long zsb_get_option(const zsb_ctx *ctx, const char *name);
 ZSB_API long zsb_profile_read(zsb_ctx *ctx, int dev_index, double *lane_ms, double *lz_ms);
 /* ... and of the k_check launches (Adler-32 / CRC-32 + trailer checks). */
 ZSB_API long zsb_profile_read_check(zsb_ctx *ctx, int dev_index, double *check_ms);
+/* ... and of the segmented parts (large members decoded in segments, option "segment"): search, decode, chain, resolve. */
+ZSB_API long zsb_profile_read_seg(zsb_ctx *ctx, int dev_index, double *seg_ms);
 
 /* Number of kernels the last zsb_inflate_batch*() call launched (for accounting). */
 ZSB_API long zsb_last_launches(const zsb_ctx *ctx);

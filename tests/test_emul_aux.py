@@ -2,6 +2,7 @@
 the device code of the z_stream surface (zsb_stream.cuh, compiled for the host by tests/emul) against the
 UNMODIFIED reference, over chunked traces with Z_NO_FLUSH and Z_BLOCK."""
 import ctypes
+import os
 import random
 
 import pytest
@@ -61,9 +62,11 @@ def ref_trace(data, wb, chunks, ocap, flush):
 
 
 def test_mark_codes_used_sync_point_traces():
+    # (ZSB_TEST_SCALE=full: 300 damaged streams and every fifth valid one — 2 minutes; the default keeps the CPU tier short)
+    full = os.environ.get("ZSB_TEST_SCALE") == "full"
     rnd = random.Random(13)
-    pool = [(n, d, w) for n, d, w, p in cases.valid_streams()[1::5]] + [(n, d, -16) for n, d, m in cases.golden_fixtures()[:5]]
-    pool += [(n, d, w) for n, d, w, c in cases.damaged_streams(300)[:300]]
+    pool = [(n, d, w) for n, d, w, p in cases.valid_streams()[1::5 if full else 14]] + [(n, d, -16) for n, d, m in cases.golden_fixtures()[:5 if full else 2]]
+    pool += [(n, d, w) for n, d, w, c in cases.damaged_streams(300)[:300 if full else 90]]
     pool += [(n, d, w) for n, d, w, c, _ in cases.probe_vectors()]
     for name, data, wb in pool:
         for flush in (0, 5, 6):

@@ -52,9 +52,11 @@ def compare(name, data, wb, chunks, ocap, finish=True, flush=0):
 
 
 def test_stream_traces_random_chunkings():
+    # (ZSB_TEST_SCALE=full: every second stream, two chunkings each — 2.5 minutes; the default keeps the CPU tier short)
+    full = os.environ.get("ZSB_TEST_SCALE") == "full"
     rnd = random.Random(11)
-    for name, data, wb, plain in pool()[::2]:
-        for trial in range(2):
+    for name, data, wb, plain in pool()[::2 if full else 5]:
+        for trial in range(2 if full else 1):
             chunks = [rnd.choice([1, 2, 3, 7, 64, 1000, 32768]) for _ in range(5)]
             ocap = rnd.choice([1, 5, 300, 65536])
             compare(name, data, wb, chunks, ocap)

@@ -13,7 +13,7 @@ PKG = os.path.join(ROOT, "zlib-streams_b200")
 LIB = os.environ.get("ZSB_LIB") or os.path.join(PKG, "libzsb.so")      # ZSB_LIB: a variant build (experiments)
 EMUL_DIR = os.path.join(ROOT, "tests", "emul")
 
-API_SYMBOLS = ["zsb_deflate_batch", "zsb_deflate_bound", "zsb_deflate_batch_static", "zsb_deflate_static_limits", "zsb_profile_read_check", "zsb_create", "zsb_destroy", "zsb_create_error", "zsb_last_error", "zsb_num_devices",
+API_SYMBOLS = ["zsb_profile_read_seg", "zsb_deflate_batch", "zsb_deflate_bound", "zsb_deflate_batch_static", "zsb_deflate_static_limits", "zsb_profile_read_check", "zsb_create", "zsb_destroy", "zsb_create_error", "zsb_last_error", "zsb_num_devices",
                "zsb_inflate_batch", "zsb_inflate_batch_device", "zsb_set_option", "zsb_get_option",
                "zsb_last_launches", "zsb_plan_shards", "zsb_host_alloc", "zsb_host_free", "zsb_message",
                "zsb_profile_read", "zsb_zip_scan", "zsb_zip_members", "zsb_zip_inflate", "zsb_gunzip_files", "zsb_plan_big", "zsb_inflate_streams", "zsb_gzip_header"]
@@ -118,6 +118,8 @@ def load_product():
     lib.zsb_deflate_bound.argtypes = [ctypes.c_size_t, ctypes.c_int]
     lib.zsb_profile_read_check.restype = ctypes.c_long
     lib.zsb_profile_read_check.argtypes = [ctypes.c_void_p, ctypes.c_int, ctypes.POINTER(ctypes.c_double)]
+    lib.zsb_profile_read_seg.restype = ctypes.c_long
+    lib.zsb_profile_read_seg.argtypes = [ctypes.c_void_p, ctypes.c_int, ctypes.POINTER(ctypes.c_double)]
     lib.zsb_profile_read.restype = ctypes.c_long
     lib.zsb_profile_read.argtypes = [ctypes.c_void_p, ctypes.c_int, ctypes.POINTER(ctypes.c_double),
                                      ctypes.POINTER(ctypes.c_double)]

@@ -728,7 +728,19 @@ static int run_device(zsb_ctx *ctx, zsb_dev &dv, size_t n, const zsb_member *dm,
             }
             CK(ctx, cudaEventRecord(dv.seg_fork, st));
             CK(ctx, cudaStreamWaitEvent(dv.seg_stream, dv.seg_fork, 0));
+            cudaEvent_t *se = nullptr;
+            if (ctx->profile) {                       // the segmented part's own duration (zsb_profile_read_seg)
+                if (dv.seg_used + 2 > dv.seg_ev.size()) {
+                    const size_t old = dv.seg_ev.size();
+                    dv.seg_ev.resize(old + 32);
+                    for (size_t i = old; i < dv.seg_ev.size(); i++) CK(ctx, cudaEventCreate(&dv.seg_ev[i]));
+                }
+                se = &dv.seg_ev[dv.seg_used];
+                dv.seg_used += 2;
+                CK(ctx, cudaEventRecord(se[0], dv.seg_stream));
+            }
             if ((rc = run_segmented(ctx, dv, dm, dr, hm, segm, dv.seg_stream, (lane::seq_t *)dv.d_seq + normal_need, seg_want))) return rc;
+            if (se) CK(ctx, cudaEventRecord(se[1], dv.seg_stream));
             CK(ctx, cudaEventRecord(dv.seg_join, dv.seg_stream));
         }
         LanePart P;
@@ -862,6 +874,8 @@ static void free_device(zsb_dev &dv) {
     dv.prof_ev.clear();
     for (cudaEvent_t e : dv.chk_ev) cudaEventDestroy(e);
     dv.chk_ev.clear();
+    for (cudaEvent_t e : dv.seg_ev) cudaEventDestroy(e);
+    dv.seg_ev.clear();
 }
 
 extern "C" zsb_ctx *zsb_create(const int *devices, int ndev) {
@@ -1011,6 +1025,24 @@ extern "C" long zsb_profile_read_check(zsb_ctx *ctx, int dev_index, double *chec
     }
     dv.chk_used = 0;
     if (check_ms) *check_ms = a;
+    return k;
+}
+
+// The same for the segmented part of the batches (find + k_lane_seg + chain + resolve + fallback, on its own stream).
+extern "C" long zsb_profile_read_seg(zsb_ctx *ctx, int dev_index, double *seg_ms) {
+    if (!ctx || dev_index < 0 || dev_index >= (int)ctx->devs.size()) return ZSB_E_ARG;
+    zsb_dev &dv = ctx->devs[dev_index];
+    double a = 0;
+    long k = 0;
+    for (size_t i = 0; i + 2 <= dv.seg_used; i += 2) {
+        float t = 0;
+        CK(ctx, cudaEventSynchronize(dv.seg_ev[i + 1]));
+        CK(ctx, cudaEventElapsedTime(&t, dv.seg_ev[i], dv.seg_ev[i + 1]));
+        a += t;
+        k++;
+    }
+    dv.seg_used = 0;
+    if (seg_ms) *seg_ms = a;
     return k;
 }
 

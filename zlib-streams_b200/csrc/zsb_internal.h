@@ -49,6 +49,8 @@ struct zsb_dev {
     size_t prof_used = 0;
     std::vector<cudaEvent_t> chk_ev;   // 2 per k_check launch
     size_t chk_used = 0;
+    std::vector<cudaEvent_t> seg_ev;   // 2 per segmented part
+    size_t seg_used = 0;
 };
 
 struct zsb_ctx {
