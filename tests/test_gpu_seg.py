@@ -97,3 +97,28 @@ def test_device_batch_of_every_test_stream():
             assert not bad, (opts, bad[:3])
     finally:
         eng.close()
+
+
+def test_host_batch_with_large_members():
+    """Host buffers: the large members are staged whole and decoded in segments, the rest goes through the chunk
+    pipeline; every record and byte as the oracle's, in the caller's order."""
+    eng = zsblib.Zsb()
+    try:
+        small = [(gen.deflate(gen.word_soup(3000 + 100 * i, i), 6, -15), -15, 3000 + 100 * i + 8) for i in range(300)]
+        big = members()
+        items = []
+        for i in range(max(len(small), len(big))):            # interleaved
+            if i < len(big):
+                items.append(big[i])
+            if i < len(small):
+                items.append(small[i])
+        for opts in ((), (("seg_bytes", 8192), ("seg_min", 32768)), (("segment", 0),)):
+            for k, v in opts:
+                eng.set_option(k, v)
+            got = eng.inflate_batch([d for d, _, _ in items], [w for _, w, _ in items], [c for _, _, c in items])
+            for j, ((data, wb, cap), (r, out)) in enumerate(zip(items, got)):
+                a, ao = CHK.oneshot(data, cap, wb)
+                assert a.astuple() == r.astuple(), (opts, j, wb, cap, a, r)
+                assert ao == out, (opts, j, "output differs")
+    finally:
+        eng.close()

@@ -1459,7 +1459,7 @@ static int batch_device_ptrs(zsb_ctx *ctx, size_t n, const zsb_member *m, zsb_re
     ctx->launches = 0;
     // (results come back through the device's pinned descriptor buffer: a copy to pageable memory would block the
     // host until the device has finished, and the devices would run one after the other)
-    struct Pending { std::vector<zsb_member> mm; std::vector<uint32_t> ord; zsb_result *hr = nullptr; };
+    struct Pending { std::vector<zsb_member> mm; zsb_result *hr = nullptr; };
     std::vector<Pending> pend(nd);
     for (int s = 0; s < nd; s++) {
         const size_t k = part[s].size();
@@ -1473,7 +1473,6 @@ static int batch_device_ptrs(zsb_ctx *ctx, size_t n, const zsb_member *m, zsb_re
         zsb_result *dr = (zsb_result *)(dm + k);
         Pending &P = pend[s];
         P.mm.resize(k);
-        P.ord.resize(k);
         if (k * sizeof(zsb_result) > dv.h_desc_cap) {
             if (dv.h_desc) CK(ctx, cudaFreeHost(dv.h_desc));
             dv.h_desc = nullptr;
@@ -1486,14 +1485,13 @@ static int batch_device_ptrs(zsb_ctx *ctx, size_t n, const zsb_member *m, zsb_re
         bool raw_only = true;
         for (size_t j = 0; j < k; j++) {
             P.mm[j] = m[part[s][j]];
-            P.ord[j] = (uint32_t)j;
             raw_only &= P.mm[j].window_bits < 0 && P.mm[j].flags == 0;
             if (P.mm[j].in_len > 0xfffffff0ull || P.mm[j].out_cap > 0xfffffff0ull) P.mm[j].window_bits = 1000;   // -> Z_STREAM_ERROR
         }
-        sort_largest_first(P.ord.data(), k, [&](uint32_t a) { return (uint64_t)P.mm[a].in_len + P.mm[a].out_cap; });
         cudaStream_t st = dv.stream;
         CK(ctx, cudaMemcpyAsync(dm, P.mm.data(), k * sizeof(zsb_member), cudaMemcpyHostToDevice, st));
-        if ((rc = run_device(ctx, dv, k, dm, dr, P.mm.data(), P.ord.data(), raw_only ? ZSB_RAW_ONLY : ZSB_HAS_WRAPPED, st))) return rc;
+        // (no slot order of our own: run_device orders largest first and takes the large members out for the segmented path)
+        if ((rc = run_device(ctx, dv, k, dm, dr, P.mm.data(), nullptr, raw_only ? ZSB_RAW_ONLY : ZSB_HAS_WRAPPED, st))) return rc;
         CK(ctx, cudaMemcpyAsync(P.hr, dr, k * sizeof(zsb_result), cudaMemcpyDeviceToHost, st));
     }
     for (int s = 0; s < nd; s++) {
@@ -1503,6 +1501,88 @@ static int batch_device_ptrs(zsb_ctx *ctx, size_t n, const zsb_member *m, zsb_re
         CK(ctx, cudaStreamSynchronize(ctx->devs[s].stream));
         for (size_t j = 0; j < k; j++) r[part[s][j]] = pend[s].hr[j];
     }
+    return 0;
+}
+
+// Host-pointer batches with LARGE members: the chunk pipeline of batch_host() decodes a member with one lane or one
+// warp, so the members the segmented path would take (run_device: seg_min compressed bytes or more, shrinking) are
+// staged whole on the devices, decoded as a device-resident batch (in segments) and copied back; the rest goes
+// through the pipeline as before.  No overlap of copies and decode for the large part.
+static int batch_host_split(zsb_ctx *ctx, size_t n, const zsb_member *m, zsb_result *r) {
+    std::vector<uint32_t> L, S;
+    if (ctx->segment && ctx->path == 0 && ctx->split_big != 2)
+        for (size_t i = 0; i < n; i++) {
+            const zsb_member &x = m[i];
+            if (x.in && x.out && x.in_len >= ctx->seg_min && x.in_len <= 0xfffffff0ull && x.out_cap <= 0xfffffff0ull &&
+                !(x.flags & ZSB_M_STORED) && wbits_valid(x.window_bits) && (uint64_t)x.in_len * 16 < (uint64_t)x.out_cap * 15)
+                L.push_back((uint32_t)i);
+        }
+    if (L.empty()) return batch_host(ctx, n, m, r);
+    int rc = 0;
+    long launches = 0;
+    if (L.size() < n) {                            // the rest, through the pipeline
+        std::vector<char> isL(n, 0);
+        for (uint32_t i : L) isL[i] = 1;
+        for (size_t i = 0; i < n; i++)
+            if (!isL[i]) S.push_back((uint32_t)i);
+        std::vector<zsb_member> ms(S.size());
+        std::vector<zsb_result> rs(S.size());
+        for (size_t k = 0; k < S.size(); k++) ms[k] = m[S[k]];
+        if ((rc = batch_host(ctx, S.size(), ms.data(), rs.data()))) return rc;
+        for (size_t k = 0; k < S.size(); k++) r[S[k]] = rs[k];
+        launches = ctx->launches;
+    }
+    const int nd = (int)ctx->devs.size();
+    const size_t nl = L.size();
+    std::vector<int32_t> shard_of(nl, 0);
+    if (nd > 1) {
+        std::vector<uint64_t> cost(nl);
+        for (size_t k = 0; k < nl; k++) cost[k] = (uint64_t)m[L[k]].in_len + m[L[k]].out_cap;
+        zsb_plan_shards(nl, cost.data(), nd, shard_of.data(), nullptr);
+    }
+    std::vector<size_t> in_off(nl), out_off(nl), in_total(nd, 0), out_total(nd, 0);
+    for (size_t k = 0; k < nl; k++) {
+        const int s = shard_of[k];
+        in_off[k] = in_total[s];
+        out_off[k] = out_total[s];
+        in_total[s] += (m[L[k]].in_len + 19 + 255) & ~(size_t)255;
+        out_total[s] += (m[L[k]].out_cap + 255) & ~(size_t)255;
+    }
+    for (int s = 0; s < nd; s++) {
+        if (!in_total[s]) continue;
+        zsb_dev &dv = ctx->devs[s];
+        CK(ctx, cudaSetDevice(dv.device));
+        if ((rc = grow(ctx, dv.d_in, dv.d_in_cap, in_total[s] + 256)) || (rc = grow(ctx, dv.d_out, dv.d_out_cap, out_total[s] + 256))) return rc;
+    }
+    std::vector<zsb_member> md(nl);
+    std::vector<zsb_result> rd(nl);
+    for (size_t k = 0; k < nl; k++) {
+        zsb_dev &dv = ctx->devs[shard_of[k]];
+        CK(ctx, cudaSetDevice(dv.device));
+        md[k] = m[L[k]];
+        md[k].in = dv.d_in + in_off[k];
+        md[k].out = dv.d_out + out_off[k];
+        CK(ctx, cudaMemcpyAsync(dv.d_in + in_off[k], m[L[k]].in, m[L[k]].in_len, cudaMemcpyHostToDevice, dv.copy_stream));
+    }
+    for (int s = 0; s < nd; s++)
+        if (in_total[s]) {
+            CK(ctx, cudaSetDevice(ctx->devs[s].device));
+            CK(ctx, cudaStreamSynchronize(ctx->devs[s].copy_stream));
+        }
+    if ((rc = batch_device_ptrs(ctx, nl, md.data(), rd.data()))) return rc;
+    for (size_t k = 0; k < nl; k++) {
+        zsb_dev &dv = ctx->devs[shard_of[k]];
+        CK(ctx, cudaSetDevice(dv.device));
+        r[L[k]] = rd[k];
+        const size_t nb = std::min<size_t>((size_t)rd[k].total_out, m[L[k]].out_cap);
+        if (nb) CK(ctx, cudaMemcpyAsync(m[L[k]].out, dv.d_out + out_off[k], nb, cudaMemcpyDeviceToHost, dv.back_stream));
+    }
+    for (int s = 0; s < nd; s++)
+        if (in_total[s]) {
+            CK(ctx, cudaSetDevice(ctx->devs[s].device));
+            CK(ctx, cudaStreamSynchronize(ctx->devs[s].back_stream));
+        }
+    ctx->launches += launches;
     return 0;
 }
 
@@ -1523,7 +1603,7 @@ extern "C" int zsb_inflate_batch(zsb_ctx *ctx, size_t n, const zsb_member *m, zs
             cudaGetLastError();
         break;
     }
-    int rc = device_ptrs ? batch_device_ptrs(ctx, n, m, r) : batch_host(ctx, n, m, r);
+    int rc = device_ptrs ? batch_device_ptrs(ctx, n, m, r) : batch_host_split(ctx, n, m, r);
     cudaSetDevice(cur);
     return rc;
 }
