@@ -115,7 +115,7 @@ ZSB_API int zsb_inflate_batch_device(zsb_ctx *ctx, int dev_index, size_t n, cons
  * of the device's free memory, at least 32 GiB); "split_big" 1 (default) members far larger than the rest of
  * their batch are decoded a warp each (zsb_plan_big), 0 never; "chunks" pipeline depth of host-buffer batches
  * (0 = choose); "segment" 1 (default): members of "seg_min" (131072) compressed bytes or more, unless they do not
- * shrink, are decoded in parallel from block starts found near every multiple of "seg_bytes" (32768) of their input
+ * shrink, are decoded in parallel from block starts found near every multiple of "seg_bytes" (0 = chosen per batch, 8-64 KiB) of their input
  * and verified to fit together (device-resident batches), 0 never. */
 ZSB_API int zsb_set_option(zsb_ctx *ctx, const char *name, long value);
 ZSB_API long zsb_get_option(const zsb_ctx *ctx, const char *name);

@@ -102,3 +102,28 @@ def test_every_fixture_and_probe_vector_survives_tiny_segments():
         check(name, data, -16, meta["out_len"] + 16, 512)
     for name, data, wb, cap, _ in cases.probe_vectors():
         check(name, data, wb, cap, 256)
+
+
+def stream_with_a_false_start():
+    """A valid raw deflate stream whose stored block carries the bytes of ANOTHER deflate stream: the search finds that
+    stream's dynamic header inside the stored data — a false start, like the header-shaped bit patterns that turn up by
+    chance about once per 8 MB searched."""
+    p1 = b"".join(gen.word_soup(65536, 300 + i) for i in range(5))
+    inner = gen.deflate(gen.word_soup(100000, 77), 6, -15)
+    assert len(inner) < 65536
+    p3 = b"".join(gen.word_soup(65536, 400 + i) for i in range(6))
+    c = zlib.compressobj(6, zlib.DEFLATED, -15)
+    piece1 = c.compress(p1) + c.flush(zlib.Z_SYNC_FLUSH)                  # ends byte-aligned, BFINAL = 0 everywhere
+    n = len(inner)
+    piece2 = bytes([0, n & 255, n >> 8, (n & 255) ^ 255, (n >> 8) ^ 255]) + inner
+    piece3 = gen.deflate(p3, 6, -15)
+    return piece1 + piece2 + piece3, p1 + inner + p3
+
+
+def test_false_start_is_skipped_by_the_chain():
+    data, plain = stream_with_a_false_start()
+    assert CHK.oneshot(data, len(plain), -15)[1] == plain
+    for segb in (8192, 16384, 32768):
+        info = check("false_start", data, -15, len(plain), segb)
+        assert info[0] >= 3, info
+    assert check("false_start", data, -15, len(plain), 8192)[1] == 1       # small segments: the chain holds around it

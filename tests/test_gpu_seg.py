@@ -33,6 +33,9 @@ def members():
     out.append((gen.deflate(rb, 0, 15), 15, 300016))
     plain = soup[:200000] + soup[:65536] + bytes(90000) + soup[300000:350000] * 3
     out.append((d64enc.compress(plain, True, 3000, ("dynamic", "dynamic", "fixed", "stored")), -16, len(plain) + 16))
+    import test_emul_seg
+    fs, fs_plain = test_emul_seg.stream_with_a_false_start()                  # a false start inside a stored block
+    out.append((fs, -15, len(fs_plain)))
     base = list(out[:4]) + [out[6], out[9]]
     for comp, wb, cap in base:                                                # damage and truncation
         for k in range(6):

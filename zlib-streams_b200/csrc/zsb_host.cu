@@ -442,7 +442,20 @@ static int launch_lane(zsb_ctx *ctx, zsb_dev &dv, const zsb_member *dm, zsb_resu
 
 
 // ---- large members in segments (zsb_seg.cuh) ----------------------------------------------------------------------
-static inline uint32_t seg_q_of(const zsb_ctx *ctx) { return (uint32_t)(ctx->seg_bytes / 4 * 3); }   // sequences of arena per segment
+// Compressed bytes per segment.  Option "seg_bytes", or (0, the default) from the batch: a lane decodes its segment at
+// a fixed pace, so the segments should fill the GPU's lanes in whole rounds — one round of larger segments rather than
+// a round and a third of 32 KiB ones (C3) — and a batch of few members gets small segments (8 KiB: their decode is
+// what a single member waits for).
+static uint32_t seg_bytes_for(const zsb_ctx *ctx, const zsb_dev &dv, const zsb_member *hm, const std::vector<uint32_t> &segm) {
+    if (ctx->seg_bytes) return (uint32_t)ctx->seg_bytes;
+    double total = 0;
+    for (uint32_t i : segm) total += (double)hm[i].in_len;
+    const double lanes = 0.94 * dv.sm_count * lane::WARPS * 32;      // (every member rounds its last segment up)
+    const double rounds = std::max(1.0, std::floor(total / (lanes * 32768.0) + 0.35));
+    const double sb = std::min(65536.0, std::max(8192.0, total / (lanes * rounds)));
+    return ((uint32_t)sb + 255u) & ~255u;
+}
+static inline uint32_t seg_q_of(uint32_t segb) { return segb / 4 * 3; }   // sequences of arena per segment
 
 static int seg_configure(zsb_ctx *ctx, zsb_dev &dv) {
     if (dv.seg_configured) return 0;
@@ -459,10 +472,10 @@ static int seg_configure(zsb_ctx *ctx, zsb_dev &dv) {
 // The members `segm` (indices into dm / hm) through find -> k_lane_seg -> chain -> k_seg_lz -> fallback, in waves that
 // fit the sequence arena (dv.d_seq, already allocated by the caller).  Everything is queued on st.
 static int run_segmented(zsb_ctx *ctx, zsb_dev &dv, const zsb_member *dm, zsb_result *dr, const zsb_member *hm,
-                         const std::vector<uint32_t> &segm, cudaStream_t st, lane::seq_t *arena, uint64_t arena_seqs) {
+                         const std::vector<uint32_t> &segm, cudaStream_t st, lane::seq_t *arena, uint64_t arena_seqs, uint32_t segb) {
     int rc;
     if ((rc = lane_configure(ctx, dv)) || (rc = seg_configure(ctx, dv))) return rc;
-    const uint32_t segb = (uint32_t)ctx->seg_bytes, seg_q = seg_q_of(ctx);
+    const uint32_t seg_q = seg_q_of(segb);
     const size_t nm = segm.size();
     // waves: whole members, first-fit in order; slots and arena offsets restart in every wave
     std::vector<seg::MemberPlan> plan(nm);
@@ -632,6 +645,7 @@ static int run_device(zsb_ctx *ctx, zsb_dev &dv, size_t n, const zsb_member *dm,
     size_t ns = n;                         // slots of the lane / group paths (n less the segmented members)
     std::vector<uint32_t> segm;            // members decoded in segments
     uint64_t seg_want = 0, seg_least = 0;  // sequences of arena the segmented part would like / needs for its largest member
+    uint32_t segb = 32768;                 // compressed bytes per segment (seg_bytes_for)
     uint64_t normal_need = 0;              // sequences the lane path's part uses (the segmented part's range starts behind them)
     if (!planned) {
         if (!horder) {
@@ -660,8 +674,9 @@ static int run_device(zsb_ctx *ctx, zsb_dev &dv, size_t n, const zsb_member *dm,
         if (ctx->path != 2) {
             off_own.resize(n);
             if (!segm.empty()) {               // the segmented part shares the arena: as much as it can use, within the budget
+                segb = seg_bytes_for(ctx, dv, hm, segm);
                 for (uint32_t i : segm) {
-                    const uint64_t one = ((hm[i].in_len + ctx->seg_bytes - 1) / ctx->seg_bytes) * (uint64_t)seg_q_of(ctx);
+                    const uint64_t one = ((hm[i].in_len + segb - 1) / segb) * (uint64_t)seg_q_of(segb);
                     seg_want += one;
                     seg_least = std::max(seg_least, one);
                 }
@@ -739,7 +754,7 @@ static int run_device(zsb_ctx *ctx, zsb_dev &dv, size_t n, const zsb_member *dm,
                 dv.seg_used += 2;
                 CK(ctx, cudaEventRecord(se[0], dv.seg_stream));
             }
-            if ((rc = run_segmented(ctx, dv, dm, dr, hm, segm, dv.seg_stream, (lane::seq_t *)dv.d_seq + normal_need, seg_want))) return rc;
+            if ((rc = run_segmented(ctx, dv, dm, dr, hm, segm, dv.seg_stream, (lane::seq_t *)dv.d_seq + normal_need, seg_want, segb))) return rc;
             if (se) CK(ctx, cudaEventRecord(se[1], dv.seg_stream));
             CK(ctx, cudaEventRecord(dv.seg_join, dv.seg_stream));
         }
@@ -957,7 +972,7 @@ extern "C" int zsb_set_option(zsb_ctx *ctx, const char *name, long value) {
         return 0;
     }
     if (!strcmp(name, "seg_bytes")) {             // compressed bytes between the block starts looked for
-        if (value < 256 || value > (1 << 24)) return ZSB_E_ARG;
+        if (value != 0 && (value < 256 || value > (1 << 24))) return ZSB_E_ARG;      // 0 = choose from the batch
         ctx->seg_bytes = (size_t)value;
         return 0;
     }

@@ -65,7 +65,7 @@ struct zsb_ctx {
     int split_big = 1;                 // path 0: 1 = members far larger than the rest get a warp each (k_big,
                                        // split_big()), 0 = never, 2 = every member (tests)
     int segment = 1;                   // members of seg_min compressed bytes or more are decoded in segments (zsb_seg.cuh)
-    size_t seg_bytes = 32768, seg_min = 131072;
+    size_t seg_bytes = 0, seg_min = 131072;       // seg_bytes 0 = chosen per batch (seg_bytes_for)
     int profile = 0;                   // 1: record per-kernel events (zsb_profile_read)
     char err[256] = "";
 };

@@ -347,6 +347,7 @@ ZSB_DEV uint64_t find_sync_fixed(bool active, const uint8_t *in, uint32_t len, u
 // blocks the searches cannot see, or one huge block) would keep a lane busy far longer than the warp of the serial
 // path needs for the whole member, so it is not decoded in segments at all (segment 0 is marked and the chain fails).
 constexpr uint32_t MAX_SPAN = 6;
+constexpr uint64_t MAX_SPAN_BYTES = 196608;   // ... or this many compressed bytes, whichever is more (small segments)
 ZSB_DEV void plan_member(Seg *S, uint32_t segb, uint32_t len, bool d64) {
     const uint32_t nseg = S[0].nseg;
     uint64_t prev = 0;
@@ -355,7 +356,7 @@ ZSB_DEV void plan_member(Seg *S, uint32_t segb, uint32_t len, bool d64) {
         const uint64_t at = k < nseg ? S[k].start_bit : 8ull * len;
         if (at == SEG_NONE) continue;
         if (at < prev) bad = true;                                   // starts out of order: some start is false
-        else if (at - prev > 8ull * ((uint64_t)MAX_SPAN * segb + (prev ? 0u : first_start(d64)))) bad = true;   // (no start is looked for before first_start)
+        else if (at - prev > 8ull * (((uint64_t)MAX_SPAN * segb > MAX_SPAN_BYTES ? (uint64_t)MAX_SPAN * segb : MAX_SPAN_BYTES) + (prev ? 0u : first_start(d64)))) bad = true;   // (no start is looked for before first_start)
         prev = at;
     }
     if (bad) {
@@ -381,11 +382,14 @@ ZSB_DEV bool chain_member(const lane::Batch &B, uint32_t first) {
         g.live = 1;
         if (g.ev == lane::EV_SEGEND) {
             const uint64_t endbit = 8ull * g.next - g.nbits;
-            if (g.target == SEG_NONE || endbit != g.target) break;
-            base += g.pos;
+            if (g.target == SEG_NONE || endbit < g.target) break;
+            // It stopped at the first block boundary at or behind the next found start.  Behind it: that start was a false
+            // one (a header-like bit pattern inside a block — about one per 8 MB searched); the chain goes on with the
+            // segment that starts exactly where this one stopped, if there is one, and the false ones stay dead.
             uint32_t j = k + 1;
-            while (j < nseg && S[j].start_bit == SEG_NONE) j++;
-            if (j >= nseg) break;
+            while (j < nseg && (S[j].start_bit == SEG_NONE || S[j].start_bit < endbit)) j++;
+            if (j >= nseg || S[j].start_bit != endbit) break;
+            base += g.pos;
             k = j;
             continue;
         }
