@@ -615,6 +615,18 @@ static int run_segmented(zsb_ctx *ctx, zsb_dev &dv, const zsb_member *dm, zsb_re
                 LUT_BYTES + bwarps * BIG_PER_WARP, st>>>(F);
         ctx->launches++;
         CK(ctx, cudaGetLastError());
+        if (trace) {                                // (diagnostic only: waits for the wave) members that took the serial fallback
+            std::vector<uint32_t> hf(mc);
+            CK(ctx, cudaMemcpyAsync(hf.data(), dfail + m0, mc * 4, cudaMemcpyDeviceToHost, st));
+            CK(ctx, cudaStreamSynchronize(st));
+            size_t nf = 0, bytes = 0;
+            for (size_t i = 0; i < mc; i++)
+                if (hf[i] != 0xffffffffu) {
+                    nf++;
+                    bytes = std::max<size_t>(bytes, hm[hf[i]].out_cap);
+                }
+            fprintf(stderr, "zsb trace segments: wave %zu: %zu of %zu members fell back to the serial path (largest %zu bytes of output)\n", w, nf, mc, bytes);
+        }
     }
     return 0;
 }
@@ -659,8 +671,8 @@ static int run_device(zsb_ctx *ctx, zsb_dev &dv, size_t n, const zsb_member *dm,
                 for (size_t i = 0; i < n; i++) {
                     const zsb_member &x = hm[own[i]];
                     // (a member that does not shrink is stored blocks or as good as: the serial path copies those at memory speed)
-                    if (x.in_len >= ctx->seg_min && x.in_len <= 0xfffffff0ull && !(x.flags & ZSB_M_STORED) &&
-                        (uint64_t)x.in_len * 16 < (uint64_t)x.out_cap * 15)
+                    if (x.in && x.out && x.in_len >= ctx->seg_min && x.in_len <= 0xfffffff0ull && x.out_cap <= 0xfffffff0ull &&
+                        !(x.flags & ZSB_M_STORED) && wbits_valid(x.window_bits) && (uint64_t)x.in_len * 16 < (uint64_t)x.out_cap * 15)
                         segm.push_back(own[i]);
                     else own[keep++] = own[i];
                 }
