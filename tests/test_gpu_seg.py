@@ -49,14 +49,16 @@ def members():
     return out
 
 
-@pytest.mark.parametrize("seg_bytes,seg_min", [(8192, 32768), (32768, 131072), (2048, 16384)])
-def test_segmented_members_match_the_oracle(seg_bytes, seg_min):
+@pytest.mark.parametrize("seg_bytes,seg_min,arena", [(8192, 32768, 0), (32768, 131072, 0), (2048, 16384, 0), (0, 65536, 0), (8192, 32768, 6 << 20)])
+def test_segmented_members_match_the_oracle(seg_bytes, seg_min, arena):
     import torch
     import batchlib
     eng = zsblib.Zsb(devices=[0])
     try:
         eng.set_option("seg_bytes", seg_bytes)
         eng.set_option("seg_min", seg_min)
+        if arena:                                     # a small sequence arena: the segmented members go in several waves
+            eng.set_option("seq_arena_bytes", arena)
         small = [(gen.deflate(gen.word_soup(3000 + 100 * i, i), 6, -15), -15, 3000 + 100 * i + 8) for i in range(40)]
         distinct = [(c, wb, bytes(cap)) for c, wb, cap in members() + small]
         w = {"distinct": distinct, "tiles": 3, "desc": "large members in segments"}
