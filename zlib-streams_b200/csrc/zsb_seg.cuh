@@ -45,7 +45,7 @@ ZSB_DEV uint32_t first_start(bool d64) { return d64 ? 81920u : 40960u; }
 // ---- the finder's per-warp shared memory (bytes) ----
 constexpr int F_STAGE_WORDS = 256;                    // input words staged per chunk (+ F_STAGE_PAD read-ahead)
 constexpr int F_STAGE_PAD = 4;
-constexpr int F_VSLOTS = 4;                           // headers validated side by side
+constexpr int F_VSLOTS = 8;                           // headers validated side by side
 constexpr int F_STAGE = 0;                            // u32[260]
 constexpr int F_Q1_CAP = 1024 + 64;                   // u16: positions (within the chunk) that passed the 13-bit test
 constexpr int F_Q1 = (F_STAGE_WORDS + F_STAGE_PAD) * 4;
@@ -442,7 +442,7 @@ __global__ void k_seg_init(const seg::MemberPlan *__restrict__ plan, uint32_t nm
     }
 }
 
-constexpr int FIND_WARPS = 16;
+constexpr int FIND_WARPS = 12;
 constexpr size_t FIND_SMEM = LUT_BYTES + seg::KTAB_ENTRIES * 2 + FIND_WARPS * (size_t)seg::F_BYTES;
 __global__ void __launch_bounds__(FIND_WARPS * 32) k_seg_find(const zsb_member *__restrict__ members, lane::Seg *segs, uint32_t nsegs,
                                                               uint32_t segb, uint32_t *counter) {
