@@ -62,11 +62,11 @@ def test_c4_wrapped_mixed_sizes_with_checksums():
 def test_c4_large_members_get_their_own_path():
     w = workloads.c4(distinct=512, tiles=2)
     r = _run(w, split=True)
-    assert r["gpu_launches_per_step"] >= 11  # the segment kernels (zsb_seg.cuh) and k_big beside k_lane + k_lz, then k_check
+    assert r["gpu_launches_per_step"] >= 12  # the segment kernels (zsb_seg.cuh) and k_big beside k_lane + k_lz, then k_check_parts + k_check
     r = _run(w, split=True, options=(("segment", 0),))
-    assert r["gpu_launches_per_step"] == 4   # k_big beside k_lane + k_lz, then k_check
+    assert r["gpu_launches_per_step"] == 5   # k_big beside k_lane + k_lz, then k_check_parts + k_check
     r = _run(w, split=False, options=(("segment", 0),))
-    assert r["gpu_launches_per_step"] == 3
+    assert r["gpu_launches_per_step"] == 4
     r = _run(w, split=False)
     assert r["gpu_launches_per_step"] >= 10
 

@@ -808,7 +808,36 @@ static int run_device(zsb_ctx *ctx, zsb_dev &dv, size_t n, const zsb_member *dm,
             dv.chk_used += 2;
             CK(ctx, cudaEventRecord(ce[0], st));
         }
-        k_check<<<grid, CHK_THREADS, 0, st>>>(dm, dr, sc ? sc->aux : dv.aux, (uint32_t)n, (sc ? sc->counters : dv.counters) + 1);
+        // wrapped members of 2 MiB of output or more are checked in parts of 1 MiB, a CTA each, and k_check combines them
+        const uint32_t *d_first = nullptr;
+        const ChkPart *d_parts = nullptr;
+        if (!sc) {
+            std::vector<ChkPart> hp;
+            std::vector<uint32_t> first;
+            for (size_t i = 0; i < n; i++) {
+                const zsb_member &x = hm[i];
+                if (x.window_bits > 0 && x.out_cap >= 2ull * CHK_PART && x.out_cap <= 0xfffffff0ull && !(x.flags & ZSB_M_STORED)) {
+                    if (first.empty()) first.assign(n, 0xffffffffu);
+                    first[i] = (uint32_t)hp.size();
+                    const uint32_t np = (uint32_t)((x.out_cap + CHK_PART - 1) / CHK_PART);
+                    for (uint32_t k = 0; k < np; k++) hp.push_back(ChkPart{(uint32_t)i, k, 0u, 0u});
+                }
+            }
+            if (!hp.empty()) {
+                const size_t bytes = n * sizeof(uint32_t) + 256 + hp.size() * sizeof(ChkPart);
+                if ((rc = grow(ctx, dv.d_chkparts, dv.d_chkparts_cap, bytes))) return rc;
+                uint32_t *df = (uint32_t *)dv.d_chkparts;
+                ChkPart *dp = (ChkPart *)(dv.d_chkparts + ((n * sizeof(uint32_t) + 255) & ~(size_t)255));
+                CK(ctx, cudaMemcpyAsync(df, first.data(), n * sizeof(uint32_t), cudaMemcpyHostToDevice, st));
+                CK(ctx, cudaMemcpyAsync(dp, hp.data(), hp.size() * sizeof(ChkPart), cudaMemcpyHostToDevice, st));
+                k_check_parts<<<(unsigned)std::min<size_t>(hp.size(), (size_t)dv.sm_count * 8), CHK_THREADS, 0, st>>>(dm, dr, dv.aux, dp, (uint32_t)hp.size());
+                ctx->launches++;
+                CK(ctx, cudaGetLastError());
+                d_first = df;
+                d_parts = dp;
+            }
+        }
+        k_check<<<grid, CHK_THREADS, 0, st>>>(dm, dr, sc ? sc->aux : dv.aux, (uint32_t)n, (sc ? sc->counters : dv.counters) + 1, d_first, d_parts);
         ctx->launches++;
         CK(ctx, cudaGetLastError());
         if (ce) CK(ctx, cudaEventRecord(ce[1], st));
@@ -895,6 +924,7 @@ static void free_device(zsb_dev &dv) {
     cudaFree(dv.d_out);
     cudaFree(dv.d_desc);
     cudaFree(dv.d_df);
+    cudaFree(dv.d_chkparts);
     cudaFree(dv.d_segbuf);
     if (dv.h_desc) cudaFreeHost(dv.h_desc);
     for (cudaEvent_t e : dv.prof_ev) cudaEventDestroy(e);

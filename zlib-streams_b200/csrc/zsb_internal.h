@@ -40,6 +40,8 @@ struct zsb_dev {
     cudaStream_t seg_stream2 = nullptr; // the global-memory resolver beside the ring resolver
     cudaEvent_t seg_fork2 = nullptr, seg_join2 = nullptr;
     int find_occ = 0;
+    uint8_t *d_chkparts = nullptr;     // large wrapped members: per-member first part + the parts' partial check values
+    size_t d_chkparts_cap = 0;
     uint8_t *h_desc = nullptr;
     size_t h_desc_cap = 0;
     bool configured[33] = {};

@@ -87,7 +87,23 @@ __device__ __forceinline__ uint32_t crc_span(uint32_t s, const uint8_t *p, uint3
     }
     const uint32_t *w = (const uint32_t *)p;
     uint32_t nw = n >> 2;
-    for (uint32_t i = 0; i < nw; i++) {
+    uint32_t i = 0;
+    // Every lane walks a span of its own, so a 32-bit load touches 32 cache lines for 128 bytes and the L1's
+    // line-request rate bounds the kernel (1.2 TB/s over the GPU); 128-bit loads bring four times the bytes per request.
+    while (i < nw && ((uintptr_t)(w + i) & 15)) {
+        s ^= w[i++];
+        s = tab[3][s & 0xff] ^ tab[2][(s >> 8) & 0xff] ^ tab[1][(s >> 16) & 0xff] ^ tab[0][s >> 24];
+    }
+    for (; i + 8 <= nw; i += 8) {
+        const uint4 a = *(const uint4 *)(w + i), b = *(const uint4 *)(w + i + 4);
+        const uint32_t v[8] = {a.x, a.y, a.z, a.w, b.x, b.y, b.z, b.w};
+#pragma unroll
+        for (int k = 0; k < 8; k++) {
+            s ^= v[k];
+            s = tab[3][s & 0xff] ^ tab[2][(s >> 8) & 0xff] ^ tab[1][(s >> 16) & 0xff] ^ tab[0][s >> 24];
+        }
+    }
+    for (; i < nw; i++) {
         s ^= w[i];
         s = tab[3][s & 0xff] ^ tab[2][(s >> 8) & 0xff] ^ tab[1][(s >> 16) & 0xff] ^ tab[0][s >> 24];
     }
@@ -120,12 +136,14 @@ __device__ __forceinline__ void chk_init(ChkShared &sh) {
     }
 }
 
-// Check value of `init` continued over out[0..E) by the whole CTA (kind 2 = CRC-32, else Adler-32);
-// valid on thread 0.  init is the running value: crc32(0)=0 / adler32(0)=1 for a fresh stream.
-__device__ __forceinline__ uint32_t cta_check(ChkShared &sh, uint32_t kind, const uint8_t *out, uint32_t E, uint32_t init) {
+// The part of a check value that depends on the data alone, over out[0..E) (E > 0) by the whole CTA; valid on
+// thread 0.  kind 2 (CRC-32): pa = the data's polynomial remainder (register started at zero).  Else (Adler-32):
+// pa = sum of the bytes mod 65521, pb = sum of i * b_i mod 65521 (i from 0).  Parts of a buffer combine:
+// remainder(A || B) = remainder(A) * x^(8|B|) + remainder(B); the sums add, the second one with offset * sum.
+__device__ __forceinline__ void cta_partial(ChkShared &sh, uint32_t kind, const uint8_t *out, uint32_t E, uint32_t &pa, uint32_t &pb) {
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    uint32_t check = init;
-    if (E == 0) return check;
+    pa = 0;
+    pb = 0;
     if (kind == 2) {
         uint32_t s = 0;
         const uint32_t ntiles = (E + CHK_TILE - 1) / CHK_TILE;
@@ -148,30 +166,33 @@ __device__ __forceinline__ uint32_t cta_check(ChkShared &sh, uint32_t kind, cons
         if (tid == 0) {
             uint32_t z = sh.red[0][0];
             for (int wv = 1; wv < CHK_THREADS / 32; wv++) z = gf2_mul(c_crc.span_pow[5], z) ^ sh.red[wv][0];
-            check = ~(gf2_mul(crc_xpow(8ull * E), ~init) ^ z);
+            pa = z;
         }
         __syncthreads();
     } else {
         const uint32_t P = 65521u;
         unsigned long long S = 0, W = 0;
-        uint32_t head = (uint32_t)((4 - ((uintptr_t)out & 3)) & 3);
+        uint32_t head = (uint32_t)((16 - ((uintptr_t)out & 15)) & 15);
         if (head > E) head = E;
-        const uint32_t nw = (E - head) >> 2;
-        const uint32_t *w32 = (const uint32_t *)(out + head);
-        uint32_t im = (head + 4u * tid) % P;             // byte index of this thread's word, mod P
-        const uint32_t step = (4u * CHK_THREADS) % P;
-        for (uint32_t w = tid; w < nw; w += CHK_THREADS) {
-            uint32_t v = w32[w];
-            uint32_t sb = __dp4a(v, 0x01010101u, 0u);
-            uint32_t q = __dp4a(v, 0x03020100u, 0u);
+        const uint32_t nv = (E - head) >> 4;                 // 16-byte vectors: four words per load
+        const uint4 *v4 = (const uint4 *)(out + head);
+        uint32_t im = (head + 16u * tid) % P;                // byte index of this thread's vector, mod P
+        const uint32_t step = (16u * CHK_THREADS) % P;
+        for (uint32_t w = tid; w < nv; w += CHK_THREADS) {
+            const uint4 v = v4[w];
+            const uint32_t s0 = __dp4a(v.x, 0x01010101u, 0u), s1 = __dp4a(v.y, 0x01010101u, 0u);
+            const uint32_t s2 = __dp4a(v.z, 0x01010101u, 0u), s3 = __dp4a(v.w, 0x01010101u, 0u);
+            const uint32_t q = __dp4a(v.x, 0x03020100u, 0u) + __dp4a(v.y, 0x03020100u, 0u) + __dp4a(v.z, 0x03020100u, 0u) +
+                               __dp4a(v.w, 0x03020100u, 0u);
+            const uint32_t sb = s0 + s1 + s2 + s3;
             S += sb;
-            W += (unsigned long long)im * sb + q;
+            W += (unsigned long long)im * sb + 4u * (s1 + 2u * s2 + 3u * s3) + q;
             im += step;
             if (im >= P) im -= P;
         }
         if (tid == 0) {
             for (uint32_t i = 0; i < head; i++) { S += out[i]; W += (unsigned long long)i * out[i]; }
-            for (uint32_t i = head + 4 * nw; i < E; i++) { S += out[i]; W += (unsigned long long)(i % P) * out[i]; }
+            for (uint32_t i = head + 16 * nv; i < E; i++) { S += out[i]; W += (unsigned long long)(i % P) * out[i]; }
         }
         S %= P; W %= P;
         for (int o = 16; o; o >>= 1) {
@@ -183,21 +204,74 @@ __device__ __forceinline__ uint32_t cta_check(ChkShared &sh, uint32_t kind, cons
         if (tid == 0) {
             unsigned long long s = 0, wsum = 0;
             for (int wv = 0; wv < CHK_THREADS / 32; wv++) { s += sh.red64[wv][0]; wsum += sh.red64[wv][1]; }
-            s %= P; wsum %= P;
-            // s1' = s1 + S;  s2' = s2 + E*s1 + E*S - W   (W = sum of i*b_i, i from 0)
-            const unsigned long long nm = E % P, s1 = init & 0xffffu, s2 = init >> 16;
-            const uint32_t r1 = (uint32_t)((s1 + s) % P);
-            const uint32_t r2 = (uint32_t)((s2 + nm * s1 + nm * s + (unsigned long long)P - wsum) % P);
-            check = (r2 << 16) | r1;
+            pa = (uint32_t)(s % P);
+            pb = (uint32_t)(wsum % P);
         }
         __syncthreads();
     }
-    return check;
+}
+// the check value `init` continued over E bytes whose partial values are (pa, pb)
+__device__ __forceinline__ uint32_t check_finish(uint32_t kind, uint32_t pa, uint32_t pb, uint32_t E, uint32_t init) {
+    if (kind == 2) return ~(gf2_mul(crc_xpow(8ull * E), ~init) ^ pa);
+    const uint32_t P = 65521u;
+    // s1' = s1 + S;  s2' = s2 + E*s1 + E*S - W   (W = sum of i*b_i, i from 0)
+    const unsigned long long nm = E % P, s1 = init & 0xffffu, s2 = init >> 16, s = pa, wsum = pb;
+    const uint32_t r1 = (uint32_t)((s1 + s) % P);
+    const uint32_t r2 = (uint32_t)((s2 + nm * s1 + nm * s + (unsigned long long)P - wsum) % P);
+    return (r2 << 16) | r1;
+}
+// (pa, pb) of A || B from those of A and of B (B is nb bytes long and starts at offset |A| = off)
+__device__ __forceinline__ void check_append(uint32_t kind, uint32_t &pa, uint32_t &pb, uint32_t qa, uint32_t qb, uint32_t off, uint32_t nb) {
+    if (kind == 2) {
+        pa = gf2_mul(crc_xpow(8ull * nb), pa) ^ qa;
+        return;
+    }
+    const uint32_t P = 65521u;
+    pa = (pa + qa) % P;
+    pb = (uint32_t)((pb + qb + (unsigned long long)(off % P) * qa) % P);
+}
+
+// Check value of `init` continued over out[0..E) by the whole CTA (kind 2 = CRC-32, else Adler-32);
+// valid on thread 0.  init is the running value: crc32(0)=0 / adler32(0)=1 for a fresh stream.
+__device__ __forceinline__ uint32_t cta_check(ChkShared &sh, uint32_t kind, const uint8_t *out, uint32_t E, uint32_t init) {
+    if (E == 0) return init;
+    uint32_t pa, pb;
+    cta_partial(sh, kind, out, E, pa, pb);
+    return threadIdx.x == 0 ? check_finish(kind, pa, pb, E, init) : init;
+}
+
+// Large wrapped members: their output is checked in PARTS of CHK_PART bytes by a CTA each (k_check_parts), and k_check
+// only puts the parts together — one CTA per member made the 16 MiB members of C4 decide k_check's length.
+constexpr uint32_t CHK_PART = 1u << 20;
+struct ChkPart {
+    uint32_t member, part;        // member index; the part covers [part * CHK_PART, ...) of its output
+    uint32_t pa, pb;              // OUT: cta_partial of the part (zero when the member's output ends before it)
+};
+__global__ void __launch_bounds__(CHK_THREADS)
+k_check_parts(const zsb_member *__restrict__ members, const zsb_result *__restrict__ results, const Aux *__restrict__ aux,
+              ChkPart *parts, uint32_t nparts) {
+    __shared__ ChkShared sh;
+    const int tid = threadIdx.x;
+    chk_init(sh);
+    for (uint32_t i = blockIdx.x; i < nparts; i += gridDim.x) {
+        const ChkPart p = parts[i];
+        const uint32_t E = (uint32_t)results[p.member].total_out, kind = aux[p.member].kind;
+        const uint64_t from = (uint64_t)p.part * CHK_PART;
+        uint32_t pa = 0, pb = 0;
+        if (kind != 0 && from < E) {                                     // (uniform over the CTA)
+            const uint32_t len = E - (uint32_t)from < CHK_PART ? E - (uint32_t)from : CHK_PART;
+            cta_partial(sh, kind, (const uint8_t *)members[p.member].out + from, len, pa, pb);
+        }
+        if (tid == 0) {
+            parts[i].pa = pa;
+            parts[i].pb = pb;
+        }
+    }
 }
 
 __global__ void __launch_bounds__(CHK_THREADS)
 k_check(const zsb_member *__restrict__ members, zsb_result *__restrict__ results, const Aux *__restrict__ aux,
-        uint32_t n, uint32_t *counter) {
+        uint32_t n, uint32_t *counter, const uint32_t *__restrict__ part_first = nullptr, const ChkPart *__restrict__ parts = nullptr) {
     __shared__ ChkShared sh;
     __shared__ uint32_t s_idx;
     const int tid = threadIdx.x;
@@ -254,7 +328,20 @@ k_check(const zsb_member *__restrict__ members, zsb_result *__restrict__ results
         }
         const uint8_t *out = (const uint8_t *)members[idx].out;
         const uint32_t E = (uint32_t)results[idx].total_out;
-        const uint32_t check = cta_check(sh, a.kind, out, E, a.init_check);
+        uint32_t check = a.init_check;
+        if (part_first && part_first[idx] != 0xffffffffu) {       // checked in parts (k_check_parts): put them together
+            if (tid == 0 && E) {
+                const ChkPart *pp = parts + part_first[idx];
+                uint32_t pa = 0, pb = 0;
+                for (uint32_t k = 0; (uint64_t)k * CHK_PART < E; k++) {
+                    const uint32_t off = k * CHK_PART, nb = E - off < CHK_PART ? E - off : CHK_PART;
+                    check_append(a.kind, pa, pb, pp[k].pa, pp[k].pb, off, nb);
+                }
+                check = check_finish(a.kind, pa, pb, E, a.init_check);
+            }
+        } else {
+            check = cta_check(sh, a.kind, out, E, a.init_check);
+        }
         if (tid == 0) {
             zsb_result r = results[idx];
             finish_member(r, a, (const uint8_t *)members[idx].in, (uint32_t)members[idx].in_len, check, E);
