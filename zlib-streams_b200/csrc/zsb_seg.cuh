@@ -5,26 +5,36 @@
 // so this path FINDS block starts inside the member, decodes the stretches between them as if they were members
 // of their own, and then proves that the stretches fit together:
 //
-//   k_seg_find   one warp per multiple of `segb` compressed bytes: the first bit position at or behind it where a
-//                block of the dynamic type starts.  32 positions per trip go through a register-only filter (BFINAL
-//                = 0, BTYPE = 2, HLIT / HDIST in range, the code-length code exactly complete: about 1 position in
-//                600 passes); survivors are queued and validated 32 at a time, a lane each, by the decoder's own
-//                header reader (lane_dynamic_header) and then by the warp with its own table builder (build_tables)
-//                — so a start is accepted exactly when the decoder would accept that header.  Fixed and stored
-//                blocks cannot be told from their three header bits; a stretch simply runs on through them.
+//   k_seg_sync   a lane per multiple of `segb` compressed bytes: inside runs of FIXED-code blocks a parse from any bit
+//                position joins the true one (or dies on an invalid code), so the first end-of-block code behind 1 024
+//                cleanly parsed codes is a block boundary (find_sync_fixed).
+//   k_seg_find   a warp per start still missing: the first bit position at or behind the multiple where a block of
+//                the DYNAMIC type starts.  The input is staged in shared memory; a word of 32 positions per lane goes
+//                through a 13-bit test done with 64-bit logic (BFINAL = 0, BTYPE = 2, HLIT / HDIST in range), the
+//                positions that pass are queued and checked 32 at a time for an exactly complete code-length code (a
+//                table of partial Kraft sums), and what is left (about 1 position in 600) is validated eight at a time by
+//                the decoder's own header reader (lane_dynamic_header_t<EARLY>) and then by the warp with its own table
+//                builder (build_tables) — so a start is accepted exactly when the decoder would accept that header.
+//                Stored blocks cannot be told from their three header bits; a stretch simply runs on through them.
+//   k_seg_plan   a member with a stretch of more than 6 segments (192 KiB) without a start is not worth a lane: serial.
 //   k_lane_seg   k_lane with segments as its slots (zsb_lane.cuh: start_member / lane_block / finish): segment 0
 //                starts like the member itself (wrapper, capacity, distance checks exact); segment k > 0 starts at
 //                its found bit position at a block header, with 64 KiB of assumed history and no capacity of its
 //                own.  A segment ends at the first block boundary at or behind the next found start (EV_SEGEND), at
 //                the final block, at an error, or when its range of the sequence arena is full (EV_SEGFULL).
-//   k_seg_chain  one thread per member walks its segments in order: each must have ended exactly where the next
-//                one began and (k > 0) at least a window of output (32 / 64 KiB) must precede it, which makes the assumed history
-//                true; output positions are the running sum.  The first segment that ended otherwise — final block,
-//                error, input exhausted — is where the serial decoder would have stopped in the same state, so its
-//                record, with the position added, gives the member's result through the same write_result().
-//                Anything that does not fit (a false start, a full arena range, output beyond out_cap) marks the
-//                member for the fallback: k_big decodes it serially afterwards, so results never depend on a guess.
-//   k_seg_lz     the verified segments' sequences become bytes (lz::resolve_range, segment after segment).
+//   k_seg_chain  one thread per member walks its segments in order: each must have ended where the next one began —
+//                or, when it ran on past a FALSE start (a header-shaped bit pattern inside a block), where some later
+//                one began; the false ones stay dead — and (k > 0) at least a window of output (32 / 64 KiB) must
+//                precede it, which makes the assumed history true; output positions are the running sum.  The first
+//                segment that ended otherwise — final block, error, input exhausted — is where the serial decoder would
+//                have stopped in the same state, so its record, with the position added, gives the member's result
+//                through the same write_result().  Anything that does not fit (a gap, a full arena range, output beyond
+//                out_cap) marks the member for the fallback: k_big decodes it serially afterwards, so results never
+//                depend on a guess.
+//   k_seg_lz_ring / k_seg_lz   the verified segments' sequences become bytes, a warp per member, segment after segment:
+//                with the member's last 64 KiB of output mirrored in a shared-memory ring (1.6x faster for one member,
+//                three members per SM: the wave's largest members), or on global memory (lz::resolve_range: the rest,
+//                and Deflate64 members), side by side.
 #pragma once
 #include "zsb_lz.cuh"
 
@@ -35,7 +45,6 @@ using lane::Seg;
 using lane::SEG_NONE;
 using lane::Wp;
 
-constexpr uint32_t SEGB_DEFAULT = 32768;      // compressed bytes between wanted starts
 // Output that must precede a segment k > 0: the window, so that no distance it accepted could have been "too far
 // back" for the serial decoder.  Starts are only looked for behind FIRST_START compressed bytes, where that much
 // output exists unless the stream expands its data (then the chain fails and the member is decoded serially).
