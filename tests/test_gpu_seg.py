@@ -91,7 +91,8 @@ def test_device_batch_of_every_test_stream():
     stream = torch.cuda.Stream(dev)
     eng = zsblib.Zsb(devices=[0])
     try:
-        for opts in ((), (("seg_bytes", 4096), ("seg_min", 16384)), (("segment", 0),)):
+        # (the last: a small sequence arena — the lane path decodes in slices)
+        for opts in ((), (("seg_bytes", 4096), ("seg_min", 16384)), (("segment", 0),), (("seq_arena_bytes", 3 << 20),)):
             for k, v in opts:
                 eng.set_option(k, v)
             batch.clear_outputs()
