@@ -463,6 +463,7 @@ static int seg_configure(zsb_ctx *ctx, zsb_dev &dv) {
     CK(ctx, cudaFuncSetAttribute(k_lane_seg, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared));
     CK(ctx, cudaFuncSetAttribute(k_seg_find, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)FIND_SMEM));
     CK(ctx, cudaFuncSetAttribute(k_seg_lz_ring, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)lz::RING_BYTES));
+    CK(ctx, cudaFuncSetAttribute(k_seg_lz_ring_cta, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)lz::RING_BYTES));
     CK(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&dv.find_occ, k_seg_find, FIND_WARPS * 32, FIND_SMEM));
     if (dv.find_occ < 1) dv.find_occ = 1;
     dv.seg_configured = true;
@@ -592,6 +593,12 @@ static int run_segmented(zsb_ctx *ctx, zsb_dev &dv, const zsb_member *dm, zsb_re
         CK(ctx, cudaGetLastError());
         CK(ctx, cudaEventRecord(dv.seg_join2, dv.seg_stream2));
         if (ring_k) {
+            // few members: four warps on each member's ring (270 MB/s per member; one 16 MiB member 83 -> 62 ms); many:
+            // one warp each (C4: 293 ms against 338 ms — with every slot busy the four warps get in each other's way)
+            if (ring_k <= (size_t)dv.sm_count)
+                k_seg_lz_ring_cta<<<(unsigned)std::min(ring_k, (size_t)dv.sm_count * 3), SEGR_THREADS, lz::RING_BYTES, st>>>(B, dplan + m0, (uint32_t)ring_k,
+                                                                                                                         doff + s0, cnt + 2);
+            else
             k_seg_lz_ring<<<(unsigned)std::min(ring_k, (size_t)dv.sm_count * 3), 32, lz::RING_BYTES, st>>>(B, dplan + m0, (uint32_t)ring_k, doff + s0, cnt + 2);
             ctx->launches++;
             CK(ctx, cudaGetLastError());

@@ -33,8 +33,8 @@
 //                depend on a guess.
 //   k_seg_lz_ring / k_seg_lz   the verified segments' sequences become bytes, a warp per member, segment after segment:
 //                with the member's last 64 KiB of output mirrored in a shared-memory ring (1.6x faster for one member,
-//                three members per SM: the wave's largest members), or on global memory (lz::resolve_range: the rest,
-//                and Deflate64 members), side by side.
+//                three members per SM: the wave's largest members; four warps per member when there are few), or on
+//                global memory (lz::resolve_range: the rest, and Deflate64 members), side by side.
 #pragma once
 #include "zsb_lz.cuh"
 
@@ -582,6 +582,123 @@ __global__ void __launch_bounds__(32) k_seg_lz_ring(lane::Batch B, const seg::Me
             if (!g.live || !g.nseq) continue;
             lz::resolve_range_ring<32>((uint8_t *)m.out, (const uint8_t *)m.in, B.seq_base + seq_off[p.first + k], g.nseq, ln, g.base, ring);
             __syncwarp();
+        }
+    }
+}
+
+// The ring resolver with SEGR_WARPS warps on ONE member and one ring: a ROUND is SEGR_WARPS trips of 32 sequences, a warp
+// each.  The warps scan their byte counts and exchange the totals (positions), store their literals and copy every
+// match whose source lies before the round at once; a match that reaches into the round waits until the warps before
+// it have published that those bytes are final (done[w] = the position up to which warp w's trip is final, ~0 when it
+// is complete) — lz::resolve_range's rule with the frontier shared through shared memory.  Sources come from the ring,
+// so what a waiting warp waits for is a shared-memory round trip, not an L2 one.  Rounds are separated by a barrier.
+constexpr int SEGR_WARPS = 4, SEGR_THREADS = SEGR_WARPS * 32;
+__device__ __forceinline__ uint32_t resolve_range_ring_cta(uint8_t *out, const uint8_t *in, const lane::seq_t *seq, uint32_t nseq, uint32_t base,
+                                                           uint8_t *ring, volatile uint32_t *done, uint32_t *tot) {
+    const int ln = threadIdx.x & 31, w = threadIdx.x >> 5;
+    lane::seq_t qn;
+    qn.lo = 0;
+    qn.hi = 0;
+    {
+        const uint32_t i0 = (uint32_t)w * 32u + (uint32_t)ln;
+        if (i0 < nseq) qn = seq[i0];
+    }
+    for (uint32_t c = 0; c < nseq; c += 32 * SEGR_WARPS) {
+        const lane::seq_t q = qn;
+        {
+            const uint32_t tn = c + 32 * SEGR_WARPS + (uint32_t)w * 32u + (uint32_t)ln;      // next round's sequence, requested now
+            qn.lo = 0;
+            qn.hi = 0;
+            if (tn < nseq) qn = seq[tn];
+        }
+        const uint32_t nlit = (q.lo >> lane::Q_NLIT_SHIFT) & 3u;
+        const bool is_match = (q.lo & lane::Q_MATCH) != 0, is_raw = (q.lo & lane::Q_RAW) != 0;
+        uint32_t mlen = 0;
+        if (is_match) mlen = (q.hi >> 16) + ((q.lo & lane::Q_ABSLEN) ? 0u : 3u);
+        if (is_raw) mlen = q.lo & 0xffffu;
+        const uint32_t dist = (q.hi & 0xffffu) + 1u;
+        const uint32_t nbytes = nlit + mlen;
+        uint32_t incl = nbytes;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            const uint32_t v = __shfl_up_sync(0xffffffffu, incl, o);
+            if (ln >= o) incl += v;
+        }
+        if (ln == 31) tot[w] = incl;
+        if (ln == 0) done[w] = 0u;
+        __syncthreads();
+        uint32_t before = 0, all = 0;
+#pragma unroll
+        for (int k = 0; k < SEGR_WARPS; k++) {
+            const uint32_t t = tot[k];
+            before += k < w ? t : 0u;
+            all += t;
+        }
+        const uint32_t mypos = base + before + incl - nbytes;
+        if (nlit > 0) lz::ring_put(out, ring, mypos, q.lo);
+        if (nlit > 1) lz::ring_put(out, ring, mypos + 1, q.lo >> 8);
+        if (nlit > 2) lz::ring_put(out, ring, mypos + 2, q.lo >> 16);
+        const uint32_t mp = mypos + nlit;
+        const bool solo = is_match && mlen <= lz::SHORT && dist >= mlen;
+        bool pending = mlen != 0;
+        const uint64_t need = is_raw ? 0ull : (uint64_t)mp + (dist < mlen ? dist : mlen);
+        __syncwarp();
+        for (;;) {
+            const unsigned pm = __ballot_sync(0xffffffffu, pending);
+            const uint32_t own = pm ? __shfl_sync(0xffffffffu, mp, __ffs(pm) - 1) : 0xffffffffu;
+            if (ln == 0) {
+                __threadfence_block();                       // the bytes written so far are visible before the position is
+                done[w] = own;
+            }
+            if (!pm) break;
+            uint32_t F = own;
+            const uint32_t dv = ln < w ? done[ln] : 0xffffffffu;
+            __threadfence_block();
+            const unsigned inc = __ballot_sync(0xffffffffu, dv != 0xffffffffu);
+            if (inc) {
+                const uint32_t f2 = __shfl_sync(0xffffffffu, dv, __ffs(inc) - 1);
+                F = f2 < F ? f2 : F;
+            }
+            const bool ready = pending && need <= (uint64_t)F + dist;
+            if (ready && solo) lz::lane_copy16_ring(out, ring, mp, mp - dist, mlen);
+            unsigned cm = __ballot_sync(0xffffffffu, ready && !solo);
+            while (cm) {
+                const int src = __ffs(cm) - 1;
+                cm &= cm - 1;
+                const uint32_t p = __shfl_sync(0xffffffffu, mp, src), n = __shfl_sync(0xffffffffu, mlen, src);
+                const uint32_t hi = __shfl_sync(0xffffffffu, q.hi, src);
+                const bool raw = __shfl_sync(0xffffffffu, (uint32_t)is_raw, src) != 0;
+                if (raw) lz::coop_raw_ring<32>(out, ring, p, in + hi, n, ln);
+                else lz::coop_copy_ring<32>(out, ring, p, (hi & 0xffffu) + 1u, n, ln);
+            }
+            if (ready) pending = false;
+            __syncwarp();
+        }
+        __syncthreads();                                  // the round's bytes are final (and in the ring)
+        base += all;
+    }
+    return base;
+}
+
+__global__ void __launch_bounds__(SEGR_THREADS) k_seg_lz_ring_cta(lane::Batch B, const seg::MemberPlan *__restrict__ plan, uint32_t nm,
+                                                                   const uint64_t *__restrict__ seq_off, uint32_t *counter) {
+    extern __shared__ __align__(16) uint8_t ring[];
+    __shared__ uint32_t s_i;
+    __shared__ volatile uint32_t done[SEGR_WARPS];
+    __shared__ uint32_t tot[SEGR_WARPS];
+    for (;;) {
+        if (threadIdx.x == 0) s_i = atomicAdd(counter, 1u);
+        __syncthreads();
+        const uint32_t i = s_i;
+        __syncthreads();
+        if (i >= nm) break;
+        const seg::MemberPlan p = plan[i];
+        const zsb_member m = B.members[p.idx];
+        if (m.window_bits == -16) continue;                    // (k_seg_lz resolves those)
+        for (uint32_t k = 0; k < p.nseg; k++) {
+            const lane::Seg &g = B.segs[p.first + k];
+            if (!g.live || !g.nseq) continue;
+            resolve_range_ring_cta((uint8_t *)m.out, (const uint8_t *)m.in, B.seq_base + seq_off[p.first + k], g.nseq, g.base, ring, done, tot);
         }
     }
 }
