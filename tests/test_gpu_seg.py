@@ -128,3 +128,39 @@ def test_host_batch_with_large_members():
                 assert ao == out, (opts, j, "output differs")
     finally:
         eng.close()
+
+
+def test_checksums_of_large_members_in_parts():
+    """Wrapped members of 2 MiB of output or more have their Adler-32 / CRC-32 computed in parts of 1 MiB by a CTA each
+    and combined (k_check_parts, k_check): sizes around the part boundaries, both wrappers, compressible and stored
+    data, good and damaged trailers — records (check value, ret, msg, total_in) as the oracle's."""
+    import torch
+    import batchlib
+    rnd = random.Random(8)
+    distinct = []
+    for size in (2 << 20, (2 << 20) + 1, (3 << 20) - 1, 3 << 20, (5 << 20) + 12345, (1 << 20) + 77):
+        stored = rnd.randbytes(size)
+        soup = (gen.word_soup(65536, size & 1023) * (size // 65536 + 1))[:size]
+        for wb in (15, 31):
+            for plain, level in ((stored, 0), (soup, 6)):
+                comp = gen.deflate(plain, level, wb)
+                distinct.append((comp, wb, plain))
+                bad = bytearray(comp)
+                bad[-1] ^= 0x40                                   # the trailer: "incorrect data check" / "incorrect length check"
+                distinct.append((bytes(bad), wb, plain))
+                distinct.append((comp[:-3], wb, plain))           # the trailer cut short
+    w = {"distinct": distinct, "tiles": 1, "desc": "large wrapped members"}
+    dev = torch.device("cuda", 0)
+    batch = batchlib.DeviceBatch(w, dev).to_device()
+    eng = zsblib.Zsb(devices=[0])
+    try:
+        st = torch.cuda.current_stream(dev)
+        for segment in (1, 0):
+            eng.set_option("segment", segment)
+            batch.clear_outputs()
+            batch.step(eng, st)
+            torch.cuda.synchronize()
+            bad = batch.verify()
+            assert not bad, (segment, bad[:3])
+    finally:
+        eng.close()
